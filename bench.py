@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native SL hot path (one JSON line on stdout).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload W]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workloads (BASELINE.json configs):
+  encode  configs[1]: 16384 synthetic random-playout 19x19 positions per step through the feature
+          encoder; metric = positions/s; roofline = HBM (18,054 algorithmic bytes per position).
+  train   configs[2]/[3]: SL policy net (13 convs, 192 filters, 48 planes) bf16 training step,
+          batch 256 per GPU; metric = positions/s; roofline = tensor (8.2380 GFLOP per position).
+`value` is device-timed (CUDA events on the launching stream, barrier + synchronize on both
+sides, max over ranks) with inputs resident in HBM; `e2e` goes through the public Python API with
+pinned HOST buffers and counts the copies.  `--impl reference` times the CPU oracle port of the
+reference's algorithm on the host cores (the reference's own Keras/Theano stack is not installable
+here; its Python encoder cannot travel to the GPU box).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FEATS46 = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
+           "liberties_after", "sensibleness", "zeros"]
+ENC_BYTES_PER_POSITION = 48 * 361 + 361 + 361 + 4  # planes out + board + age + player/ko
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "tensor_burst": d["bf16_tflops"], "tensor_sustained": d["bf16_tflops_sustained"],
+                "source": "measured"}
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(object):
+    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.idx = device_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = vis.split(",")[self.idx] if vis else str(self.idx)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", phys, "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            # samples "under load": power above 40% of the maximum seen, else all of them
+            lim = 0.4 * max(pw) if pw else 0
+            load = sorted(s for s, p in zip(sm, pw) if p >= lim) or sorted(sm)
+            out.update(sm_mhz=load[len(load) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=max(pw))
+        return out
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------ encode
+class EncodeWorkload(object):
+    name = "encode"
+    metric = "encode_positions_per_sec"
+    unit = "positions/s"
+    dtype = "u8"
+
+    def __init__(self, n_positions, feats, rank):
+        import numpy as np
+        import torch
+        from alphago_b200 import go
+        from alphago_b200.preprocessing import Preprocess
+        self.torch, self.np = torch, np
+        self.n = n_positions
+        self.feats = feats
+        self.pp = Preprocess(feats)
+        self.size = 19
+        b, a, pl, ko = go.playout_positions(1000 + rank, n_positions, size=19, max_moves=400, per_game=16)
+        # four input variants (board symmetries are again legal positions) so consecutive steps never
+        # re-read the same input lines; each step also writes ~n*17 KB of planes through L2
+        self.host = []
+        for v in range(4):
+            bb = b.reshape(-1, 19, 19); aa = a.reshape(-1, 19, 19)
+            kx, ky = np.divmod(np.maximum(ko, 0), 19)
+            if v & 1:
+                bb, aa, kx, ky = bb.transpose(0, 2, 1), aa.transpose(0, 2, 1), ky, kx
+            if v & 2:
+                bb, aa, kx = bb[:, ::-1, :], aa[:, ::-1, :], 18 - kx
+            kk = np.where(ko >= 0, kx * 19 + ky, -1).astype(np.int16)
+            self.host.append((np.ascontiguousarray(bb).reshape(-1, 361), np.ascontiguousarray(aa).reshape(-1, 361), pl, kk))
+        self.dev = [tuple(torch.from_numpy(x).cuda() for x in h) for h in self.host]
+        self.out = torch.empty((n_positions, self.pp.output_dim, 19, 19), dtype=torch.uint8, device="cuda")
+        self.i = 0
+        self.units_per_step = n_positions
+        self.launches_per_step = 1
+        self.pinned = None
+
+    def step(self):
+        d = self.dev[self.i & 3]
+        self.i += 1
+        self.pp.encode_packed(d[0], d[1], d[2], d[3], self.size, out=self.out)
+
+    def e2e_setup(self):
+        t = self.torch
+        self.pinned = [tuple(t.from_numpy(x).pin_memory() for x in h) for h in self.host]
+        self.pin_out = t.empty(self.out.shape, dtype=t.uint8).pin_memory()
+        self.h2d = sum(x.numel() * x.element_size() for x in self.pinned[0])
+        self.d2h = self.pin_out.numel()
+
+    def e2e_step(self):
+        h = self.pinned[self.i & 3]
+        self.i += 1
+        d = [x.cuda(non_blocking=True) for x in h]
+        self.pp.encode_packed(d[0], d[1], d[2], d[3], self.size, out=self.out)
+        self.pin_out.copy_(self.out, non_blocking=True)
+        self.torch.cuda.current_stream().synchronize()
+        return int(self.pin_out[0, 3, 0, 0])
+
+    def roofline(self, ms_per_step, pk):
+        ach = self.n * ENC_BYTES_PER_POSITION / (ms_per_step * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": round(ach, 2), "peak": pk["hbm"], "unit": "GB/s",
+                "frac": round(ach / pk["hbm"], 5), "traffic": None, "kernel": "ag::enc::encode_kernel",
+                "peak_source": pk["source"] + " (copy bandwidth, kernel timed inside a long step)",
+                "algorithmic_bytes_per_launch": self.n * ENC_BYTES_PER_POSITION}
+
+    def config(self):
+        return {"workload": "feature-plane encoder, %d synthetic random-playout 19x19 positions/step, %d planes (%s)"
+                % (self.n, self.pp.output_dim, ",".join(self.feats)),
+                "positions_per_step": self.n, "planes": self.pp.output_dim,
+                "l2": "4 rotating input sets; each step streams %d MB of output planes through the 126 MB L2"
+                % (self.n * self.pp.output_dim * 361 // 2 ** 20)}
+
+    def cpu_baseline(self, sample=2048):
+        from oracle import go_oracle as og
+        cores = os.cpu_count() or 1
+        h = self.host[0]
+        s = min(sample, self.n)
+        og.encode_batch(h[0][:64], h[1][:64], h[2][:64], h[3][:64], 19, self.feats, threads=cores)
+        t = time.time()
+        og.encode_batch(h[0][:s], h[1][:s], h[2][:s], h[3][:s], 19, self.feats, threads=cores)
+        dt = time.time() - t
+        return {"value": round(s / dt, 1), "unit": self.unit, "cores": cores, "kind": "port",
+                "sample": "%d of the step's positions, C oracle (oracle/go_oracle.c) with OpenMP over all host cores, %.2f s" % (s, dt)}
+
+
+def reference_arm(args, rank):
+    """CPU implementation of the path on the host cores: the oracle port (the reference's Python
+    cannot travel to the GPU box and its Keras/Theano stack is not installable)."""
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle import go_oracle as og
+    cores = os.cpu_count() or 1
+    feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
+    sample = 1024
+    b, a, pl, ko = og.playout_positions(1000, sample, size=19, max_moves=400, per_game=16)
+    for _ in range(args.warmup):
+        og.encode_batch(b[:128], a[:128], pl[:128], ko[:128], 19, feats, threads=cores)
+    t = time.time()
+    for _ in range(args.steps):
+        og.encode_batch(b, a, pl, ko, 19, feats, threads=cores)
+    dt = time.time() - t
+    v = round(args.steps * sample / dt, 1)
+    line = {"impl": "reference", "metric": EncodeWorkload.metric, "value": v, "unit": EncodeWorkload.unit, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "feature-plane encoder on host cores, %d-position sample per step, %d planes" % (sample, og.output_dim(feats))},
+            "cpu_baseline": {"value": v, "unit": EncodeWorkload.unit, "cores": cores, "kind": "port",
+                             "sample": "%d positions per step, C oracle with OpenMP over all host cores" % sample},
+            "e2e": {"value": v, "unit": EncodeWorkload.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=["encode", "train"])
+    ap.add_argument("--positions", type=int, default=16384)
+    ap.add_argument("--planes", type=int, default=46, choices=[46, 48])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world, local = dist_env()
+    workload = args.workload or "encode"
+    if args.steps is None:
+        args.steps = 200 if args.impl == "ours" else 5
+    if args.warmup is None:
+        args.warmup = 5 if args.impl == "ours" else 1
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from alphago_b200 import _lib
+    from oracle import go_oracle as og
+
+    feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
+    wl = EncodeWorkload(args.positions, feats, rank)
+    pk = peaks()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        wl.step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    l0 = _lib.lib().ag_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        wl.step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.lib().ag_launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * wl.units_per_step * args.steps / (ms * 1e-3)
+
+    # end to end through the public API with host buffers
+    wl.e2e_setup()
+    ke = max(3, min(args.steps, 10))
+    wl.e2e_step()
+    barrier()
+    t0 = time.time()
+    for _ in range(ke):
+        wl.e2e_step()
+    torch.cuda.synchronize()
+    te = time.time() - t0
+    if world > 1:
+        t = torch.tensor([te], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        te = float(t.item())
+    e2e = {"value": round(world * wl.units_per_step * ke / te, 1), "unit": wl.unit, "h2d_bytes_per_step": wl.h2d,
+           "d2h_bytes_per_step": wl.d2h, "steps": ke}
+
+    if rank == 0:
+        line = {"metric": wl.metric, "value": round(value, 1), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic", "config": wl.config(),
+                "roofline": wl.roofline(ms_per_step, pk), "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = wl.cpu_baseline()
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,98 @@
+/*
+ * alphago_b200.h -- C ABI of libalphago_b200.so (hand-written sm_100a CUDA, one GPU per process).
+ *
+ * This is the drop-in boundary for the reference's supervised-learning hot path.  The reference
+ * (linghuaj/AlphaGo, a pure-Python project) has no FFI of its own: its boundary is the Python API
+ * Preprocess / CNNPolicy / run_training.  The alphago_b200 Python package keeps that API and binds the entry
+ * points below with ctypes; INTEGRATION.md shows the stub a reference maintainer would add.
+ * Each declaration cites the reference interface it replaces (paths relative to the reference).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative AG_E* code; ag_last_error() gives the text
+ *   - "d_" pointers are DEVICE pointers owned by the caller, "h_" pointers are host pointers
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); no entry point
+ *     synchronises the host unless it says so
+ *   - points are (x,y), flat index x*size+y; planes are [f][x][y] (AlphaGo/util.py:6-8)
+ *   - colours: +1 black, -1 white, 0 empty (AlphaGo/go.py:3-5)
+ *   - thread-compatible, not thread-safe: one caller thread per process/GPU
+ */
+#ifndef ALPHAGO_B200_H
+#define ALPHAGO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AG_OK 0
+#define AG_EINVAL (-1) /* bad argument */
+#define AG_ECUDA (-2)  /* CUDA runtime / driver error */
+#define AG_ENOMEM (-3)
+#define AG_ESTATE (-4) /* illegal move, wrong object state */
+
+/* feature ids: order of DEFAULT_FEATURES (AlphaGo/preprocessing/preprocessing.py:211-214);
+ * AG_F_COLOR is the value net's 49th "side to move is black" plane (AlphaGo/models/value.py:16). */
+enum {
+    AG_F_BOARD = 0, AG_F_ONES, AG_F_TURNS_SINCE, AG_F_LIBERTIES, AG_F_CAPTURE_SIZE, AG_F_SELF_ATARI_SIZE,
+    AG_F_LIBERTIES_AFTER, AG_F_LADDER_CAPTURE, AG_F_LADDER_ESCAPE, AG_F_SENSIBLENESS, AG_F_ZEROS, AG_F_COLOR,
+    AG_F_COUNT
+};
+
+/* ------------------------------------------------------------------ library */
+const char* ag_last_error(void);
+int ag_version(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+long long ag_launch_count(void);
+/* planes a feature contributes (FEATURES[name]["size"], preprocessing.py:164-209); -1 if unknown */
+int ag_feature_planes(int feature);
+
+/* ------------------------------------------------------------------ stage 1: feature encoder
+ * Replaces Preprocess.state_to_tensor (preprocessing.py:238-245) and the eleven feature functions
+ * it calls (preprocessing.py:9-161, on go.py:63-267) for a batch of n positions of one board size.
+ *   d_board  int8  [n][size*size]   GameState.board (go.py:14)
+ *   d_age    uint8 [n][size*size]   turns_since input: ag_age_from_history() of (history, board)
+ *   d_player int8  [n]              GameState.current_player
+ *   d_ko     int16 [n]              GameState.ko as flat index, -1 for None (an INPUT: go.py:322-331
+ *                                   can leave a stale ko that cannot be re-derived from the board)
+ *   h_features / n_features         feature ids in list order (any subset, order, repeats)
+ *   d_out    uint8 [n][planes][size*size], one-hot 0/1 (the reference emits the same values as float64)
+ * size in {2..19}; total planes <= 64. */
+int ag_encode(const int8_t* d_board, const uint8_t* d_age, const int8_t* d_player, const int16_t* d_ko,
+              int n, int size, const int32_t* h_features, int n_features, uint8_t* d_out, void* stream);
+
+/* ------------------------------------------------------------------ host rules engine
+ * Backs alphago_b200.go.GameState (the product's mirror of AlphaGo/go.py:9-349) and the synthetic
+ * random-playout generator.  Pure host code. */
+typedef struct ag_state ag_state;
+ag_state* ag_state_new(int size);                                  /* go.py:13-45 */
+ag_state* ag_state_copy(const ag_state* s);                        /* go.py:159-179 (history de-aliased) */
+void ag_state_free(ag_state* s);
+int ag_state_do_move(ag_state* s, int point, int colour);          /* go.py:295-349; point -1 = pass; colour 0 = side to move; AG_ESTATE = IllegalMove */
+int ag_state_is_legal(ag_state* s, int point);                     /* go.py:204-216 */
+int ag_state_is_eyeish(ag_state* s, int point, int owner);         /* go.py:218-228 */
+int ag_state_is_eye(ag_state* s, int point, int owner);            /* go.py:230-259 */
+int ag_state_legal_moves(ag_state* s, int include_eyes, int16_t* h_out); /* go.py:261-267; returns count */
+int ag_state_winner(const ag_state* s, double komi);               /* go.py:269-293 */
+/* scalar fields: 0 size, 1 current_player, 2 ko, 3 len(history), 4 is_end_of_game, 5 turns_played,
+ * 6 num_black_prisoners, 7 num_white_prisoners, 8 passes_black, 9 passes_white */
+int ag_state_get(const ag_state* s, int field);
+int ag_state_set_player(ag_state* s, int colour);
+int ag_state_set_ko(ag_state* s, int point);
+void ag_state_board(const ag_state* s, int8_t* h_board);
+void ag_state_history(const ag_state* s, int16_t* h_hist);
+/* per-point group id (-1 empty), stones and liberties of the point's group (liberty_counts, go.py:40) */
+void ag_state_groups(ag_state* s, int16_t* h_gid, int16_t* h_stones, int16_t* h_libs);
+/* encoder inputs of this state */
+void ag_state_pack(const ag_state* s, int8_t* h_board, uint8_t* h_age, int8_t* h_player, int16_t* h_ko);
+/* the literal turns_since walk (preprocessing.py:20-43) for any (history, board) pair */
+void ag_age_from_history(int size, const int8_t* h_board, const int16_t* h_hist, int n_hist, uint8_t* h_age);
+/* n positions from seeded random playouts, uniform over get_legal_moves(include_eyes=False)
+ * (AlphaGo/ai.py:15), `per_game` snapshots per game at move numbers uniform in [0, max_moves] */
+int ag_playout_positions(uint64_t seed, int n, int size, int max_moves, int per_game,
+                         int8_t* h_board, uint8_t* h_age, int8_t* h_player, int16_t* h_ko);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ALPHAGO_B200_H */
