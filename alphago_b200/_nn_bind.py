@@ -1,5 +1,22 @@
-"""ctypes signatures of the network entry points (stage 2); filled in as they are built."""
+"""ctypes signatures of the network entry points (stage 2 of include/alphago_b200.h)."""
+import ctypes as C
 
 
 def bind(L):
+    vp, i = C.c_void_p, C.c_int
+    L.ag_net_create.restype = vp
+    L.ag_net_create.argtypes = [i, i, i, vp, vp, i, i]
+    L.ag_net_destroy.argtypes = [vp]; L.ag_net_destroy.restype = None
+    L.ag_net_layer_info.argtypes = [vp, i, i]
+    L.ag_net_set_conv.argtypes = [vp, i, vp, vp]
+    L.ag_net_get_conv.argtypes = [vp, i, vp, vp]
+    L.ag_net_set_head.argtypes = [vp, i, vp, vp]
+    L.ag_net_get_head.argtypes = [vp, i, vp, vp]
+    L.ag_net_forward.argtypes = [vp, vp, i, vp, vp]
+    L.ag_net_forward_loss.argtypes = [vp, vp, vp, i, vp, vp, vp]
+    L.ag_net_backward_layer.argtypes = [vp, i, i, vp]
+    L.ag_net_grads.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_longlong), vp]
+    L.ag_net_sgd.argtypes = [vp, C.c_float, C.c_float, C.c_float, vp]
+    L.ag_net_train_step.argtypes = [vp, vp, vp, i, C.c_float, C.c_float, vp, vp]
+    L.ag_net_debug_read.argtypes = [vp, i, i, i, vp]
     return L

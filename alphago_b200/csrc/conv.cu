@@ -1,0 +1,228 @@
+// Implicit-GEMM convolution for the policy/value conv stack (AlphaGo/models/policy.py:119-150,
+// AlphaGo/models/value.py:14-25; in the reference these are Keras Convolution2D layers executed by
+// Theano).  One persistent, warp-specialised tcgen05 kernel serves every KxK 'same' layer, forward
+// and data-gradient:
+//
+//     D[m, co] = sum_taps sum_ci A[m + shift(tap), ci] * W[tap][co][ci]
+//
+// A is the padded-pixel-row activation matrix (conv.cuh), so each tap is a row-shifted TMA box of
+// the same 2D tensor; W[tap] is a K-major [co][ci] matrix.  Per CTA: 128 output rows x N channels,
+// accumulated in TMEM (two accumulator buffers so the epilogue of tile i overlaps the MMAs of
+// tile i+1), K streamed in 64-channel slices through a 4-stage TMA->smem ring.
+//   warp 0    TMA producer (one elected lane)
+//   warp 1    TMEM allocation + UMMA issue (one elected lane)
+//   warps 2-5 epilogue: tcgen05.ld -> bias / ReLU / ReLU-gate -> bf16 -> global (pad rows skipped)
+#include "common.cuh"
+#include "conv.cuh"
+#include "tcgen.cuh"
+
+namespace ag {
+
+namespace {
+
+constexpr int kTileM = 128;
+constexpr int kStages = 4;
+constexpr int kABytes = kTileM * 128;  // 128 rows x 64 bf16
+constexpr int kThreads = 192;
+constexpr int kAccStride = 256;  // TMEM columns between the two accumulator buffers
+constexpr int kTmemCols = 512;
+
+struct __align__(8) ConvBarriers {
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const ConvArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    // carve: stages x (A | B), then barriers, then bias
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    const int b_bytes = p.n * 128;
+    const int stage_bytes = kABytes + b_bytes;
+    ConvBarriers* bars = reinterpret_cast<ConvBarriers*>(base + kStages * stage_bytes);
+    float* s_bias = reinterpret_cast<float*>(bars + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tiles = (p.m_total + kTileM - 1) / kTileM;
+    const int kblocks = p.taps * p.kchunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 128); }
+        tc::fence_mbar_init();
+        tc::tma_prefetch_desc(&tmap_a);
+        tc::tma_prefetch_desc(&tmap_b);
+    }
+    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
+    if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ===== TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m0 = tile * kTileM;
+                for (int t = 0; t < p.taps; t++) {
+                    const int arow = m0 + p.off[t];
+                    for (int kc = 0; kc < p.kchunks; kc++) {
+                        tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                        uint8_t* sa = base + stage * stage_bytes;
+                        tc::mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
+                        tc::tma_load_2d(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
+                        tc::tma_load_2d(sa + kABytes, &tmap_b, &bars->full[stage], kc * 64, t * p.b_tap_rows);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== UMMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = tc::idesc_bf16(kTileM, p.n, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+                const int buf = it & 1;
+                tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t d_tmem = tmem_base + buf * kAccStride;
+                for (int kb = 0; kb < kblocks; kb++) {
+                    tc::mbar_wait(&bars->full[stage], phase);
+                    tc::fence_after_sync();
+                    const uint32_t sa = tc::smem_u32(base + stage * stage_bytes);
+                    const uint64_t adesc = tc::desc_kmajor_sw128(sa);
+                    const uint64_t bdesc = tc::desc_kmajor_sw128(sa + kABytes);
+#pragma unroll
+                    for (int k = 0; k < 4; k++)  // 4 x K=16 inside the 64-channel slice: +32 B each
+                        tc::umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    tc::umma_commit(&bars->empty[stage]);  // frees the smem slot when these MMAs retire
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                tc::umma_commit(&bars->acc_full[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: warp w may only touch TMEM lanes [32*(w%4), +32)
+        const int q = warp & 3;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+            const int buf = it & 1;
+            const int m = tile * kTileM + q * 32 + lane;
+            // decode the GEMM row into (image, x, y); pad slots produce no output
+            const int img = m / p.in.img_stride;
+            const int rem = m - img * p.in.img_stride;
+            const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
+            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size;
+            const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
+            __nv_bfloat16* dst = p.out + orow * p.out_ld;
+            const __nv_bfloat16* gate = nullptr;
+            if (p.gate)
+                gate = p.gate + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * p.gate_ld;
+            tc::mbar_wait(&bars->acc_full[buf], (it >> 1) & 1);
+            tc::fence_after_sync();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride;
+            for (int c0 = 0; c0 < p.n; c0 += 32) {
+                uint32_t r[32];
+                tc::tmem_ld32(taddr + c0, r);
+                tc::tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int g = 0; g < 4; g++) {  // 8 channels -> one 16-byte store
+                        if (c0 + g * 8 < p.n) {
+                            float v[8];
+#pragma unroll
+                            for (int j = 0; j < 8; j++) v[j] = __uint_as_float(r[g * 8 + j]) + s_bias[c0 + g * 8 + j];
+                            if (p.relu) {
+#pragma unroll
+                                for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
+                            }
+                            if (gate) {
+                                uint4 gv = *reinterpret_cast<const uint4*>(gate + c0 + g * 8);
+                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gv);
+#pragma unroll
+                                for (int j = 0; j < 8; j++) v[j] = __bfloat162float(gb[j]) > 0.f ? v[j] : 0.f;
+                            }
+                            uint4 o;
+                            __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                            for (int j = 0; j < 4; j++) ob[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            *reinterpret_cast<uint4*>(dst + c0 + g * 8) = o;
+                        }
+                    }
+                }
+            }
+            tc::fence_before_sync();
+            tc::mbar_arrive(&bars->acc_empty[buf]);
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+}  // namespace
+
+int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return AG_ECUDA; }
+    if (cols % 64 != 0 || box_rows == 0 || box_rows > 256) { set_error("make_tmap_2d: cols %llu / box_rows %u unsupported", (unsigned long long)cols, box_rows); return AG_EINVAL; }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu box=%u", (int)r, (unsigned long long)rows, (unsigned long long)cols, box_rows); return AG_ECUDA; }
+    return AG_OK;
+}
+
+static size_t conv_smem_bytes(int n) { return 1024 + (size_t)kStages * (kABytes + n * 128) + sizeof(ConvBarriers) + 256 * sizeof(float); }
+
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvArgs& args, cudaStream_t stream) {
+    if (args.n < 16 || args.n > 256 || args.n % 16 != 0) { set_error("conv: N=%d must be a multiple of 16 in [16,256]", args.n); return AG_EINVAL; }
+    if (args.taps < 1 || args.taps > kConvMaxTaps || args.kchunks < 1) { set_error("conv: bad taps/kchunks"); return AG_EINVAL; }
+    static size_t configured = 0;
+    size_t smem = conv_smem_bytes(args.n);
+    if (smem > 227 * 1024) { set_error("conv: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
+    if (smem > configured) {
+        AG_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    int tiles = (args.m_total + kTileM - 1) / kTileM;
+    int grid = tiles < sm_count() ? tiles : sm_count();
+    if (grid < 1) return AG_OK;
+    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, args);
+    AG_LAUNCH_CHECK("conv_gemm_kernel");
+    return AG_OK;
+}
+
+}  // namespace ag

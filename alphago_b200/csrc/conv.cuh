@@ -1,0 +1,49 @@
+// Shifted-window implicit-GEMM convolution on tcgen05 (see conv.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ag {
+
+// Activation layout in HBM ("padded pixel rows"): a bf16 matrix [rows][C] whose row index is
+//   m = n*img_stride + x*row_stride + y      (x, y in [0, size); n = image)
+// with at least `pad` all-zero slots after every board row and `pad` all-zero board rows after
+// every image, so a KxK 'same' convolution tap (dx, dy) is the plain row shift dx*row_stride + dy:
+// the halo is read from the zero slots (and, before the first / after the last image, from TMA's
+// out-of-bounds zero fill).  3x3 layers use (row_stride, img_stride) = (20, 400); the 5x5 first
+// layer reads (21, 441).  Pad slots are never written after the one-time zero fill.
+struct PixelLayout {
+    int size;        // board edge (19)
+    int row_stride;  // slots per board row
+    int img_stride;  // slots per image
+};
+
+constexpr int kConvMaxTaps = 25;
+
+struct ConvArgs {
+    int m_total;          // rows of the A matrix the GEMM covers (= images * in.img_stride)
+    int n;                // output channels of this GEMM (UMMA N): multiple of 8... 16, <= 256
+    int taps;
+    int kchunks;          // K per tap / 64
+    int off[kConvMaxTaps];  // A row shift per tap
+    int b_tap_rows;       // rows of the B tensor per tap (tap t's matrix starts at row t*b_tap_rows)
+    PixelLayout in, dst;  // row decode of the GEMM's M index, and where the result row goes
+    const float* bias;    // [n] or nullptr
+    const __nv_bfloat16* gate;  // nullptr, or rows in gate_layout, gate_ld wide: result zeroed where gate <= 0 (ReLU backward)
+    PixelLayout gate_layout;
+    int gate_ld;
+    __nv_bfloat16* out;   // rows in dst layout, out_ld wide
+    int out_ld;
+    int relu;
+};
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no libcuda link dependency).
+// 2D bf16 matrix [rows][cols], box [box_rows][64 columns], 128-byte swizzle, zero OOB fill.
+int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows);
+
+// D[m, :] = sum_t sum_k A[m + off[t], k] * B[t][:, k]   (+bias, ReLU / gate), bf16 in, fp32 accumulate
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvArgs& args, cudaStream_t stream);
+
+}  // namespace ag

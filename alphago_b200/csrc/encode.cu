@@ -107,11 +107,13 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
     const int16_t* __restrict__ g_ko, int npos, int size, PlaneTable tab, uint8_t* __restrict__ g_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint8_t s_arr[MAX_PLANES], s_val[MAX_PLANES];
+    __shared__ uint16_t s_xy[NPAD];  // x | y << 8 of every point: replaces p / size in the hot loops
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpMem& W = reinterpret_cast<WarpMem*>(smem_raw)[warp];
     const int n = size * size;
     const int F = tab.n_planes;
     for (int i = threadIdx.x; i < F; i += blockDim.x) { s_arr[i] = tab.arr[i]; s_val[i] = tab.val[i]; }
+    for (int i = threadIdx.x; i < NPAD; i += blockDim.x) { int x = i / size; s_xy[i] = (uint16_t)(x | ((i - x * size) << 8)); }
     __syncthreads();
     uint8_t* const codes = reinterpret_cast<uint8_t*>(W.codes);  // [N_CODE][CODE_STRIDE]
 #define CODE(a, p) codes[(a) * CODE_STRIDE + (p)]
@@ -146,7 +148,7 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
             for (int p = lane; p < n; p += 32) {
                 int c = W.col[p];
                 if (c == 0) continue;
-                int x = p / size, y = p - x * size;
+                const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
 #pragma unroll
                 for (int e = 0; e < 2; e++) {
                     int q = e == 0 ? p + 1 : p + size;
@@ -171,7 +173,7 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
         for (int p = lane; p < n; p += 32) {
             int c = W.col[p];
             if (c != 0) { atomicAdd(&W.cnt[label[p]], 1u << 16); continue; }
-            int x = p / size, y = p - x * size;
+            const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
             uint32_t r[4]; int k = 0;
             if (x > 0 && W.col[p - size] != 0) r[k++] = label[p - size];
             if (x < size - 1 && W.col[p + size] != 0) r[k++] = label[p + size];
@@ -195,7 +197,7 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
                 int l = W.cnt[label[p]] & 0xFFFF;                         // preprocessing.py:46-61
                 if (l >= 1) c_libs = (uint8_t)(l >= 8 ? 7 : l - 1);
             } else if (p < n) {
-                int x = p / size, y = p - x * size;
+                const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
                 int nb[4], k = 0;                                        // go.py:96 order
                 if (x > 0) nb[k++] = p - size;
                 if (x < size - 1) nb[k++] = p + size;
@@ -260,43 +262,46 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
         }
         __syncwarp();
 
-        // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (code[arr][p] == val)
-        const size_t total = (size_t)F * n;
+        // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (code[arr][p] == val).
+        // A position's planes are one contiguous run of F*n bytes: a few head bytes up to the next
+        // 16-byte boundary, 16-byte vectors, a few tail bytes.
+        const int total = F * n;
         uint8_t* out = g_out + (size_t)pos * total;
-        if ((total & 15) == 0 && (reinterpret_cast<uintptr_t>(g_out) & 15) == 0) {
-            const int nvec = (int)(total >> 4);
-            for (int v = lane; v < nvec; v += 32) {
-                int i0 = v << 4;
-                int plane = i0 / n, p = i0 - plane * n;
-                uint32_t wds[4];
+        int lead = (int)((16 - (reinterpret_cast<uintptr_t>(out) & 15)) & 15);
+        if (lead > total) lead = total;
+        const int nvec = (total - lead) >> 4;
+        const int tail0 = lead + (nvec << 4);
+        for (int i = lane; i < lead + (total - tail0); i += 32) {
+            int b = i < lead ? i : tail0 + (i - lead);
+            int plane = b / n, p = b - plane * n;
+            out[b] = CODE(s_arr[plane], p) == s_val[plane];
+        }
+        for (int v = lane; v < nvec; v += 32) {
+            int i0 = lead + (v << 4);
+            int plane = i0 / n, p = i0 - plane * n;
+            uint32_t wds[4];
 #pragma unroll
-                for (int w = 0; w < 4; w++) {
-                    uint32_t word;
-                    if (p + 3 < n) {
-                        const uint32_t* ca = W.codes[s_arr[plane]];
-                        uint32_t lo = ca[p >> 2], hi = ca[(p >> 2) + 1];
-                        uint32_t cv = __funnelshift_r(lo, hi, (p & 3) * 8);
-                        word = __vcmpeq4(cv, s_val[plane] * 0x01010101u) & 0x01010101u;
-                        p += 4;
-                        if (p == n) { p = 0; plane++; }
-                    } else {
-                        word = 0;
+            for (int w = 0; w < 4; w++) {
+                uint32_t word;
+                if (p + 3 < n) {
+                    const uint32_t* ca = W.codes[s_arr[plane]];
+                    uint32_t lo = ca[p >> 2], hi = ca[(p >> 2) + 1];
+                    uint32_t cv = __funnelshift_r(lo, hi, (p & 3) * 8);
+                    word = __vcmpeq4(cv, s_val[plane] * 0x01010101u) & 0x01010101u;
+                    p += 4;
+                    if (p == n) { p = 0; plane++; }
+                } else {
+                    word = 0;
 #pragma unroll
-                        for (int b = 0; b < 4; b++) {
-                            uint32_t bit = (plane < F) && (CODE(s_arr[plane], p) == s_val[plane]);
-                            word |= bit << (8 * b);
-                            if (++p == n) { p = 0; plane++; }
-                        }
+                    for (int b = 0; b < 4; b++) {
+                        uint32_t bit = (plane < F) && (CODE(s_arr[plane], p) == s_val[plane]);
+                        word |= bit << (8 * b);
+                        if (++p == n) { p = 0; plane++; }
                     }
-                    wds[w] = word;
                 }
-                reinterpret_cast<uint4*>(out)[v] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+                wds[w] = word;
             }
-        } else {
-            for (int i = lane; i < (int)total; i += 32) {
-                int plane = i / n, p = i - plane * n;
-                out[i] = CODE(s_arr[plane], p) == s_val[plane];
-            }
+            *reinterpret_cast<uint4*>(out + i0) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
         }
         __syncwarp();
     }

@@ -1,0 +1,812 @@
+// The conv-stack network object behind CNNPolicy / CNNValue (AlphaGo/models/policy.py:93-156,
+// AlphaGo/models/value.py:12-28) and its SL training step (supervised_policy_trainer.py:199-213):
+// device buffers, weight import/export, forward, fused softmax/cross-entropy head, backward and the
+// SGD update.  The GEMM-shaped work runs in conv.cu / wgrad.cu (tcgen05); this file holds the
+// memory-bound kernels around them and the orchestration.  Everything is allocated in
+// ag_net_create; no entry point allocates or synchronises afterwards (except the host<->device
+// weight/debug copies, which say so).
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "conv.cuh"
+#include "wgrad.cuh"
+
+namespace ag {
+
+typedef __nv_bfloat16 bf16;
+
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// ------------------------------------------------------------------------------------ kernels
+
+// uint8 planes [n][C][S][S] (the encoder's / HDF5 layout) -> bf16 padded-pixel rows [n*img_stride][64k]
+// for the first conv layer; channels >= C and pad slots stay zero (buffer zero-filled once).
+__global__ void pack_input_kernel(const uint8_t* __restrict__ planes, int n, int C, int S, PixelLayout L, int ld,
+                                  bf16* __restrict__ out) {
+    // one thread per (image, point, 8-channel group): reads 8 planes' bytes, writes 16 B
+    const int groups = ld / 8;
+    const int pts = S * S;
+    size_t total = (size_t)n * pts * groups;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int p = (int)(i % pts);
+        size_t r = i / pts;
+        int g = (int)(r % groups);
+        int img = (int)(r / groups);
+        int x = p / S, y = p - x * S;
+        uint4 o;
+        bf16* ob = reinterpret_cast<bf16*>(&o);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            int c = g * 8 + j;
+            float v = c < C ? (float)planes[((size_t)img * C + c) * pts + p] : 0.f;
+            ob[j] = __float2bfloat16(v);
+        }
+        size_t row = (size_t)img * L.img_stride + (size_t)x * L.row_stride + y;
+        *reinterpret_cast<uint4*>(out + row * ld + g * 8) = o;
+    }
+}
+
+// Policy head, forward (+ backward when labels are given).  One CTA per image.
+//   logits[p] = sum_c X[p][c] * w[c] + b (+ pos_bias[p])          policy.py:144-150 (1x1 conv, Flatten)
+//   probs = softmax(logits)                                        policy.py:154
+//   loss  = -log(clip(probs[label], 1e-7, 1-1e-7)), acc = argmax == label   spt.py:200 (Keras CE / accuracy)
+//   dlogit = (probs - onehot) * inv_batch; G[p][c] = dlogit[p] * w[c] * (X[p][c] > 0)
+//   per-image partials of dw[c], db, dpos[p] go to `partial` (reduced by head_reduce_kernel)
+constexpr int kHeadThreads = 384;
+__global__ void __launch_bounds__(kHeadThreads)
+policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float* __restrict__ w, const float* __restrict__ bias,
+                   const float* __restrict__ pos_bias, float* __restrict__ probs, const int32_t* __restrict__ labels,
+                   float inv_batch, bf16* __restrict__ G, float* __restrict__ partial, float* __restrict__ loss_acc,
+                   float* __restrict__ dlogits_out) {
+    __shared__ float s_logit[368];
+    __shared__ float s_w[256];
+    __shared__ float s_red[kHeadThreads / 32];
+    __shared__ float s_dw[kHeadThreads / 32][256];  // per-warp partials, summed in warp order (deterministic)
+    const int img = blockIdx.x, S = L.size, pts = S * S;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kHeadThreads / 32;
+    for (int c = threadIdx.x; c < 256; c += kHeadThreads) s_w[c] = c < ld ? w[c] : 0.f;
+    __syncthreads();
+    const int groups = ld / 8;  // 16-byte groups per row; lanes >= groups idle (ld <= 256)
+    const float b0 = bias[0];
+    for (int p = warp; p < pts; p += nwarps) {
+        int x = p / S, y = p - x * S;
+        const bf16* row = X + ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld;
+        float acc = 0.f;
+        if (lane < groups) {
+            uint4 v = *reinterpret_cast<const uint4*>(row + lane * 8);
+            const bf16* vb = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * s_w[lane * 8 + j];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) s_logit[p] = acc + b0 + (pos_bias ? pos_bias[p] : 0.f);
+    }
+    __syncthreads();
+    // softmax over pts (block reductions)
+    float mx = -INFINITY;
+    for (int p = threadIdx.x; p < pts; p += kHeadThreads) mx = fmaxf(mx, s_logit[p]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
+    mx = s_red[0];
+    for (int i = 1; i < nwarps; i++) mx = fmaxf(mx, s_red[i]);
+    __syncthreads();
+    float sum = 0.f;
+    for (int p = threadIdx.x; p < pts; p += kHeadThreads) { float e = expf(s_logit[p] - mx); s_logit[p] = e; sum += e; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) s_red[warp] = sum;
+    __syncthreads();
+    sum = 0.f;
+    for (int i = 0; i < nwarps; i++) sum += s_red[i];
+    const float inv = 1.f / sum;
+    for (int p = threadIdx.x; p < pts; p += kHeadThreads) {
+        float pr = s_logit[p] * inv;
+        s_logit[p] = pr;
+        if (probs) probs[(size_t)img * pts + p] = pr;
+    }
+    __syncthreads();
+    if (!labels) return;
+
+    const int label = labels[img];
+    if (threadIdx.x == 0) {
+        // accuracy: first maximum, as numpy/Theano argmax
+        int best = 0;
+        float bv = s_logit[0];
+        for (int p = 1; p < pts; p++) if (s_logit[p] > bv) { bv = s_logit[p]; best = p; }
+        float pl = fminf(fmaxf(s_logit[label], 1e-7f), 1.f - 1e-7f);
+        atomicAdd(&loss_acc[0], -logf(pl));
+        atomicAdd(&loss_acc[1], best == label ? 1.f : 0.f);
+    }
+    __syncthreads();
+    // dlogit in place
+    float dbl = 0.f;
+    for (int p = threadIdx.x; p < pts; p += kHeadThreads) {
+        float d = (s_logit[p] - (p == label ? 1.f : 0.f)) * inv_batch;
+        s_logit[p] = d;
+        dbl += d;
+        if (dlogits_out) dlogits_out[(size_t)img * pts + p] = d;
+        if (partial) partial[(size_t)img * (256 + 1 + 368) + 257 + p] = d;  // d(pos_bias)
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dbl += __shfl_xor_sync(0xffffffffu, dbl, o);
+    __syncthreads();
+    if (lane == 0) s_red[warp] = dbl;
+    __syncthreads();
+    // G rows and dw partial
+    float dw[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int p = warp; p < pts; p += nwarps) {
+        int x = p / S, y = p - x * S;
+        size_t roff = ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld;
+        float d = s_logit[p];
+        if (lane < groups) {
+            uint4 v = *reinterpret_cast<const uint4*>(X + roff + lane * 8);
+            const bf16* vb = reinterpret_cast<const bf16*>(&v);
+            uint4 o;
+            bf16* ob = reinterpret_cast<bf16*>(&o);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                float xv = __bfloat162float(vb[j]);
+                dw[j] += d * xv;
+                ob[j] = __float2bfloat16(xv > 0.f ? d * s_w[lane * 8 + j] : 0.f);
+            }
+            *reinterpret_cast<uint4*>(G + roff + lane * 8) = o;
+        }
+    }
+    if (lane < groups) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) s_dw[warp][lane * 8 + j] = dw[j];
+    }
+    __syncthreads();
+    if (partial) {
+        float* pp = partial + (size_t)img * (256 + 1 + 368);
+        for (int c = threadIdx.x; c < ld; c += kHeadThreads) {
+            float t = 0.f;
+            for (int k = 0; k < nwarps; k++) t += s_dw[k][c];
+            pp[c] = t;
+        }
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int i = 0; i < nwarps; i++) t += s_red[i];
+            pp[256] = t;
+        }
+    }
+}
+
+// sums the per-image head partials [n][625] -> grads: dw[ld], db[1], dpos[pts]
+__global__ void head_reduce_kernel(const float* __restrict__ partial, int n, int ld, int pts, float* __restrict__ dw,
+                                   float* __restrict__ db, float* __restrict__ dpos) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 256 + 1 + 368) return;
+    float s = 0.f;
+    for (int k = 0; k < n; k++) s += partial[(size_t)k * 625 + i];
+    if (i < 256) { if (i < ld) dw[i] = s; }
+    else if (i == 256) db[0] = s;
+    else if (i - 257 < pts && dpos) dpos[i - 257] = s;
+}
+
+// Value head (value.py:23-28): 1x1 conv -> Flatten -> Dense(256, linear) -> Dense(1, tanh).  One CTA per image.
+__global__ void __launch_bounds__(256)
+value_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float* __restrict__ w, const float* __restrict__ bias,
+                  const float* __restrict__ W1, const float* __restrict__ b1, const float* __restrict__ w2,
+                  const float* __restrict__ b2, int hidden, float* __restrict__ out) {
+    __shared__ float s_v[368];
+    __shared__ float s_w[256];
+    __shared__ float s_red[8];
+    const int img = blockIdx.x, S = L.size, pts = S * S;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int c = threadIdx.x; c < 256; c += 256) s_w[c] = c < ld ? w[c] : 0.f;
+    __syncthreads();
+    const int groups = ld / 8;
+    for (int p = warp; p < pts; p += 8) {
+        int x = p / S, y = p - x * S;
+        const bf16* row = X + ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld;
+        float acc = 0.f;
+        if (lane < groups) {
+            uint4 v = *reinterpret_cast<const uint4*>(row + lane * 8);
+            const bf16* vb = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * s_w[lane * 8 + j];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) s_v[p] = acc + bias[0];
+    }
+    __syncthreads();
+    float part = 0.f;
+    for (int h = threadIdx.x; h < hidden; h += 256) {
+        const float* wr = W1 + (size_t)h * pts;
+        float a = b1[h];
+        for (int p = 0; p < pts; p++) a += wr[p] * s_v[p];
+        part += a * w2[h];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) s_red[warp] = part;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = b2[0];
+        for (int i = 0; i < 8; i++) t += s_red[i];
+        out[img] = tanhf(t);
+    }
+}
+
+// bias gradient: db[c] = sum_m G[m][c]; two deterministic stages (row slabs, then slabs)
+__global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restrict__ G, size_t rows, int ld, float* __restrict__ part) {
+    __shared__ float s[256][9];
+    const int groups = ld / 8, lanes = 256 / groups;
+    const int g = threadIdx.x % groups, rl = threadIdx.x / groups;
+    size_t per = (rows + gridDim.x - 1) / gridDim.x;
+    size_t r0 = blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
+    float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (rl < lanes)
+        for (size_t r = r0 + rl; r < r1; r += lanes) {
+            uint4 v = *reinterpret_cast<const uint4*>(G + r * ld + g * 8);
+            const bf16* vb = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+            for (int j = 0; j < 8; j++) a[j] += __bfloat162float(vb[j]);
+        }
+#pragma unroll
+    for (int j = 0; j < 8; j++) s[threadIdx.x][j] = a[j];
+    __syncthreads();
+    if (threadIdx.x < ld) {
+        int gg = threadIdx.x / 8, j = threadIdx.x % 8;
+        float t = 0.f;
+        for (int k = 0; k < lanes; k++) t += s[k * groups + gg][j];
+        part[(size_t)blockIdx.x * ld + threadIdx.x] = t;
+    }
+}
+__global__ void colsum_stage2_kernel(const float* __restrict__ part, int nblocks, int ld, int cout, float* __restrict__ db) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cout) return;
+    float t = 0.f;
+    for (int b = 0; b < nblocks; b++) t += part[(size_t)b * ld + c];
+    db[c] = t;
+}
+
+// SGD with momentum (Keras 1.0 SGD.get_updates: v = momentum*v - lr*g; w += v), one launch per layer.
+// Refreshes the bf16 operand copies: wf [tap][co][ci] (forward) and wb [tap][ci][co] (data gradient).
+__global__ void sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, size_t count, int taps,
+                                int ldout, int kin, float lr, float momentum, float gscale, bf16* __restrict__ wf, bf16* __restrict__ wb,
+                                float* __restrict__ b, float* __restrict__ bvel, const float* __restrict__ gb, int nbias) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count + nbias; i += (size_t)gridDim.x * blockDim.x) {
+        if (i < count) {
+            float v = momentum * vel[i] - lr * g[i] * gscale;
+            vel[i] = v;
+            float nw = w[i] + v;
+            w[i] = nw;
+            bf16 h = __float2bfloat16(nw);
+            wf[i] = h;
+            if (wb) {
+                int ci = (int)(i % kin);
+                size_t r = i / kin;
+                int co = (int)(r % ldout);
+                int t = (int)(r / ldout);
+                wb[((size_t)t * kin + ci) * ldout + co] = h;
+            }
+        } else {
+            size_t j = i - count;
+            float v = momentum * bvel[j] - lr * gb[j] * gscale;
+            bvel[j] = v;
+            b[j] += v;
+        }
+    }
+}
+__global__ void sgd_flat_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, size_t count, float lr,
+                                float momentum, float gscale) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        float v = momentum * vel[i] - lr * g[i] * gscale;
+        vel[i] = v;
+        w[i] += v;
+    }
+}
+// debug / test: padded-pixel rows -> fp32 [n][C][S][S]
+__global__ void unpack_rows_kernel(const bf16* __restrict__ rows, int n, int C, int S, PixelLayout L, int ld, float* __restrict__ out) {
+    size_t total = (size_t)n * C * S * S;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int p = (int)(i % (S * S));
+        size_t r = i / (S * S);
+        int c = (int)(r % C);
+        int img = (int)(r / C);
+        int x = p / S, y = p - x * S;
+        out[i] = __bfloat162float(rows[((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld + c]);
+    }
+}
+
+// ------------------------------------------------------------------------------------ net object
+
+struct ConvLayer {
+    int cin, cout, width, taps, pad;
+    int kin;    // input row length (cin padded to 64)
+    int ldout;  // output row length (cout padded to 64)
+    int nout;   // UMMA N forward (cout padded to 16)
+    int nin;    // UMMA N of the data gradient (cin padded to 16)
+    PixelLayout lin, lout;
+    size_t wcount;  // taps*ldout*kin
+    float *w, *b, *vw, *vb;  // fp32 master weights [tap][ldout][kin], bias [ldout], velocities
+    float *gw, *gb;          // slices of the flat gradient buffer
+    bf16 *wf, *wb;           // bf16 operand copies (wb null for layer 0)
+    bf16* act;               // output activations [max_batch*lout.img_stride][ldout]
+    int off_fwd[kConvMaxTaps], off_bwd[kConvMaxTaps];
+    CUtensorMap tm_in, tm_wf, tm_g, tm_wb;      // forward A / B, dgrad A / B (full-size tensors)
+    CUtensorMap tm_wg_g, tm_wg_x;               // wgrad operands, exact batch rows (rebuilt when n changes)
+    int wgrad_splits;
+};
+
+}  // namespace ag
+
+using namespace ag;
+
+struct ag_net {
+    int board, in_planes, n_conv, head_kind, max_batch;
+    std::vector<ConvLayer> L;
+    PixelLayout lay_in, lay_mid;
+    bf16* x0 = nullptr;        // packed input rows [max_batch*lay_in.img_stride][kin0]
+    bf16* x0_grad = nullptr;   // G of layer 0 in the input layout (only when layer 0's layout differs)
+    bf16* gbuf[2] = {nullptr, nullptr};  // ping-pong pre-activation gradients in lay_mid
+    // head
+    float *hw = nullptr, *hb = nullptr, *hpos = nullptr;       // 1x1 conv w[ld], b[1], position bias[pts] (optional)
+    float *vhw = nullptr, *vhb = nullptr, *vhpos = nullptr;    // velocities
+    float *g_hw = nullptr, *g_hb = nullptr, *g_hpos = nullptr;  // gradient slices
+    int use_pos_bias = 0;
+    float *d1w = nullptr, *d1b = nullptr, *d2w = nullptr, *d2b = nullptr;  // value head dense layers
+    int hidden = 256;
+    float* head_partial = nullptr;  // [max_batch][625]
+    float* colsum_part = nullptr;   // [colsum_blocks][256]
+    float* wgrad_scratch = nullptr;
+    size_t wgrad_scratch_floats = 0;
+    float* grads = nullptr;  // flat: per conv layer gw then gb; then head w, b, pos
+    size_t grad_count = 0;
+    std::vector<long long> grad_offsets;  // start of each conv layer's slice, then head, then end
+    int wgrad_n = -1;
+    int colsum_blocks = 0;
+    long long iterations = 0;
+};
+
+namespace ag {
+
+template <class T>
+static int dev_alloc(T** p, size_t count, bool zero = true) {
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T) + 256);
+    if (e != cudaSuccess) { set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e)); return AG_ENOMEM; }
+    if (zero) { e = cudaMemset(*p, 0, count * sizeof(T) + 256); if (e != cudaSuccess) return cuda_fail(e, "cudaMemset"); }
+    return AG_OK;
+}
+
+static void tap_offsets(int width, const PixelLayout& L, int* fwd, int* bwd) {
+    int pad = width / 2, t = 0;
+    for (int kx = 0; kx < width; kx++)
+        for (int ky = 0; ky < width; ky++, t++) {
+            fwd[t] = (kx - pad) * L.row_stride + (ky - pad);  // cross-correlation tap (kx, ky)
+            bwd[t] = -fwd[t];
+        }
+}
+
+static int grid_for(size_t work, int threads) {
+    size_t g = (work + threads - 1) / threads;
+    size_t cap = (size_t)sm_count() * 16;
+    return (int)(g < cap ? (g ? g : 1) : cap);
+}
+
+static int net_build_wgrad_maps(ag_net* net, int n) {
+    if (net->wgrad_n == n) return AG_OK;
+    for (int l = 0; l < net->n_conv; l++) {
+        ConvLayer& c = net->L[l];
+        const bf16* xin = l == 0 ? net->x0 : net->L[l - 1].act;
+        const bf16* g = (l == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[l & 1];
+        uint64_t rows = (uint64_t)n * c.lin.img_stride;
+        int rc = make_tmap_2d(&c.tm_wg_g, g, rows, c.ldout, 64);
+        if (rc) return rc;
+        rc = make_tmap_2d(&c.tm_wg_x, xin, rows, c.kin, 64);
+        if (rc) return rc;
+        c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, (int)rows);
+        size_t need = (size_t)c.wgrad_splits * c.wcount;
+        if (need > net->wgrad_scratch_floats) { set_error("wgrad scratch too small"); return AG_ESTATE; }
+    }
+    net->wgrad_n = n;
+    return AG_OK;
+}
+
+}  // namespace ag
+
+extern "C" {
+
+ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters, const int* h_widths, int head_kind, int max_batch) {
+    if (board < 2 || board > 19 || in_planes < 1 || in_planes > 256 || n_conv < 1 || n_conv > 64 || max_batch < 1 ||
+        (head_kind != 0 && head_kind != 1)) {
+        set_error("ag_net_create: bad argument");
+        return nullptr;
+    }
+    int midpad = 0;
+    for (int l = 0; l < n_conv; l++) {
+        if (h_widths[l] < 1 || h_widths[l] > 5 || h_widths[l] % 2 == 0) { set_error("ag_net_create: filter width %d must be odd and <= 5", h_widths[l]); return nullptr; }
+        if (h_filters[l] < 1 || h_filters[l] > 256) { set_error("ag_net_create: %d filters unsupported (1..256)", h_filters[l]); return nullptr; }
+        if (l > 0 && h_widths[l] / 2 > midpad) midpad = h_widths[l] / 2;
+        if (h_filters[l] != h_filters[0]) { set_error("ag_net_create: all conv layers must have the same filter count (policy.py:97-103 filters_per_layer)"); return nullptr; }
+    }
+    if (midpad == 0) midpad = 0;
+    ag_net* net = new ag_net();
+    net->board = board; net->in_planes = in_planes; net->n_conv = n_conv; net->head_kind = head_kind; net->max_batch = max_batch;
+    int pad0 = h_widths[0] / 2;
+    net->lay_in = PixelLayout{board, board + pad0, (board + pad0) * (board + pad0)};
+    net->lay_mid = PixelLayout{board, board + midpad, (board + midpad) * (board + midpad)};
+    if (pad0 == midpad) net->lay_in = net->lay_mid;
+    const bool same_layout = net->lay_in.row_stride == net->lay_mid.row_stride;
+    net->L.resize(n_conv);
+    int rc = AG_OK;
+    size_t gcount = 0, scratch = 0;
+    for (int l = 0; l < n_conv && !rc; l++) {
+        ConvLayer& c = net->L[l];
+        c.cin = l == 0 ? in_planes : h_filters[l - 1];
+        c.cout = h_filters[l];
+        c.width = h_widths[l]; c.taps = c.width * c.width; c.pad = c.width / 2;
+        c.kin = round_up(c.cin, 64); c.ldout = round_up(c.cout, 64);
+        c.nout = round_up(c.cout, 16); c.nin = round_up(c.cin, 16);
+        c.lin = l == 0 ? net->lay_in : net->lay_mid;
+        c.lout = net->lay_mid;
+        c.wcount = (size_t)c.taps * c.ldout * c.kin;
+        tap_offsets(c.width, c.lin, c.off_fwd, c.off_bwd);
+        net->grad_offsets.push_back((long long)gcount);
+        gcount += c.wcount + c.ldout;
+        size_t rows_in = (size_t)max_batch * c.lin.img_stride;
+        int splits = wgrad_plan_splits(c.taps, c.ldout, (int)rows_in);
+        if ((size_t)kWgradMaxSplits * c.wcount > scratch) scratch = (size_t)kWgradMaxSplits * c.wcount;
+        (void)splits;
+    }
+    net->grad_offsets.push_back((long long)gcount);  // head slice
+    const int ldh = net->L[n_conv - 1].ldout, pts = board * board;
+    gcount += 256 + 1 + 368;
+    net->grad_offsets.push_back((long long)gcount);
+    net->grad_count = gcount;
+    rc = dev_alloc(&net->grads, gcount);
+    net->wgrad_scratch_floats = scratch;
+    if (!rc) rc = dev_alloc(&net->wgrad_scratch, scratch, false);
+    if (!rc) rc = dev_alloc(&net->x0, (size_t)max_batch * net->lay_in.img_stride * net->L[0].kin);
+    if (!rc && !same_layout) rc = dev_alloc(&net->x0_grad, (size_t)max_batch * net->lay_in.img_stride * net->L[0].ldout);
+    size_t gmax = 0;
+    for (int l = 0; l < n_conv; l++) { size_t s = (size_t)max_batch * net->lay_mid.img_stride * net->L[l].ldout; if (s > gmax) gmax = s; }
+    for (int i = 0; i < 2 && !rc; i++) rc = dev_alloc(&net->gbuf[i], gmax);
+    for (int l = 0; l < n_conv && !rc; l++) {
+        ConvLayer& c = net->L[l];
+        rc = dev_alloc(&c.w, c.wcount);
+        if (!rc) rc = dev_alloc(&c.b, (size_t)c.ldout);
+        if (!rc) rc = dev_alloc(&c.vw, c.wcount);
+        if (!rc) rc = dev_alloc(&c.vb, (size_t)c.ldout);
+        if (!rc) rc = dev_alloc(&c.wf, c.wcount);
+        c.wb = nullptr;
+        if (!rc && l > 0) rc = dev_alloc(&c.wb, c.wcount);
+        if (!rc) rc = dev_alloc(&c.act, (size_t)max_batch * c.lout.img_stride * c.ldout);
+        c.gw = net->grads + net->grad_offsets[l];
+        c.gb = c.gw + c.wcount;
+        if (rc) break;
+        const bf16* xin = l == 0 ? net->x0 : net->L[l - 1].act;
+        rc = make_tmap_2d(&c.tm_in, xin, (uint64_t)max_batch * c.lin.img_stride, c.kin, 128);
+        if (!rc) rc = make_tmap_2d(&c.tm_wf, c.wf, (uint64_t)c.taps * c.ldout, c.kin, c.nout);
+        if (!rc && l > 0) {
+            // data gradient: A = G of this layer (lay_mid rows, ldout wide), B = wb [tap][ci][co]
+            rc = make_tmap_2d(&c.tm_g, net->gbuf[l & 1], (uint64_t)max_batch * c.lout.img_stride, c.ldout, 128);
+            if (!rc) rc = make_tmap_2d(&c.tm_wb, c.wb, (uint64_t)c.taps * c.kin, c.ldout, c.nin);
+        }
+    }
+    if (!rc) rc = dev_alloc(&net->hw, 256);
+    if (!rc) rc = dev_alloc(&net->hb, 4);
+    if (!rc) rc = dev_alloc(&net->hpos, 368);
+    if (!rc) rc = dev_alloc(&net->vhw, 256);
+    if (!rc) rc = dev_alloc(&net->vhb, 4);
+    if (!rc) rc = dev_alloc(&net->vhpos, 368);
+    if (!rc) rc = dev_alloc(&net->head_partial, (size_t)max_batch * 625);
+    net->colsum_blocks = sm_count() * 2;
+    if (!rc) rc = dev_alloc(&net->colsum_part, (size_t)net->colsum_blocks * 256);
+    if (!rc && head_kind == 1) {
+        rc = dev_alloc(&net->d1w, (size_t)net->hidden * pts);
+        if (!rc) rc = dev_alloc(&net->d1b, (size_t)net->hidden);
+        if (!rc) rc = dev_alloc(&net->d2w, (size_t)net->hidden);
+        if (!rc) rc = dev_alloc(&net->d2b, 4);
+    }
+    if (!rc) {
+        net->g_hw = net->grads + net->grad_offsets[n_conv];
+        net->g_hb = net->g_hw + 256;
+        net->g_hpos = net->g_hb + 1;
+        (void)ldh;
+        if (cudaDeviceSynchronize() != cudaSuccess) rc = AG_ECUDA;
+    }
+    if (rc) { ag_net_destroy(net); return nullptr; }
+    return net;
+}
+
+void ag_net_destroy(ag_net* net) {
+    if (!net) return;
+    for (auto& c : net->L) { cudaFree(c.w); cudaFree(c.b); cudaFree(c.vw); cudaFree(c.vb); cudaFree(c.wf); cudaFree(c.wb); cudaFree(c.act); }
+    float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
+                  net->head_partial, net->colsum_part, net->wgrad_scratch, net->grads};
+    for (float* p : f) cudaFree(p);
+    cudaFree(net->x0); cudaFree(net->x0_grad); cudaFree(net->gbuf[0]); cudaFree(net->gbuf[1]);
+    delete net;
+}
+
+// layer geometry for the Python side: field 0 cin, 1 cout, 2 width, 3 kin, 4 ldout
+int ag_net_layer_info(const ag_net* net, int layer, int field) {
+    if (layer < 0 || layer >= net->n_conv) return -1;
+    const ConvLayer& c = net->L[layer];
+    switch (field) { case 0: return c.cin; case 1: return c.cout; case 2: return c.width; case 3: return c.kin; case 4: return c.ldout; }
+    return -1;
+}
+
+// Conv weights as cross-correlation filters in Keras 'th' order OIHW: w[co][ci][kx][ky], b[co]
+// (policy.py:119-150 layers).  A Theano-trained file stores true-convolution filters: flip both
+// spatial axes before calling (the Python layer's flip_kernels switch).  Synchronous.
+int ag_net_set_conv(ag_net* net, int layer, const float* h_w, const float* h_b) {
+    if (layer < 0 || layer >= net->n_conv) { set_error("bad layer %d", layer); return AG_EINVAL; }
+    ConvLayer& c = net->L[layer];
+    std::vector<float> w(c.wcount, 0.f), b(c.ldout, 0.f);
+    std::vector<bf16> wf(c.wcount), wb(c.wcount);
+    for (int co = 0; co < c.cout; co++) {
+        b[co] = h_b ? h_b[co] : 0.f;
+        for (int ci = 0; ci < c.cin; ci++)
+            for (int t = 0; t < c.taps; t++)
+                w[((size_t)t * c.ldout + co) * c.kin + ci] = h_w[((size_t)co * c.cin + ci) * c.taps + t];
+    }
+    for (size_t i = 0; i < c.wcount; i++) {
+        wf[i] = __float2bfloat16(w[i]);
+        int ci = (int)(i % c.kin); size_t r = i / c.kin; int co = (int)(r % c.ldout); int t = (int)(r / c.ldout);
+        wb[((size_t)t * c.kin + ci) * c.ldout + co] = wf[i];
+    }
+    AG_CUDA(cudaMemcpy(c.w, w.data(), c.wcount * 4, cudaMemcpyHostToDevice));
+    AG_CUDA(cudaMemcpy(c.b, b.data(), (size_t)c.ldout * 4, cudaMemcpyHostToDevice));
+    AG_CUDA(cudaMemcpy(c.wf, wf.data(), c.wcount * 2, cudaMemcpyHostToDevice));
+    if (c.wb) AG_CUDA(cudaMemcpy(c.wb, wb.data(), c.wcount * 2, cudaMemcpyHostToDevice));
+    AG_CUDA(cudaMemset(c.vw, 0, c.wcount * 4));
+    AG_CUDA(cudaMemset(c.vb, 0, (size_t)c.ldout * 4));
+    return AG_OK;
+}
+int ag_net_get_conv(ag_net* net, int layer, float* h_w, float* h_b) {
+    if (layer < 0 || layer >= net->n_conv) { set_error("bad layer %d", layer); return AG_EINVAL; }
+    ConvLayer& c = net->L[layer];
+    std::vector<float> w(c.wcount), b(c.ldout);
+    AG_CUDA(cudaMemcpy(w.data(), c.w, c.wcount * 4, cudaMemcpyDeviceToHost));
+    AG_CUDA(cudaMemcpy(b.data(), c.b, (size_t)c.ldout * 4, cudaMemcpyDeviceToHost));
+    for (int co = 0; co < c.cout; co++) {
+        if (h_b) h_b[co] = b[co];
+        for (int ci = 0; ci < c.cin; ci++)
+            for (int t = 0; t < c.taps; t++)
+                h_w[((size_t)co * c.cin + ci) * c.taps + t] = w[((size_t)t * c.ldout + co) * c.kin + ci];
+    }
+    return AG_OK;
+}
+// head parameters.  which: 0 = 1x1 conv (w[C_last], b[1]); 1 = position bias (w[board*board], enables it);
+// 2 = value Dense(256) (w[256][board*board], b[256]); 3 = value Dense(1) (w[256], b[1]).  Synchronous.
+int ag_net_set_head(ag_net* net, int which, const float* h_w, const float* h_b) {
+    const int pts = net->board * net->board, cl = net->L[net->n_conv - 1].cout;
+    switch (which) {
+        case 0:
+            AG_CUDA(cudaMemset(net->hw, 0, 256 * 4));
+            AG_CUDA(cudaMemcpy(net->hw, h_w, (size_t)cl * 4, cudaMemcpyHostToDevice));
+            if (h_b) AG_CUDA(cudaMemcpy(net->hb, h_b, 4, cudaMemcpyHostToDevice));
+            AG_CUDA(cudaMemset(net->vhw, 0, 256 * 4)); AG_CUDA(cudaMemset(net->vhb, 0, 4));
+            return AG_OK;
+        case 1:
+            AG_CUDA(cudaMemcpy(net->hpos, h_w, (size_t)pts * 4, cudaMemcpyHostToDevice));
+            AG_CUDA(cudaMemset(net->vhpos, 0, 368 * 4));
+            net->use_pos_bias = 1;
+            return AG_OK;
+        case 2:
+            if (net->head_kind != 1) break;
+            AG_CUDA(cudaMemcpy(net->d1w, h_w, (size_t)net->hidden * pts * 4, cudaMemcpyHostToDevice));
+            if (h_b) AG_CUDA(cudaMemcpy(net->d1b, h_b, (size_t)net->hidden * 4, cudaMemcpyHostToDevice));
+            return AG_OK;
+        case 3:
+            if (net->head_kind != 1) break;
+            AG_CUDA(cudaMemcpy(net->d2w, h_w, (size_t)net->hidden * 4, cudaMemcpyHostToDevice));
+            if (h_b) AG_CUDA(cudaMemcpy(net->d2b, h_b, 4, cudaMemcpyHostToDevice));
+            return AG_OK;
+    }
+    set_error("ag_net_set_head: bad selector %d for this head", which);
+    return AG_EINVAL;
+}
+int ag_net_get_head(ag_net* net, int which, float* h_w, float* h_b) {
+    const int pts = net->board * net->board, cl = net->L[net->n_conv - 1].cout;
+    switch (which) {
+        case 0:
+            AG_CUDA(cudaMemcpy(h_w, net->hw, (size_t)cl * 4, cudaMemcpyDeviceToHost));
+            if (h_b) AG_CUDA(cudaMemcpy(h_b, net->hb, 4, cudaMemcpyDeviceToHost));
+            return AG_OK;
+        case 1:
+            AG_CUDA(cudaMemcpy(h_w, net->hpos, (size_t)pts * 4, cudaMemcpyDeviceToHost));
+            return AG_OK;
+        case 2:
+            if (net->head_kind != 1) break;
+            AG_CUDA(cudaMemcpy(h_w, net->d1w, (size_t)net->hidden * pts * 4, cudaMemcpyDeviceToHost));
+            if (h_b) AG_CUDA(cudaMemcpy(h_b, net->d1b, (size_t)net->hidden * 4, cudaMemcpyDeviceToHost));
+            return AG_OK;
+        case 3:
+            if (net->head_kind != 1) break;
+            AG_CUDA(cudaMemcpy(h_w, net->d2w, (size_t)net->hidden * 4, cudaMemcpyDeviceToHost));
+            if (h_b) AG_CUDA(cudaMemcpy(h_b, net->d2b, 4, cudaMemcpyDeviceToHost));
+            return AG_OK;
+    }
+    set_error("ag_net_get_head: bad selector %d for this head", which);
+    return AG_EINVAL;
+}
+
+static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStream_t st) {
+    const int S = net->board;
+    ConvLayer& c0 = net->L[0];
+    size_t work = (size_t)n * S * S * (c0.kin / 8);
+    pack_input_kernel<<<grid_for(work, 256), 256, 0, st>>>(d_planes, n, net->in_planes, S, net->lay_in, c0.kin, net->x0);
+    AG_LAUNCH_CHECK("pack_input_kernel");
+    for (int l = 0; l < net->n_conv; l++) {
+        ConvLayer& c = net->L[l];
+        ConvArgs a;
+        memset(&a, 0, sizeof(a));
+        a.m_total = n * c.lin.img_stride;
+        a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
+        memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
+        a.in = c.lin; a.dst = c.lout;
+        a.bias = c.b; a.gate = nullptr; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        int rc = conv_gemm_launch(c.tm_in, c.tm_wf, a, st);
+        if (rc) return rc;
+    }
+    return AG_OK;
+}
+
+// Forward pass (policy.py:26-42 `forward`).  d_planes uint8 [n][in_planes][board][board].
+// policy head: d_out fp32 [n][board*board] probabilities; value head: d_out fp32 [n] in [-1, 1].
+int ag_net_forward(ag_net* net, const uint8_t* d_planes, int n, float* d_out, void* stream) {
+    if (n < 0 || n > net->max_batch) { set_error("ag_net_forward: batch %d exceeds max_batch %d", n, net->max_batch); return AG_EINVAL; }
+    if (n == 0) return AG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = net_conv_stack(net, d_planes, n, st);
+    if (rc) return rc;
+    ConvLayer& cl = net->L[net->n_conv - 1];
+    if (net->head_kind == 0) {
+        policy_head_kernel<<<n, kHeadThreads, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
+                                                      d_out, nullptr, 0.f, nullptr, nullptr, nullptr, nullptr);
+        AG_LAUNCH_CHECK("policy_head_kernel");
+    } else {
+        value_head_kernel<<<n, 256, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->d1w, net->d1b, net->d2w, net->d2b,
+                                             net->hidden, d_out);
+        AG_LAUNCH_CHECK("value_head_kernel");
+    }
+    return AG_OK;
+}
+
+// Forward + fused softmax / categorical cross-entropy / accuracy head and its backward
+// (spt.py:200 compile(loss='categorical_crossentropy', metrics=['accuracy'])).  d_labels int32 [n] =
+// flat move index x*board+y.  d_loss_acc fp32[2] is ACCUMULATED into: sum of losses, number correct.
+// Leaves the gradient w.r.t. the last conv layer's pre-activation in place for ag_net_backward_layer.
+// d_probs may be NULL.  Gradients are means over this call's n.
+int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float* d_probs, float* d_loss_acc, void* stream) {
+    if (net->head_kind != 0) { set_error("ag_net_forward_loss: policy head only"); return AG_ESTATE; }
+    if (n < 1 || n > net->max_batch) { set_error("ag_net_forward_loss: batch %d not in 1..%d", n, net->max_batch); return AG_EINVAL; }
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = net_conv_stack(net, d_planes, n, st);
+    if (rc) return rc;
+    rc = net_build_wgrad_maps(net, n);
+    if (rc) return rc;
+    const int last = net->n_conv - 1;
+    ConvLayer& cl = net->L[last];
+    bf16* G = (last == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[last & 1];
+    if (last == 0 && net->x0_grad) { set_error("single-layer nets with a wide first filter are not trainable"); return AG_ESTATE; }
+    policy_head_kernel<<<n, kHeadThreads, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
+                                                  d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr);
+    AG_LAUNCH_CHECK("policy_head_kernel");
+    head_reduce_kernel<<<(625 + 127) / 128, 128, 0, st>>>(net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
+                                                        net->use_pos_bias ? net->g_hpos : nullptr);
+    AG_LAUNCH_CHECK("head_reduce_kernel");
+    return AG_OK;
+}
+
+// Backward of conv layer `layer` (call for layer = n_conv-1 down to 0 after ag_net_forward_loss):
+// weight + bias gradients into the flat gradient buffer, then (layer > 0) the data gradient,
+// gated by the ReLU of the layer below, as the next layer's pre-activation gradient.
+int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
+    if (layer < 0 || layer >= net->n_conv || n < 1 || n > net->max_batch || net->wgrad_n != n) {
+        set_error("ag_net_backward_layer: bad layer/batch or no forward_loss before it");
+        return AG_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    ConvLayer& c = net->L[layer];
+    const bf16* G = (layer == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[layer & 1];
+    const size_t rows = (size_t)n * c.lin.img_stride;
+    // bias gradient
+    colsum_stage1_kernel<<<net->colsum_blocks, 256, 0, st>>>(G, rows, c.ldout, net->colsum_part);
+    AG_LAUNCH_CHECK("colsum_stage1_kernel");
+    colsum_stage2_kernel<<<(c.ldout + 127) / 128, 128, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
+    AG_LAUNCH_CHECK("colsum_stage2_kernel");
+    // weight gradient
+    WgradArgs w;
+    memset(&w, 0, sizeof(w));
+    w.m_total = (int)rows; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
+    w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
+    int rc = wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, st);
+    if (rc) return rc;
+    if (layer == 0) return AG_OK;
+    // data gradient into the layer below
+    ConvLayer& below = net->L[layer - 1];
+    ConvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.m_total = n * c.lout.img_stride;
+    a.n = c.nin; a.taps = c.taps; a.kchunks = c.ldout / 64;
+    memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
+    a.in = c.lout;
+    a.bias = nullptr; a.relu = 0;
+    a.gate = below.act; a.gate_ld = below.ldout; a.gate_layout = below.lout;
+    a.out_ld = below.ldout; a.b_tap_rows = c.kin;
+    if (layer - 1 == 0 && net->x0_grad) {
+        // the first layer's G lives in the INPUT layout so its weight gradient can pair it with x0; the gate
+        // (layer-0 activations) is still read in the mid layout
+        a.dst = net->lay_in; a.out = net->x0_grad;
+    } else {
+        a.dst = c.lout; a.out = net->gbuf[(layer - 1) & 1];
+    }
+    return conv_gemm_launch(c.tm_g, c.tm_wb, a, st);
+}
+
+// Flat fp32 gradient buffer (device): conv layers in order (weights [tap][ldout][kin] then bias [ldout]),
+// then the head (w[256], b[1], pos[368]).  h_offsets receives n_conv+2 element offsets (layer starts,
+// head start, end).  This is what data-parallel training all-reduces.
+int ag_net_grads(ag_net* net, float** d_grads, long long* count, long long* h_offsets) {
+    *d_grads = net->grads;
+    *count = (long long)net->grad_count;
+    if (h_offsets) for (size_t i = 0; i < net->grad_offsets.size(); i++) h_offsets[i] = net->grad_offsets[i];
+    return AG_OK;
+}
+
+// Fused SGD(+momentum) update over every parameter (spt.py:199 SGD(lr, decay); the host applies Keras'
+// lr/(1+decay*iterations) schedule and passes the step's lr).  grad_scale multiplies the gradients
+// first (1/world_size after a sum all-reduce).  Also refreshes the bf16 operand copies.
+int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int l = 0; l < net->n_conv; l++) {
+        ConvLayer& c = net->L[l];
+        sgd_conv_kernel<<<grid_for(c.wcount + c.ldout, 256), 256, 0, st>>>(c.w, c.vw, c.gw, c.wcount, c.taps, c.ldout, c.kin, lr, momentum,
+                                                                         grad_scale, c.wf, c.wb, c.b, c.vb, c.gb, c.ldout);
+        AG_LAUNCH_CHECK("sgd_conv_kernel");
+    }
+    sgd_flat_kernel<<<1, 256, 0, st>>>(net->hw, net->vhw, net->g_hw, 256, lr, momentum, grad_scale);
+    AG_LAUNCH_CHECK("sgd_flat_kernel");
+    sgd_flat_kernel<<<1, 32, 0, st>>>(net->hb, net->vhb, net->g_hb, 1, lr, momentum, grad_scale);
+    AG_LAUNCH_CHECK("sgd_flat_kernel");
+    if (net->use_pos_bias) {
+        sgd_flat_kernel<<<1, 256, 0, st>>>(net->hpos, net->vhpos, net->g_hpos, (size_t)net->board * net->board, lr, momentum, grad_scale);
+        AG_LAUNCH_CHECK("sgd_flat_kernel");
+    }
+    net->iterations++;
+    return AG_OK;
+}
+
+// One single-GPU SL training step: forward, loss, full backward, SGD update.
+int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float lr, float momentum,
+                      float* d_loss_acc, void* stream) {
+    int rc = ag_net_forward_loss(net, d_planes, d_labels, n, nullptr, d_loss_acc, stream);
+    for (int l = net->n_conv - 1; l >= 0 && !rc; l--) rc = ag_net_backward_layer(net, l, n, stream);
+    if (!rc) rc = ag_net_sgd(net, lr, momentum, 1.f, stream);
+    return rc;
+}
+
+// Test/debug readback (synchronous): output activations of conv layer `layer` (kind 0) or the
+// pre-activation gradient currently held for it (kind 1) as fp32 [n][cout][board][board] on the host.
+int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out) {
+    if (layer < 0 || layer >= net->n_conv || n < 1 || n > net->max_batch) { set_error("ag_net_debug_read: bad argument"); return AG_EINVAL; }
+    ConvLayer& c = net->L[layer];
+    const bf16* src; PixelLayout lay;
+    if (kind == 0) { src = c.act; lay = c.lout; }
+    else if (layer == 0 && net->x0_grad) { src = net->x0_grad; lay = net->lay_in; }
+    else { src = net->gbuf[layer & 1]; lay = c.lout; }
+    size_t count = (size_t)n * c.cout * net->board * net->board;
+    float* d = nullptr;
+    AG_CUDA(cudaMalloc(&d, count * 4));
+    unpack_rows_kernel<<<grid_for(count, 256), 256>>>(src, n, c.cout, net->board, lay, c.ldout, d);
+    count_launch();
+    cudaError_t e = cudaMemcpy(h_out, d, count * 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return cuda_fail(e, "ag_net_debug_read");
+    return AG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,197 @@
+// Weight gradient of a KxK 'same' convolution as a split-K tcgen05 GEMM over the pixel dimension
+// (the backward of Keras' Convolution2D inside fit_generator, supervised_policy_trainer.py:207-213):
+//
+//     dW[tap][co][ci] = sum_m G[m - shift(tap)][co] * X[m][ci]
+//
+// G = gradient w.r.t. the layer's pre-activation output, X = the layer's input, both padded-pixel-
+// row matrices (conv.cuh) whose zero pad slots make the halo terms vanish.  The reduction index m
+// is the ROW index of both matrices, so both operands are MN-major: TMA brings [64 pixel rows][64
+// channels] boxes (128-byte swizzle) that the UMMA reads transposed.  A CTA owns 128 rows of the
+// flattened (tap, co) axis = two 64-channel chunks, each loaded with its own tap shift, and a
+// contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tap*co][ci] and
+// wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
+#include "common.cuh"
+#include "conv.cuh"
+#include "tcgen.cuh"
+#include "wgrad.cuh"
+
+namespace ag {
+
+namespace {
+
+constexpr int kStages = 4;
+constexpr int kChunkBytes = 64 * 128;  // [64 pixel rows][64 bf16]
+constexpr int kThreads = 192;
+constexpr int kTmemCols = 256;
+
+struct __align__(8) WgradBarriers {
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t acc_full;
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x, const WgradArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    const int xchunks = p.kin / 64;
+    const int stage_bytes = (2 + xchunks) * kChunkBytes;
+    WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
+    const int kb_total = (p.m_total + 63) / 64;
+    const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
+    const int cochunks = p.ldout / 64;
+    const int nchunks = p.taps * cochunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
+        tc::mbar_init(&bars->acc_full, 1);
+        tc::fence_mbar_init();
+        tc::tma_prefetch_desc(&tmap_g);
+        tc::tma_prefetch_desc(&tmap_x);
+    }
+    if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // the two (tap, co-chunk) halves of this CTA's 128 dW rows
+            int shift[2], col[2];
+            bool live[2];
+            for (int h = 0; h < 2; h++) {
+                int c = tile * 2 + h;
+                live[h] = c < nchunks;
+                int t = live[h] ? c / cochunks : 0;
+                shift[h] = p.off[t];
+                col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
+            }
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = kb0; kb < kb1; kb++) {
+                tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                uint8_t* s = base + stage * stage_bytes;
+                tc::mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
+                const int m0 = kb * 64;
+                for (int h = 0; h < 2; h++)  // a dead half reads far out of bounds -> zeros
+                    tc::tma_load_2d(s + h * kChunkBytes, &tmap_g, &bars->full[stage], col[h], live[h] ? m0 - shift[h] : 0x40000000);
+                for (int c = 0; c < xchunks; c++)
+                    tc::tma_load_2d(s + (2 + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, m0);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = tc::idesc_bf16(128, p.kin, 1, 1);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = kb0; kb < kb1; kb++) {
+                tc::mbar_wait(&bars->full[stage], phase);
+                tc::fence_after_sync();
+                const uint32_t s = tc::smem_u32(base + stage * stage_bytes);
+                const uint64_t adesc = tc::desc_mnmajor_sw128(s, kChunkBytes);
+                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + 2 * kChunkBytes, kChunkBytes);
+#pragma unroll
+                for (int k = 0; k < 4; k++)  // 16 pixel rows per UMMA: +2048 B
+                    tc::umma_bf16(tmem_base, adesc + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                tc::umma_commit(&bars->empty[stage]);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+            tc::umma_commit(&bars->acc_full);
+        }
+    } else {
+        const int q = warp & 3;
+        const int r = q * 32 + lane;           // row of the 128-row tile
+        const int chunk = tile * 2 + (r >> 6);
+        const bool valid = chunk < nchunks;
+        // scratch row = tap*ldout + co  (chunk*64 + r%64 by construction)
+        float* dst = p.scratch + ((size_t)split * p.taps * p.ldout + (size_t)chunk * 64 + (r & 63)) * p.kin;
+        if (kb1 > kb0) {
+            tc::mbar_wait(&bars->acc_full, 0);
+            tc::fence_after_sync();
+        }
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        for (int c0 = 0; c0 < p.kin; c0 += 32) {
+            uint32_t v[32];
+            if (kb1 > kb0) {
+                tc::tmem_ld32(taddr + c0, v);
+                tc::tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; j++) v[j] = 0;
+            }
+            if (valid) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            }
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// dW[i] = sum_s scratch[s][i], fixed order
+__global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits) {
+    const float4* s4 = reinterpret_cast<const float4*>(scratch);
+    float4* d4 = reinterpret_cast<float4*>(dw);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count4; i += (size_t)gridDim.x * blockDim.x) {
+        float4 a = s4[i];
+        for (int s = 1; s < splits; s++) {
+            float4 b = s4[(size_t)s * count4 + i];
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        d4[i] = a;
+    }
+}
+
+}  // namespace
+
+size_t wgrad_smem_bytes(int kin) { return 1024 + (size_t)kStages * (2 + kin / 64) * kChunkBytes + sizeof(WgradBarriers) + 64; }
+
+int wgrad_plan_splits(int taps, int ldout, int m_total) {
+    int chunks = taps * (ldout / 64);
+    int tiles = (chunks + 1) / 2;
+    int kb = (m_total + 63) / 64;
+    int s = (2 * sm_count() + tiles - 1) / tiles;  // about two waves of CTAs
+    if (s > kb) s = kb;
+    if (s < 1) s = 1;
+    if (s > kWgradMaxSplits) s = kWgradMaxSplits;
+    return s;
+}
+
+int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, cudaStream_t stream) {
+    if (args.kin % 64 != 0 || args.kin < 64 || args.kin > 256 || args.ldout % 64 != 0) {
+        set_error("wgrad: channel counts must be padded to 64 (kin=%d <= 256, ldout=%d)", args.kin, args.ldout);
+        return AG_EINVAL;
+    }
+    int chunks = args.taps * (args.ldout / 64);
+    args.tiles = (chunks + 1) / 2;
+    if (args.splits < 1) args.splits = 1;
+    static size_t configured = 0;
+    size_t smem = wgrad_smem_bytes(args.kin);
+    if (smem > 227 * 1024) { set_error("wgrad: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
+    if (smem > configured) {
+        AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    wgrad_kernel<<<args.tiles * args.splits, kThreads, smem, stream>>>(tmap_g, tmap_x, args);
+    AG_LAUNCH_CHECK("wgrad_kernel");
+    size_t count4 = (size_t)args.taps * args.ldout * args.kin / 4;
+    int grid = (int)((count4 + 255) / 256);
+    if (grid > sm_count() * 8) grid = sm_count() * 8;
+    wgrad_reduce_kernel<<<grid, 256, 0, stream>>>(args.scratch, dw, count4, args.splits);
+    AG_LAUNCH_CHECK("wgrad_reduce_kernel");
+    return AG_OK;
+}
+
+}  // namespace ag

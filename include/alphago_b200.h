@@ -92,6 +92,50 @@ void ag_age_from_history(int size, const int8_t* h_board, const int16_t* h_hist,
 int ag_playout_positions(uint64_t seed, int n, int size, int max_moves, int per_game,
                          int8_t* h_board, uint8_t* h_age, int8_t* h_player, int16_t* h_ko);
 
+/* ------------------------------------------------------------------ stage 2: conv-stack network
+ * One object per GPU holds the weights, activations and gradients of a CNNPolicy / CNNValue net
+ * (AlphaGo/models/policy.py:93-156, AlphaGo/models/value.py:12-28): n_conv KxK 'same' ReLU convs
+ * with a common filter count (widths odd, <= 5), then a 1x1 conv to one plane and
+ *   head_kind 0: Flatten + softmax over board*board moves (+ optional per-position bias)
+ *   head_kind 1: Flatten + Dense(256, linear) + Dense(1, tanh)
+ * bf16 tensor-core math with fp32 accumulation, fp32 master weights.  All device memory is
+ * allocated here (sized for max_batch); later calls allocate nothing.  NULL + ag_last_error() on failure. */
+typedef struct ag_net ag_net;
+ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters, const int* h_widths,
+                      int head_kind, int max_batch);                /* policy.py:93-156 create_network */
+void ag_net_destroy(ag_net* net);
+int ag_net_layer_info(const ag_net* net, int layer, int field);    /* 0 cin, 1 cout, 2 width, 3 padded cin, 4 padded cout */
+/* conv weights, cross-correlation filters in Keras 'th' order w[co][ci][kx][ky], b[co] (host, synchronous);
+ * Keras model.get_weights / set_weights (tests/test_policy.py:42-51, policy.py:165-167,188-190) */
+int ag_net_set_conv(ag_net* net, int layer, const float* h_w, const float* h_b);
+int ag_net_get_conv(ag_net* net, int layer, float* h_w, float* h_b);
+/* head parameters: which 0 = 1x1 conv (w[C], b[1]); 1 = position bias (w[board*board]; setting it enables it);
+ * 2 = value Dense(256) (w[256][board*board], b[256]); 3 = value Dense(1) (w[256], b[1]) */
+int ag_net_set_head(ag_net* net, int which, const float* h_w, const float* h_b);
+int ag_net_get_head(ag_net* net, int which, float* h_w, float* h_b);
+/* CNNPolicy.forward (policy.py:26-42): d_planes uint8 [n][in_planes][board][board] (the encoder's output /
+ * the HDF5 `states` layout) -> d_out fp32 [n][board*board] probabilities (head 0) or [n] values (head 1) */
+int ag_net_forward(ag_net* net, const uint8_t* d_planes, int n, float* d_out, void* stream);
+/* forward + categorical cross-entropy + accuracy + head backward (supervised_policy_trainer.py:200).
+ * d_labels int32 [n] = x*board+y.  d_loss_acc fp32[2] is ACCUMULATED: sum of losses, number correct.
+ * d_probs may be NULL.  Gradients are means over n. */
+int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float* d_probs,
+                        float* d_loss_acc, void* stream);
+/* backward of conv layer `layer`; call for n_conv-1 ... 0 after ag_net_forward_loss (fit_generator's backprop,
+ * supervised_policy_trainer.py:207-213).  The layer's slice of the gradient buffer is final when it returns. */
+int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream);
+/* the flat fp32 gradient buffer (device) data-parallel training all-reduces; h_offsets gets n_conv+2 offsets */
+int ag_net_grads(ag_net* net, float** d_grads, long long* count, long long* h_offsets);
+/* fused SGD(+momentum) over all parameters; gradients are multiplied by grad_scale first
+ * (keras.optimizers.SGD as used at supervised_policy_trainer.py:199; lr already decayed by the caller) */
+int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* stream);
+/* single-GPU step: forward_loss + every backward_layer + sgd */
+int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float lr, float momentum,
+                      float* d_loss_acc, void* stream);
+/* test/debug readback (synchronous, allocates): kind 0 = activations of conv layer, 1 = its pre-activation
+ * gradient, as fp32 [n][cout][board][board] on the host */
+int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out);
+
 #ifdef __cplusplus
 }
 #endif

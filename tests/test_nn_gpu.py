@@ -1,0 +1,230 @@
+"""GPU parity tests of the conv stack (tcgen05 implicit-GEMM forward, data/weight gradients, fused
+softmax-CE head, SGD) through the C ABI (ag_net_*), against the CPU oracle oracle/nn_oracle.py.
+
+Tolerances (floating point, bf16 inputs with fp32 accumulation, stated per check):
+  * vs the oracle with bf16 rounding emulated at the same points: only fp32 summation order and
+    one-ulp bf16 re-rounding of activations differ -> activations within 2 bf16 ulps of the layer's
+    largest value, probabilities within 2e-3 relative
+  * vs the plain fp32 oracle: max-abs logit-probability error < 5e-2 relative and >= 99 % top-1 move
+    agreement on a shared U(-0.05, 0.05) init (BASELINE north_star tolerance)
+  * gradients: relative Frobenius error < 3e-2 per tensor, cosine similarity > 0.999
+"""
+import numpy as np
+import pytest
+
+from alphago_b200 import nn
+from oracle import nn_oracle as no
+
+pytestmark = pytest.mark.gpu
+
+
+def make_net(board, planes, filters, widths, params, max_batch, head=nn.POLICY_HEAD):
+    net = nn.ConvNet(board, planes, filters, widths, head=head, max_batch=max_batch)
+    for l, (w, b) in enumerate(params["convs"]):
+        net.set_conv(l, w, b)
+    net.set_head(0, params["head_w"], params["head_b"])
+    if params.get("pos_bias") is not None:
+        net.set_head(1, params["pos_bias"])
+    if head == nn.VALUE_HEAD:
+        net.set_head(2, params["d1w"], params["d1b"])
+        net.set_head(3, params["d2w"], params["d2b"])
+    return net
+
+
+def rand_planes(n, c, s, seed):
+    rng = np.random.RandomState(seed)
+    return (rng.rand(n, c, s, s) < 0.3).astype(np.uint8)
+
+
+def rel_err(a, b):
+    return float(np.linalg.norm(a.astype(np.float64) - b) / (np.linalg.norm(b) + 1e-30))
+
+
+def cosine(a, b):
+    a = a.astype(np.float64).ravel(); b = b.astype(np.float64).ravel()
+    return float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-30))
+
+
+def grads_from_flat(net, flat):
+    """flat device gradient buffer -> [dw OIHW, db] per conv layer + head (dw, db, dpos)"""
+    out = []
+    for l in range(net.n_conv):
+        co, ci, k, _ = net.conv_shape(l)
+        kin = (ci + 63) // 64 * 64; ld = (co + 63) // 64 * 64
+        o = net.grad_offsets[l]
+        w = flat[o:o + k * k * ld * kin].reshape(k * k, ld, kin)[:, :co, :ci]
+        out.append(np.ascontiguousarray(w.transpose(1, 2, 0)).reshape(co, ci, k, k))
+        out.append(flat[o + k * k * ld * kin:o + k * k * ld * kin + co].copy())
+    o = net.grad_offsets[net.n_conv]
+    out.append(flat[o:o + net.filters[-1]].copy())
+    out.append(flat[o + 256:o + 257].copy())
+    out.append(flat[o + 257:o + 257 + net.board * net.board].copy())
+    return out
+
+
+CONFIGS = [
+    # board, planes, filters, widths, batch
+    (19, 48, [192, 192, 192], [5, 3, 3], 5),
+    (19, 12, [16] * 5, [5, 3, 3, 3, 3], 16),     # tests/test_data/minimodel.json
+    (13, 48, [64, 64], [5, 3], 3),               # tests/test_policy.py:27-30 board=13
+    (19, 48, [128, 128, 128], [3, 3, 3], 2),     # first layer 3x3: one layout throughout
+    (7, 4, [32, 32], [3, 5], 9),                 # filter_width_K override on a later layer (policy.py:134-135)
+]
+
+
+@pytest.mark.parametrize("board,planes,filters,widths,batch", CONFIGS)
+def test_forward_matches_oracle(board, planes, filters, widths, batch):
+    import torch
+    params = no.make_params(planes, filters, widths, seed=3, bias_scale=0.05)
+    x = rand_planes(batch, planes, board, 5)
+    net = make_net(board, planes, filters, widths, params, max_batch=max(batch, 8))
+    probs = net.forward(torch.from_numpy(x).cuda())
+    torch.cuda.synchronize()
+    probs = probs.cpu().numpy()
+    em = no.forward(params, x, emulate_bf16=True)
+    for l in range(len(filters)):
+        got = net.debug_read(l, 0, batch)
+        want = em["acts"][l].numpy()
+        tol = 2 * 2.0 ** -8 * max(1.0, float(np.abs(want).max()))
+        assert np.abs(got - want).max() <= tol, "layer %d: max err %g (tol %g)" % (l, np.abs(got - want).max(), tol)
+    assert probs.shape == (batch, board * board)
+    assert np.allclose(probs.sum(1), 1.0, atol=1e-5)
+    assert np.abs(probs - em["probs"].numpy()).max() <= 2e-3 * em["probs"].numpy().max()
+    fp = no.forward(params, x, emulate_bf16=False)["probs"].numpy()
+    assert np.abs(probs - fp).max() <= 5e-2 * fp.max()
+    net.close()
+
+
+def test_top1_agreement_flagship_shapes():
+    """13 convs x 192 filters x 48 planes (BASELINE configs[2]) on a shared random init: >= 99 % top-1
+    agreement with the fp32 oracle, and the max-abs probability error is reported."""
+    import torch
+    filters, widths = [192] * 12, [5] + [3] * 11
+    params = no.make_params(48, filters, widths, seed=1)
+    # boost the last layers so the move distribution is not flat and top-1 is meaningful
+    params["head_w"] = (params["head_w"] * 40).astype(np.float32)
+    x = rand_planes(64, 48, 19, 8)
+    net = make_net(19, 48, filters, widths, params, max_batch=64)
+    probs = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    fp = no.forward(params, x)["probs"].numpy()
+    agree = float((probs.argmax(1) == fp.argmax(1)).mean())
+    err = float(np.abs(probs - fp).max())
+    print("top-1 agreement %.4f, max-abs prob err %.3g (max prob %.3g)" % (agree, err, fp.max()))
+    assert agree >= 0.99
+    assert err <= 5e-2 * fp.max()
+    net.close()
+
+
+@pytest.mark.parametrize("board,planes,filters,widths,batch", CONFIGS[:3] + CONFIGS[4:])
+def test_backward_matches_oracle(board, planes, filters, widths, batch):
+    import torch
+    params = no.make_params(planes, filters, widths, seed=11, bias_scale=0.05)
+    params["head_w"] = (params["head_w"] * 20).astype(np.float32)
+    x = rand_planes(batch, planes, board, 6)
+    labels = np.random.RandomState(2).randint(0, board * board, batch).astype(np.int32)
+    net = make_net(board, planes, filters, widths, params, max_batch=batch + 3)
+    acc = torch.zeros(2, device="cuda")
+    probs = torch.empty(batch, board * board, device="cuda")
+    net.forward_loss(torch.from_numpy(x).cuda(), torch.from_numpy(labels).cuda(), acc, probs)
+    for l in range(len(filters) - 1, -1, -1):
+        net.backward_layer(l, batch)
+    torch.cuda.synchronize()
+    loss, accuracy, grads, out = no.loss_and_grads(params, x, labels, emulate_bf16=True)
+    got_loss, got_correct = acc.cpu().numpy()
+    assert abs(got_loss / batch - loss) <= 2e-3 * max(1.0, abs(loss))
+    assert got_correct == round(accuracy * batch)
+    got = grads_from_flat(net, net.grad_tensor().cpu().numpy())
+    names = []
+    for l in range(len(filters)):
+        names += ["conv%d.w" % l, "conv%d.b" % l]
+    names += ["head.w", "head.b"]
+    for name, g, want in zip(names, got, grads):
+        assert g.shape == want.shape, name
+        assert rel_err(g, want) < 3e-2 and cosine(g, want) > 0.999, "%s rel %g cos %g" % (name, rel_err(g, want), cosine(g, want))
+    net.close()
+
+
+def test_train_step_sgd_momentum_and_loss_decreases():
+    import torch
+    board, planes, filters, widths, batch = 19, 48, [64, 64, 64], [5, 3, 3], 32
+    params = no.make_params(planes, filters, widths, seed=4)
+    params["head_w"] = (params["head_w"] * 20).astype(np.float32)
+    x = rand_planes(batch, planes, board, 9)
+    labels = np.random.RandomState(3).randint(0, 361, batch).astype(np.int32)
+    net = make_net(board, planes, filters, widths, params, max_batch=batch)
+    dx, dl = torch.from_numpy(x).cuda(), torch.from_numpy(labels).cuda()
+    acc = torch.zeros(2, device="cuda")
+    lr, mom = 0.05, 0.9
+    # one step against the oracle's SGD (Keras 1.0: v = mom*v - lr*g; w += v)
+    net.train_step(dx, dl, lr, mom, acc)
+    torch.cuda.synchronize()
+    _, _, grads, _ = no.loss_and_grads(params, x, labels, emulate_bf16=True)
+    new, vel = no.sgd_update(params, grads, lr, mom)
+    for l in range(len(filters)):
+        w, b = net.get_conv(l)
+        dw = w - params["convs"][l][0]; want = new["convs"][l][0] - params["convs"][l][0]
+        assert rel_err(dw, want) < 3e-2, l
+        assert rel_err(b - params["convs"][l][1], new["convs"][l][1] - params["convs"][l][1]) < 3e-2
+    hw, hb = net.get_head(0)
+    assert rel_err(hw - params["head_w"], new["head_w"] - params["head_w"]) < 3e-2
+    # keep training on the same batch: the loss must fall
+    losses = [float(acc.cpu()[0]) / batch]
+    for _ in range(15):
+        acc.zero_()
+        net.train_step(dx, dl, lr, mom, acc)
+        losses.append(float(acc.cpu()[0]) / batch)
+    assert losses[-1] < 0.5 * losses[0], losses
+    net.close()
+
+
+def test_position_bias_and_value_head():
+    import torch
+    board, planes, filters, widths, batch = 19, 49, [64, 64], [5, 3], 6
+    params = no.make_params(planes, filters, widths, seed=5, bias_scale=0.05, value_head=True)
+    x = rand_planes(batch, planes, board, 10)
+    net = make_net(board, planes, filters, widths, params, max_batch=8, head=nn.VALUE_HEAD)
+    v = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    want = no.forward(params, x, emulate_bf16=True)["value"].numpy()
+    assert v.shape == (batch,) and np.all(np.abs(v) <= 1.0)
+    assert np.abs(v - want).max() < 2e-3
+    net.close()
+    params = no.make_params(48, filters, widths, seed=6)
+    params["pos_bias"] = np.random.RandomState(1).uniform(-1, 1, 361).astype(np.float32)
+    x = rand_planes(batch, 48, board, 11)
+    net = make_net(board, 48, filters, widths, params, max_batch=8)
+    p = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    want = no.forward(params, x, emulate_bf16=True)["probs"].numpy()
+    assert np.abs(p - want).max() <= 2e-3 * want.max()
+    # and its gradient
+    labels = np.arange(batch, dtype=np.int32) * 7
+    acc = torch.zeros(2, device="cuda")
+    net.forward_loss(torch.from_numpy(x).cuda(), torch.from_numpy(labels).cuda(), acc)
+    torch.cuda.synchronize()
+    _, _, grads, _ = no.loss_and_grads(params, x, labels, emulate_bf16=True)
+    got = grads_from_flat(net, net.grad_tensor().cpu().numpy())
+    assert rel_err(got[-1], grads[-1]) < 1e-2
+    net.close()
+
+
+def test_batch_sizes_and_stale_rows():
+    """a small batch after a large one must not see the large batch's leftovers (wgrad reads exactly n images)"""
+    import torch
+    board, planes, filters, widths = 19, 48, [64, 64], [5, 3]
+    params = no.make_params(planes, filters, widths, seed=7)
+    params["head_w"] = (params["head_w"] * 20).astype(np.float32)
+    net = make_net(board, planes, filters, widths, params, max_batch=40)
+    for batch in (40, 1, 7, 33):
+        x = rand_planes(batch, planes, board, 20 + batch)
+        labels = np.random.RandomState(batch).randint(0, 361, batch).astype(np.int32)
+        acc = torch.zeros(2, device="cuda")
+        net.forward_loss(torch.from_numpy(x).cuda(), torch.from_numpy(labels).cuda(), acc)
+        for l in (1, 0):
+            net.backward_layer(l, batch)
+        torch.cuda.synchronize()
+        _, _, grads, _ = no.loss_and_grads(params, x, labels, emulate_bf16=True)
+        got = grads_from_flat(net, net.grad_tensor().cpu().numpy())
+        for g, want in zip(got[:4], grads[:4]):
+            assert rel_err(g, want) < 3e-2, batch
+    with pytest.raises(Exception):
+        net.forward(torch.zeros((41, 48, 19, 19), dtype=torch.uint8, device="cuda"))
+    net.close()
