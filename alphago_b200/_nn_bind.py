@@ -19,4 +19,6 @@ def bind(L):
     L.ag_net_sgd.argtypes = [vp, C.c_float, C.c_float, C.c_float, vp]
     L.ag_net_train_step.argtypes = [vp, vp, vp, i, C.c_float, C.c_float, vp, vp]
     L.ag_net_debug_read.argtypes = [vp, i, i, i, vp]
+    L.ag_net_run_layer.argtypes = [vp, i, i, i, vp]
+    L.ag_augment.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp]
     return L

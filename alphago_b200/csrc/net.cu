@@ -789,6 +789,46 @@ int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_lab
     return rc;
 }
 
+// Measurement hook: re-runs ONE kernel of the step on the buffers the last forward_loss/backward left in
+// place: mode 0 = forward conv of `layer`, 1 = its data gradient, 2 = its weight gradient (+ reduce).
+int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
+    if (layer < 0 || layer >= net->n_conv || n < 1 || n > net->max_batch) { set_error("ag_net_run_layer: bad argument"); return AG_EINVAL; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ConvLayer& c = net->L[layer];
+    if (mode == 0) {
+        ConvArgs a;
+        memset(&a, 0, sizeof(a));
+        a.m_total = n * c.lin.img_stride;
+        a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
+        memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
+        a.in = c.lin; a.dst = c.lout;
+        a.bias = c.b; a.gate = nullptr; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        return conv_gemm_launch(c.tm_in, c.tm_wf, a, st);
+    }
+    if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
+    if (mode == 2) {
+        WgradArgs w;
+        memset(&w, 0, sizeof(w));
+        w.m_total = n * c.lin.img_stride; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
+        w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
+        return wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, st);
+    }
+    if (mode == 1 && layer > 0 && !(layer == 1 && net->x0_grad)) {
+        ConvLayer& below = net->L[layer - 1];
+        ConvArgs a;
+        memset(&a, 0, sizeof(a));
+        a.m_total = n * c.lout.img_stride;
+        a.n = c.nin; a.taps = c.taps; a.kchunks = c.ldout / 64;
+        memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
+        a.in = c.lout; a.dst = c.lout;
+        a.gate = below.act; a.gate_ld = below.ldout; a.gate_layout = below.lout;
+        a.out = net->gbuf[(layer - 1) & 1]; a.out_ld = below.ldout; a.b_tap_rows = c.kin;
+        return conv_gemm_launch(c.tm_g, c.tm_wb, a, st);
+    }
+    set_error("ag_net_run_layer: mode %d not available for layer %d", mode, layer);
+    return AG_EINVAL;
+}
+
 // Test/debug readback (synchronous): output activations of conv layer `layer` (kind 0) or the
 // pre-activation gradient currently held for it (kind 1) as fp32 [n][cout][board][board] on the host.
 int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out) {

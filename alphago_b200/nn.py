@@ -119,6 +119,9 @@ class ConvNet(object):
                                                 lr, momentum, C.c_void_p(loss_acc.data_ptr()), _lib.current_stream()),
                    "ag_net_train_step")
 
+    def run_layer(self, layer, mode, n):
+        _lib.check(_lib.lib().ag_net_run_layer(self._h, layer, mode, n, _lib.current_stream()), "ag_net_run_layer")
+
     def grad_tensor(self):
         """the flat gradient buffer as a torch tensor sharing the library's device memory"""
         import torch

@@ -1,0 +1,106 @@
+"""SL training on the device network: the data-parallel step and the `run_training` entry point.
+
+`SLTrainer` is what AlphaGo/training/supervised_policy_trainer.py gets from Keras'
+`model.compile(SGD, categorical_crossentropy) + fit_generator` (spt.py:199-213): minibatch assembly
+with the 8 board symmetries (spt.py:18-40,71-80) as a device gather, forward, softmax cross-entropy,
+backward and the SGD update with Keras' `lr / (1 + decay * iterations)` schedule.  With
+torch.distributed initialised (one process per GPU, NCCL over NVLink) every rank takes its share of
+the global minibatch and the per-layer gradient slices are all-reduced while backward is still
+running on the layers below.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, nn
+
+
+class SLTrainer(object):
+    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=4, process_group=None):
+        import torch
+        self.torch = torch
+        self.net, self.lr0, self.decay, self.momentum = net, float(lr), float(decay), float(momentum)
+        self.iterations = 0
+        self.loss_acc = torch.zeros(2, dtype=torch.float32, device="cuda")
+        self.dist = None
+        self.world = 1
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(process_group) > 1:
+                self.dist, self.world, self.group = dist, dist.get_world_size(process_group), process_group
+        except ImportError:
+            pass
+        # gradient buckets: contiguous runs of layers, last layers first (they finish first in backward)
+        L = net.n_conv
+        per = max(1, (L + buckets - 1) // buckets)
+        self.bucket_of_layer = {}
+        self.buckets = []
+        hi = L
+        while hi > 0:
+            lo = max(0, hi - per)
+            self.buckets.append((lo, hi))
+            hi = lo
+        self._out = None
+        self._labels = None
+
+    def current_lr(self):
+        """Keras 1.0 SGD: lr * 1 / (1 + decay * iterations)"""
+        return self.lr0 / (1.0 + self.decay * self.iterations)
+
+    # ------------------------------------------------------------------ minibatch assembly
+    def assemble(self, d_states, d_actions, index, transform):
+        """dataset tensors resident on the device + host index/transform arrays -> (planes, labels)"""
+        torch = self.torch
+        n = len(index)
+        planes, size = d_states.shape[1], d_states.shape[-1]
+        if self._out is None or self._out.shape[0] != n:
+            self._out = torch.empty((n, planes, size, size), dtype=torch.uint8, device="cuda")
+            self._labels = torch.empty(n, dtype=torch.int32, device="cuda")
+        idx = torch.from_numpy(np.ascontiguousarray(index, np.int64)).cuda(non_blocking=True)
+        tf = torch.from_numpy(np.ascontiguousarray(transform, np.uint8)).cuda(non_blocking=True)
+        _lib.check(_lib.lib().ag_augment(C.c_void_p(d_states.data_ptr()), C.c_void_p(d_actions.data_ptr()),
+                                         C.c_void_p(idx.data_ptr()), C.c_void_p(tf.data_ptr()), n, planes, size,
+                                         C.c_void_p(self._out.data_ptr()), C.c_void_p(self._labels.data_ptr()),
+                                         _lib.current_stream()), "ag_augment")
+        return self._out, self._labels
+
+    # ------------------------------------------------------------------ one optimisation step
+    def step(self, planes, labels):
+        """one SGD step on this rank's (planes uint8 (n,C,S,S), labels int32 (n,)); asynchronous.
+        Loss sum / correct count of the step are accumulated into self.loss_acc."""
+        net, n = self.net, planes.shape[0]
+        lr = self.current_lr()
+        if self.dist is None:
+            net.train_step(planes, labels, lr, self.momentum, self.loss_acc)
+        else:
+            g = net.grad_tensor()
+            offs = net.grad_offsets
+            net.forward_loss(planes, labels, self.loss_acc)
+            works = []
+            for bi, (lo, hi) in enumerate(self.buckets):
+                for l in range(hi - 1, lo - 1, -1):
+                    net.backward_layer(l, n)
+                # this bucket's slice is final: reduce it while the layers below are still in backward.
+                # (NCCL's stream picks up after the kernels enqueued so far; later kernels overlap it.)
+                end = offs[hi] if bi > 0 else offs[-1]  # the first bucket also carries the head's gradients
+                works.append(self.dist.all_reduce(g[offs[lo]:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
+            for w in works:
+                w.wait()
+            net.sgd(lr, self.momentum, 1.0 / self.world)
+        self.iterations += 1
+
+    def evaluate(self, planes, labels):
+        """loss / accuracy only (validation): accumulates into self.loss_acc, no update"""
+        self.net.forward_loss(planes, labels, self.loss_acc)
+
+    def pop_metrics(self, samples):
+        """(mean loss, accuracy) over `samples` local samples since the last call; synchronises"""
+        t = self.loss_acc.clone()
+        self.loss_acc.zero_()
+        cnt = self.torch.tensor([float(samples)], device="cuda")
+        if self.dist is not None:
+            self.dist.all_reduce(t, group=self.group)
+            self.dist.all_reduce(cnt, group=self.group)
+        t = t.cpu().numpy()
+        c = float(cnt.cpu()[0])
+        return float(t[0]) / max(c, 1.0), float(t[1]) / max(c, 1.0)

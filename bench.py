@@ -180,10 +180,146 @@ class EncodeWorkload(object):
         s = min(sample, self.n)
         og.encode_batch(h[0][:64], h[1][:64], h[2][:64], h[3][:64], 19, self.feats, threads=cores)
         t = time.time()
-        og.encode_batch(h[0][:s], h[1][:s], h[2][:s], h[3][:s], 19, self.feats, threads=cores)
+        reps = 0
+        while time.time() - t < 5.0 or reps < 1:
+            og.encode_batch(h[0][:s], h[1][:s], h[2][:s], h[3][:s], 19, self.feats, threads=cores)
+            reps += 1
         dt = time.time() - t
-        return {"value": round(s / dt, 1), "unit": self.unit, "cores": cores, "kind": "port",
-                "sample": "%d of the step's positions, C oracle (oracle/go_oracle.c) with OpenMP over all host cores, %.2f s" % (s, dt)}
+        return {"value": round(reps * s / dt, 1), "unit": self.unit, "cores": cores, "kind": "port",
+                "sample": "%d x %d of the step's positions, C oracle (oracle/go_oracle.c) with OpenMP over all host cores, %.2f s"
+                          % (reps, s, dt)}
+
+
+# ------------------------------------------------------------------------------------------ train
+TRAIN_FLOP_PER_POSITION = 8.2380e9   # fwd 2.8015 + wgrad 2.8015 + dgrad 2.6352 GFLOP (192 filters, 48 planes)
+FWD3x3_FLOP_PER_POSITION = 2 * 361 * 9 * 192 * 192  # one 3x3 192->192 layer, algorithmic (no padding flops)
+TRAIN_FEATS = FEATS46[:-1] + ["zeros", "zeros", "zeros"]  # 48 planes; the two ladder planes are zero until the ladder kernel lands
+
+
+class TrainWorkload(object):
+    name = "train"
+    metric = "sl_policy_train_positions_per_sec"
+    unit = "positions/s"
+    dtype = "bf16"
+
+    def __init__(self, batch, rank, dataset=4096):
+        import numpy as np
+        import torch
+        from alphago_b200 import go, nn
+        from alphago_b200.preprocessing import Preprocess
+        from alphago_b200.training import SLTrainer
+        self.torch, self.np = torch, np
+        self.batch = batch
+        rng = np.random.RandomState(77 + rank)
+        # synthetic dataset: random-playout positions encoded by the CUDA encoder, labels uniform over legal moves
+        b, a, pl, ko = go.playout_positions(500 + rank, dataset, size=19, max_moves=400, per_game=16)
+        pp = Preprocess(TRAIN_FEATS)
+        self.states = pp.encode_packed(*[torch.from_numpy(x).cuda() for x in (b, a, pl, ko)], 19)
+        legal = self.states[:, 20:28].sum(1).reshape(dataset, 361).cpu().numpy() > 0
+        acts = np.zeros((dataset, 2), np.uint8)
+        for i in range(dataset):
+            mv = np.flatnonzero(legal[i])
+            m = int(mv[rng.randint(len(mv))]) if len(mv) else 0
+            acts[i] = divmod(m, 19)
+        self.h_states = self.states.cpu().numpy()
+        self.h_actions = acts
+        self.actions = torch.from_numpy(acts).cuda()
+        self.net = nn.ConvNet(19, 48, [192] * 12, [5] + [3] * 11, max_batch=batch)
+        self.net.init_uniform(seed=1)  # identical weights on every rank
+        self.trainer = SLTrainer(self.net, lr=0.003, decay=0.0001, momentum=0.0)
+        self.dataset = dataset
+        self.rng = rng
+        self.i = 0
+        self.units_per_step = batch
+        self.launches_per_step = None
+
+    def _next(self):
+        idx = (self.np.arange(self.batch) + self.i * self.batch) % self.dataset
+        self.i += 1
+        return idx, self.rng.randint(0, 8, self.batch)
+
+    def step(self):
+        idx, tf = self._next()
+        x, y = self.trainer.assemble(self.states, self.actions, idx, tf)
+        self.trainer.step(x, y)
+
+    def e2e_setup(self):
+        t = self.torch
+        self.pin_x = t.empty((self.batch, 48, 19, 19), dtype=t.uint8).pin_memory()
+        self.pin_a = t.empty((self.batch, 2), dtype=t.uint8).pin_memory()
+        self.h2d = self.pin_x.numel() + self.pin_a.numel() + self.batch * 9
+        self.d2h = 8
+        self.ident = self.np.arange(self.batch)
+
+    def e2e_step(self):
+        # the public training path with a HOST dataset: gather on the host, copy, augment + step on the device, read the loss
+        idx, tf = self._next()
+        self.pin_x.numpy()[...] = self.h_states[idx]
+        self.pin_a.numpy()[...] = self.h_actions[idx]
+        dx = self.pin_x.cuda(non_blocking=True); da = self.pin_a.cuda(non_blocking=True)
+        x, y = self.trainer.assemble(dx, da, self.ident, tf)
+        self.trainer.step(x, y)
+        return float(self.trainer.loss_acc.cpu()[0])
+
+    def kernel_rooflines(self, pk):
+        """per-launch device time of the three GEMM kernels of a middle 3x3 layer, CUDA events on the launching stream"""
+        t = self.torch
+        out = {}
+        flop = self.batch * FWD3x3_FLOP_PER_POSITION
+        for mode, name in ((0, "conv_gemm_kernel(fwd 3x3)"), (1, "conv_gemm_kernel(dgrad 3x3)"), (2, "wgrad_kernel+reduce(3x3)")):
+            for _ in range(3):
+                self.net.run_layer(6, mode, self.batch)
+            e0, e1 = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
+            reps = 20
+            e0.record()
+            for _ in range(reps):
+                self.net.run_layer(6, mode, self.batch)
+            e1.record()
+            t.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            out[name] = {"ms": round(ms, 4), "tflops": round(flop / (ms * 1e-3) / 1e12, 1),
+                         "frac_of_burst_peak": round(flop / (ms * 1e-3) / 1e12 / pk["tensor_burst"], 4)}
+        return out
+
+    def roofline(self, ms_per_step, pk):
+        ach = self.batch * TRAIN_FLOP_PER_POSITION / (ms_per_step * 1e-3) / 1e12
+        k = self.kernel_rooflines(pk)
+        dom = k["conv_gemm_kernel(fwd 3x3)"]
+        return {"bound": "tensor", "achieved": dom["tflops"], "peak": pk["tensor_burst"], "unit": "TFLOP/s",
+                "frac": dom["frac_of_burst_peak"], "traffic": None, "kernel": "ag::conv_gemm_kernel (3x3 192->192 forward, layer 6, timed alone)",
+                "peak_source": pk["source"] + " (cuBLAS bf16 burst, kernel timed alone)",
+                "algorithmic_flops_per_launch": self.batch * FWD3x3_FLOP_PER_POSITION,
+                "whole_step": {"achieved": round(ach, 1), "peak": pk["tensor_sustained"], "frac": round(ach / pk["tensor_sustained"], 4),
+                               "unit": "TFLOP/s", "note": "8.2380 GFLOP/position over the whole step vs sustained peak"},
+                "kernels": k}
+
+    def config(self):
+        return {"workload": "AlphaGo SL policy net (13 convs: 5x5 + 11x 3x3 + 1x1, 192 filters, 48 planes) bf16 training step, "
+                            "batch %d per GPU, device-side D4 augmentation, SGD lr decay" % self.batch,
+                "per_gpu_batch": self.batch, "planes": 48,
+                "l2": "each step touches ~1 GB of activations/gradients (> 126 MB L2); dataset of %d positions rotates" % self.dataset,
+                "note": "ladder planes are zero-filled until the ladder kernel lands"}
+
+    def cpu_baseline(self):
+        import torch
+        from oracle import nn_oracle as no
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        params = no.make_params(48, [192] * 12, [5] + [3] * 11, seed=1)
+        bs = 16
+        x = self.h_states[:bs]
+        y = self.h_actions[:bs, 0].astype("int64") * 19 + self.h_actions[:bs, 1]
+        no.loss_and_grads(params, x[:2], y[:2])
+        t = time.time()
+        steps = 0
+        while time.time() - t < 10 or steps < 1:
+            _, _, grads, _ = no.loss_and_grads(params, x, y)
+            params, _ = no.sgd_update(params, grads, 0.003)
+            steps += 1
+        dt = time.time() - t
+        return {"value": round(steps * bs / dt, 2), "unit": self.unit, "cores": cores, "kind": "port",
+                "sample": "%d steps at batch %d of the same architecture, fp32 torch-CPU restatement (oracle/nn_oracle.py), %.1f s; "
+                          "the reference's Keras 1.0/Theano 0.8 path is unavailable on this box" % (steps, bs, dt)}
 
 
 def reference_arm(args, rank):
@@ -222,13 +358,15 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=["encode", "train"])
     ap.add_argument("--positions", type=int, default=16384)
+    ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--planes", type=int, default=46, choices=[46, 48])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-encoder", action="store_true")
     args = ap.parse_args()
     rank, world, local = dist_env()
-    workload = args.workload or "encode"
+    workload = args.workload or "train"
     if args.steps is None:
-        args.steps = 200 if args.impl == "ours" else 5
+        args.steps = (200 if workload == "encode" else 100) if args.impl == "ours" else 5
     if args.warmup is None:
         args.warmup = 5 if args.impl == "ours" else 1
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -246,7 +384,10 @@ def main():
     from oracle import go_oracle as og
 
     feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
-    wl = EncodeWorkload(args.positions, feats, rank)
+    if workload == "train":
+        wl = TrainWorkload(args.batch, rank)
+    else:
+        wl = EncodeWorkload(args.positions, feats, rank)
     pk = peaks()
 
     def barrier():
@@ -303,6 +444,21 @@ def main():
                 "roofline": wl.roofline(ms_per_step, pk), "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = wl.cpu_baseline()
+        if workload == "train" and not args.no_encoder:
+            # the metric's second half: 48-plane encode positions/s on this GPU (configs[1]), same timing rules
+            ew = EncodeWorkload(args.positions, feats, rank)
+            for _ in range(3):
+                ew.step()
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            for _ in range(50):
+                ew.step()
+            f1.record()
+            torch.cuda.synchronize()
+            ems = f0.elapsed_time(f1) / 50
+            line["encoder"] = {"metric": ew.metric, "value": round(ew.n / (ems * 1e-3), 1), "unit": ew.unit, "ms_per_step": round(ems, 4),
+                               "config": ew.config(), "roofline": ew.roofline(ems, pk)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

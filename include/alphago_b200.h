@@ -132,6 +132,16 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
 /* single-GPU step: forward_loss + every backward_layer + sgd */
 int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float lr, float momentum,
                       float* d_loss_acc, void* stream);
+/* Minibatch assembly (shuffled_hdf5_batch_generator + BOARD_TRANSFORMATIONS + one_hot_action,
+ * supervised_policy_trainer.py:10-40,71-80): for b in [0, batch): sample d_index[b] of the dataset
+ * (d_states uint8 [N][planes][size][size], d_actions uint8 [N][2] as (x, y)) under dihedral transform
+ * d_transform[b] in 0..7 (the order of BOARD_TRANSFORMATIONS) -> d_out uint8 [batch][planes][size][size]
+ * and d_labels int32 [batch] = flat index of the transformed action. */
+int ag_augment(const uint8_t* d_states, const uint8_t* d_actions, const int64_t* d_index, const uint8_t* d_transform,
+               int batch, int planes, int size, uint8_t* d_out, int32_t* d_labels, void* stream);
+/* measurement hook for bench.py's per-kernel roofline: re-run one kernel of the step on the buffers in place.
+ * mode 0 = forward conv of `layer`, 1 = its data gradient, 2 = its weight gradient */
+int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream);
 /* test/debug readback (synchronous, allocates): kind 0 = activations of conv layer, 1 = its pre-activation
  * gradient, as fp32 [n][cout][board][board] on the host */
 int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out);

@@ -112,3 +112,31 @@ def sgd_update(params, grads, lr, momentum=0.0, velocity=None):
     if params.get("pos_bias") is not None:
         out["pos_bias"] = new[2 * n + 2]
     return out, velocity
+
+
+# supervised_policy_trainer.py:71-80 BOARD_TRANSFORMATIONS, restated (same order, arrays indexed [x][y])
+BOARD_TRANSFORMATIONS = [
+    lambda f: f,
+    lambda f: np.rot90(f, 1),
+    lambda f: np.rot90(f, 2),
+    lambda f: np.rot90(f, 3),
+    lambda f: np.fliplr(f),
+    lambda f: np.flipud(f),
+    lambda f: np.transpose(f),
+    lambda f: np.fliplr(np.rot90(f, 1)),
+]
+
+
+def augment_batch(states, actions, index, transform):
+    """shuffled_hdf5_batch_generator's per-sample work (spt.py:27-36): transform every plane and the
+    one-hot action; returns uint8 (B, F, S, S) and the flat label of the transformed one-hot."""
+    size = states.shape[-1]
+    X = np.zeros((len(index),) + states.shape[1:], np.uint8)
+    Y = np.zeros(len(index), np.int32)
+    for b, (i, t) in enumerate(zip(index, transform)):
+        tf = BOARD_TRANSFORMATIONS[t]
+        X[b] = np.array([tf(plane) for plane in states[i]])
+        onehot = np.zeros((size, size))
+        onehot[tuple(actions[i])] = 1  # one_hot_action, spt.py:10-15
+        Y[b] = int(np.argmax(tf(onehot).flatten()))
+    return X, Y

