@@ -30,6 +30,19 @@ def _r(t, emulate):
     return t + (t.detach().to(torch.bfloat16).to(t.dtype) - t.detach())
 
 
+class _RoundGrad(torch.autograd.Function):
+    """identity forward; rounds the incoming gradient to bf16 in backward.  The CUDA path stores every
+    layer's pre-activation gradient in bf16 before its weight, bias and data gradients are formed."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(g.dtype)
+
+
 def make_params(in_planes, filters, widths, seed=0, scale=0.05, bias_scale=0.0, board=19, value_head=False):
     """init='uniform' of Keras 1.0: U(-0.05, 0.05), zero biases (policy.py:127).  bias_scale>0
     gives non-zero biases so tests exercise the bias path."""
@@ -58,8 +71,10 @@ def forward(params, planes, emulate_bf16=False, dtype=torch.float32, want_grad=F
         wt = torch.tensor(w, dtype=dtype, requires_grad=want_grad)
         bt = torch.tensor(b, dtype=dtype, requires_grad=want_grad)
         tensors += [wt, bt]
-        x = F.relu(F.conv2d(x, _r(wt, emulate_bf16), bt, padding=w.shape[2] // 2))
-        x = _r(x, emulate_bf16)
+        pre = F.conv2d(x, _r(wt, emulate_bf16), bt, padding=w.shape[2] // 2)
+        if emulate_bf16 and want_grad:
+            pre = _RoundGrad.apply(pre)
+        x = _r(F.relu(pre), emulate_bf16)
         acts.append(x)
     hw = torch.tensor(params["head_w"], dtype=dtype, requires_grad=want_grad)
     hb = torch.tensor(params["head_b"], dtype=dtype, requires_grad=want_grad)
@@ -92,7 +107,7 @@ def loss_and_grads(params, planes, labels, emulate_bf16=False, dtype=torch.float
     F.cross_entropy(out["logits"], lab).backward()
     acc = (out["probs"].argmax(1) == lab).double().mean()
     grads = [t.grad.numpy() for t in out["tensors"]]
-    return float(loss), float(acc), grads, out
+    return float(loss.detach()), float(acc), grads, out
 
 
 def sgd_update(params, grads, lr, momentum=0.0, velocity=None):

@@ -2,7 +2,7 @@
 # GPU-box visit for the conv stack: NN parity tests (verbose), a slice of the encoder tests, the benches,
 # then the ncu launch list of a short train bench (only if everything before it exited 0).
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_nn_gpu.py -m gpu -v --maxfail=30 -p no:cacheprovider > gpurun_out/pytest_nn.log 2>&1
+timeout 900 python -m pytest tests/test_nn_gpu.py tests/test_policy_gpu.py -m gpu -v --maxfail=30 -p no:cacheprovider > gpurun_out/pytest_nn.log 2>&1
 NN=$?
 echo "pytest nn exit $NN" >> gpurun_out/pytest_nn.log
 timeout 600 python -m pytest tests/test_encoder_gpu.py -m gpu -q --maxfail=30 -p no:cacheprovider -k "golden or edge or subsets" > gpurun_out/pytest_enc.log 2>&1
