@@ -236,7 +236,7 @@ value_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float
     }
 }
 
-// bias gradient: db[c] = sum_m G[m][c]; two deterministic stages (row slabs, then slabs)
+// bias gradient: db[c] = sum_m G[m][c]; two deterministic stages (row slabs, then a warp per channel over the slabs)
 __global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restrict__ G, size_t rows, int ld, float* __restrict__ part) {
     __shared__ float s[256][9];
     const int groups = ld / 8, lanes = 256 / groups;
@@ -244,13 +244,26 @@ __global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restri
     size_t per = (rows + gridDim.x - 1) / gridDim.x;
     size_t r0 = blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
     float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (rl < lanes)
-        for (size_t r = r0 + rl; r < r1; r += lanes) {
+    if (rl < lanes) {
+        size_t r = r0 + rl;
+        for (; r + 3 * (size_t)lanes < r1; r += 4 * (size_t)lanes) {  // four independent 16-byte loads in flight
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = *reinterpret_cast<const uint4*>(G + (r + u * (size_t)lanes) * ld + g * 8);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bf16* vb = reinterpret_cast<const bf16*>(&v[u]);
+#pragma unroll
+                for (int j = 0; j < 8; j++) a[j] += __bfloat162float(vb[j]);
+            }
+        }
+        for (; r < r1; r += lanes) {
             uint4 v = *reinterpret_cast<const uint4*>(G + r * ld + g * 8);
             const bf16* vb = reinterpret_cast<const bf16*>(&v);
 #pragma unroll
             for (int j = 0; j < 8; j++) a[j] += __bfloat162float(vb[j]);
         }
+    }
 #pragma unroll
     for (int j = 0; j < 8; j++) s[threadIdx.x][j] = a[j];
     __syncthreads();
@@ -261,12 +274,14 @@ __global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restri
         part[(size_t)blockIdx.x * ld + threadIdx.x] = t;
     }
 }
-__global__ void colsum_stage2_kernel(const float* __restrict__ part, int nblocks, int ld, int cout, float* __restrict__ db) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restrict__ part, int nblocks, int ld, int cout, float* __restrict__ db) {
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (c >= cout) return;
     float t = 0.f;
-    for (int b = 0; b < nblocks; b++) t += part[(size_t)b * ld + c];
-    db[c] = t;
+    for (int b = lane; b < nblocks; b += 32) t += part[(size_t)b * ld + c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) db[c] = t;
 }
 
 // SGD with momentum (Keras 1.0 SGD.get_updates: v = momentum*v - lr*g; w += v), one launch per layer.
@@ -500,7 +515,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
     if (!rc) rc = dev_alloc(&net->vhb, 4);
     if (!rc) rc = dev_alloc(&net->vhpos, 368);
     if (!rc) rc = dev_alloc(&net->head_partial, (size_t)max_batch * 625);
-    net->colsum_blocks = sm_count() * 2;
+    net->colsum_blocks = sm_count() * 8;
     if (!rc) rc = dev_alloc(&net->colsum_part, (size_t)net->colsum_blocks * 256);
     if (!rc && head_kind == 1) {
         rc = dev_alloc(&net->d1w, (size_t)net->hidden * pts);
@@ -716,7 +731,7 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     // bias gradient
     colsum_stage1_kernel<<<net->colsum_blocks, 256, 0, st>>>(G, rows, c.ldout, net->colsum_part);
     AG_LAUNCH_CHECK("colsum_stage1_kernel");
-    colsum_stage2_kernel<<<(c.ldout + 127) / 128, 128, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
+    colsum_stage2_kernel<<<(c.ldout + 7) / 8, 256, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
     AG_LAUNCH_CHECK("colsum_stage2_kernel");
     // weight gradient
     WgradArgs w;

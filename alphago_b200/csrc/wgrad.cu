@@ -159,10 +159,15 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __
 size_t wgrad_smem_bytes(int kin) { return 1024 + (size_t)kStages * (2 + kin / 64) * kChunkBytes + sizeof(WgradBarriers) + 64; }
 
 int wgrad_plan_splits(int taps, int ldout, int m_total) {
+    // CTAs = tiles * splits should fill whole waves of the SMs: one wave if that keeps >= 85 % of them busy,
+    // else two.  Fewer, longer K slices also mean fewer fp32 partials to write and reduce.
     int chunks = taps * (ldout / 64);
     int tiles = (chunks + 1) / 2;
     int kb = (m_total + 63) / 64;
-    int s = (2 * sm_count() + tiles - 1) / tiles;  // about two waves of CTAs
+    int sms = sm_count();
+    int s1 = sms / tiles, s2 = 2 * sms / tiles;
+    int s = s1;
+    if (s1 < 1 || ((double)tiles * s1 / sms < 0.85 && (double)tiles * s2 / (2.0 * sms) > (double)tiles * s1 / sms + 0.05)) s = s2;
     if (s > kb) s = kb;
     if (s < 1) s = 1;
     if (s > kWgradMaxSplits) s = kWgradMaxSplits;

@@ -15,6 +15,31 @@ import numpy as np
 from . import _lib, nn
 
 
+def plan_buckets(n_conv, offsets, buckets=4):
+    """Gradient exchange plan: [(layer_lo, layer_hi, start, end)] over the flat gradient buffer, in the order the
+    slices become final during backward (last layers first).  `offsets` = n_conv+2 element offsets (layer starts,
+    head start, end); the first bucket also carries the head's slice (ready right after the loss)."""
+    per = max(1, (n_conv + buckets - 1) // buckets)
+    plan, hi = [], n_conv
+    while hi > 0:
+        lo = max(0, hi - per)
+        end = offsets[-1] if not plan else offsets[hi]
+        plan.append((lo, hi, offsets[lo], end))
+        hi = lo
+    return plan
+
+
+def allreduce_in_buckets(dist, flat, plan, group=None, after_bucket=None):
+    """sum-all-reduce `flat` slice by slice following `plan`; `after_bucket(i)` (optional) runs before bucket i is
+    issued -- SLTrainer enqueues that bucket's backward kernels there.  Returns the async work handles."""
+    works = []
+    for i, (lo, hi, start, end) in enumerate(plan):
+        if after_bucket is not None:
+            after_bucket(i, lo, hi)
+        works.append(dist.all_reduce(flat[start:end], op=dist.ReduceOp.SUM, group=group, async_op=True))
+    return works
+
+
 class SLTrainer(object):
     def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=4, process_group=None):
         import torch
@@ -31,15 +56,7 @@ class SLTrainer(object):
         except ImportError:
             pass
         # gradient buckets: contiguous runs of layers, last layers first (they finish first in backward)
-        L = net.n_conv
-        per = max(1, (L + buckets - 1) // buckets)
-        self.bucket_of_layer = {}
-        self.buckets = []
-        hi = L
-        while hi > 0:
-            lo = max(0, hi - per)
-            self.buckets.append((lo, hi))
-            hi = lo
+        self.plan = plan_buckets(net.n_conv, net.grad_offsets, buckets)
         self._out = None
         self._labels = None
 
@@ -73,17 +90,14 @@ class SLTrainer(object):
         if self.dist is None:
             net.train_step(planes, labels, lr, self.momentum, self.loss_acc)
         else:
-            g = net.grad_tensor()
-            offs = net.grad_offsets
             net.forward_loss(planes, labels, self.loss_acc)
-            works = []
-            for bi, (lo, hi) in enumerate(self.buckets):
+
+            def backward_bucket(i, lo, hi):
                 for l in range(hi - 1, lo - 1, -1):
                     net.backward_layer(l, n)
-                # this bucket's slice is final: reduce it while the layers below are still in backward.
-                # (NCCL's stream picks up after the kernels enqueued so far; later kernels overlap it.)
-                end = offs[hi] if bi > 0 else offs[-1]  # the first bucket also carries the head's gradients
-                works.append(self.dist.all_reduce(g[offs[lo]:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
+            # each bucket is reduced as soon as its layers' gradients are enqueued: NCCL's stream picks up after the
+            # kernels issued so far, so the exchange overlaps the backward of the layers below
+            works = allreduce_in_buckets(self.dist, net.grad_tensor(), self.plan, self.group, backward_bucket)
             for w in works:
                 w.wait()
             net.sgd(lr, self.momentum, 1.0 / self.world)
