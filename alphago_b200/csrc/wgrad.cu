@@ -10,6 +10,8 @@
 // flattened (tap, co) axis = two 64-channel chunks, each loaded with its own tap shift, and a
 // contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tap*co][ci] and
 // wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
+#include <string.h>
+
 #include "common.cuh"
 #include "conv.cuh"
 #include "tcgen.cuh"
@@ -200,3 +202,51 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
 }
 
 }  // namespace ag
+
+// ------------------------------------------------------------------------------------ standalone op
+namespace ag {
+static int wgrad_offsets(int width, int row_stride, int* off) {
+    if (width < 1 || width > 5 || width % 2 == 0) { set_error("wgrad: filter width %d must be odd and <= 5", width); return AG_EINVAL; }
+    int pad = width / 2, t = 0;
+    for (int kx = 0; kx < width; kx++)
+        for (int ky = 0; ky < width; ky++, t++) off[t] = (kx - pad) * row_stride + (ky - pad);
+    return AG_OK;
+}
+static int wgrad_check(long long rows, int ldout, int kin, int row_stride) {
+    if (rows < 1 || rows > 0x7fffffffLL - 4096 || row_stride < 1) { set_error("wgrad: bad rows/row_stride"); return AG_EINVAL; }
+    if (ldout < 64 || ldout % 64 || kin < 64 || kin % 64 || kin > 256) { set_error("wgrad: channels must be padded to 64 (ldout=%d, kin=%d <= 256)", ldout, kin); return AG_EINVAL; }
+    return AG_OK;
+}
+}  // namespace ag
+
+extern "C" {
+
+// bytes of scratch ag_wgrad wants for this problem (the split-K partials)
+size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows) {
+    if (ag::wgrad_check(rows, ldout, kin, 1) || width < 1 || width > 5) return 0;
+    return (size_t)ag::wgrad_plan_splits(width * width, ldout, (int)rows) * width * width * ldout * kin * sizeof(float);
+}
+
+int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride, float* d_scratch,
+             size_t scratch_bytes, float* d_dw, void* stream) {
+    int rc = ag::wgrad_check(rows, ldout, kin, row_stride);
+    if (rc) return rc;
+    ag::WgradArgs a;
+    memset(&a, 0, sizeof(a));
+    rc = ag::wgrad_offsets(width, row_stride, a.off);
+    if (rc) return rc;
+    a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
+    const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, (int)rows);
+    if ((size_t)a.splits * partial > scratch_bytes) a.splits = (int)(scratch_bytes / partial);
+    if (a.splits < 1 || !d_scratch) { ag::set_error("ag_wgrad: scratch of %zu bytes is smaller than one partial (%zu bytes)", scratch_bytes, partial); return AG_EINVAL; }
+    a.scratch = d_scratch;
+    CUtensorMap tg, tx;
+    rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
+    if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
+    if (rc) return rc;
+    return ag::wgrad_launch(tg, tx, a, d_dw, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+

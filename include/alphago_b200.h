@@ -132,6 +132,17 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
 /* single-GPU step: forward_loss + every backward_layer + sgd */
 int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float lr, float momentum,
                       float* d_loss_acc, void* stream);
+/* Stand-alone weight-gradient op on caller-owned buffers (the backward of one Keras Convolution2D layer,
+ * policy.py:119-142, as run inside fit_generator, supervised_policy_trainer.py:207-213):
+ *   d_dw[tap][co][ci] = sum_m d_g[m - shift(tap)][co] * d_x[m][ci],  shift(kx,ky) = (kx-w/2)*row_stride + (ky-w/2)
+ * d_g bf16 [rows][ldout] = gradient w.r.t. the layer's pre-activation output, d_x bf16 [rows][kin] = its input,
+ * both "padded pixel rows" (>= w/2 zero slots after every board row and zero rows after
+ * every image); ldout, kin multiples of 64 (kin <= 256); width odd <= 5; d_dw fp32 [width*width][ldout][kin].
+ * d_scratch holds the split-K partials: ag_wgrad_scratch_bytes() is the preferred size, anything down to one
+ * partial (width*width*ldout*kin*4 bytes) works with fewer splits.  Deterministic (fixed-order reduction). */
+size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows);
+int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
+             float* d_scratch, size_t scratch_bytes, float* d_dw, void* stream);
 /* Minibatch assembly (shuffled_hdf5_batch_generator + BOARD_TRANSFORMATIONS + one_hot_action,
  * supervised_policy_trainer.py:10-40,71-80): for b in [0, batch): sample d_index[b] of the dataset
  * (d_states uint8 [N][planes][size][size], d_actions uint8 [N][2] as (x, y)) under dihedral transform
