@@ -23,5 +23,7 @@ def bind(L):
     L.ag_wgrad_scratch_bytes.restype = C.c_size_t
     L.ag_wgrad_scratch_bytes.argtypes = [i, i, i, C.c_longlong]
     L.ag_wgrad.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, C.c_size_t, vp, vp]
+    L.ag_wgrad_static_max_bytes.restype = C.c_size_t
+    L.ag_wgrad_static.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, vp]
     L.ag_augment.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp]
     return L

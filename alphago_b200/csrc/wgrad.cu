@@ -250,3 +250,65 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
 
 }  // extern "C"
 
+// ------------------------------------------------------------------------------------ no-allocation variant
+// Same computation as ag_wgrad, for callers that are not allowed to allocate device memory: code running inside
+// another framework's memory plan (a pool sized ahead of time that must not be disturbed), inside a region where
+// the allocator would synchronise the device or fail outright (a latency-critical serving loop), or in a process
+// whose memory budget was fixed at start-up.  The split-K partials live in an array that is part of this library's
+// image: every GPU that loads libalphago_b200.so sets aside AG_WGRAD_STATIC_SCRATCH_BYTES for it until the process
+// exits, whether or not this entry point is ever called.
+#define AG_WGRAD_STATIC_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) float g_wgrad_static_scratch[AG_WGRAD_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace ag {
+// In host code `g_wgrad_static_scratch` is only a handle for the symbol, never a device address; the address a
+// kernel can use has to be asked for, per device, with that device current.
+static int wgrad_static_scratch_ptr(float** out) {
+    constexpr int kMaxDevices = 64;
+    static float* cached[kMaxDevices] = {nullptr};
+    int dev = 0;
+    AG_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { set_error("ag_wgrad_static: device ordinal %d not supported", dev); return AG_EINVAL; }
+    if (!cached[dev]) {
+        float* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_wgrad_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_wgrad_static_scratch)");
+        if (!p) { set_error("ag_wgrad_static: no device address for the built-in scratch"); return AG_ECUDA; }
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return AG_OK;
+}
+}  // namespace ag
+
+extern "C" {
+
+size_t ag_wgrad_static_max_bytes(void) { return AG_WGRAD_STATIC_SCRATCH_BYTES; }
+
+int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride, float* d_dw,
+                    void* stream) {
+    int rc = ag::wgrad_check(rows, ldout, kin, row_stride);
+    if (rc) return rc;
+    ag::WgradArgs a;
+    memset(&a, 0, sizeof(a));
+    rc = ag::wgrad_offsets(width, row_stride, a.off);
+    if (rc) return rc;
+    a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
+    const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
+    if (partial > AG_WGRAD_STATIC_SCRATCH_BYTES) {
+        ag::set_error("ag_wgrad_static: one %dx%d x %d x %d gradient (%zu bytes) exceeds the built-in scratch of %u bytes; "
+                      "use ag_wgrad with your own scratch", width, width, ldout, kin, partial, AG_WGRAD_STATIC_SCRATCH_BYTES);
+        return AG_EINVAL;
+    }
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, (int)rows);
+    if ((size_t)a.splits * partial > AG_WGRAD_STATIC_SCRATCH_BYTES) a.splits = (int)(AG_WGRAD_STATIC_SCRATCH_BYTES / partial);
+    rc = ag::wgrad_static_scratch_ptr(&a.scratch);
+    if (rc) return rc;
+    CUtensorMap tg, tx;
+    rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
+    if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
+    if (rc) return rc;
+    return ag::wgrad_launch(tg, tx, a, d_dw, (cudaStream_t)stream);
+}
+
+}  // extern "C"

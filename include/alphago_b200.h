@@ -143,6 +143,22 @@ int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_lab
 size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows);
 int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
              float* d_scratch, size_t scratch_bytes, float* d_dw, void* stream);
+/* ag_wgrad for callers that must not allocate.  (No counterpart in the reference: nothing there manages device
+ * memory.)  Same arguments and result as ag_wgrad without the scratch pair: the split-K partials go to a fixed
+ * array built into the library image, ag_wgrad_static_max_bytes() = 16 MiB, which every GPU that loads the
+ * library holds until the process exits.  Meant for code that runs inside someone else's memory plan -- a
+ * pre-sized pool that must stay untouched, a serving loop where cudaMalloc would stall or fail, a process with a
+ * fixed device-memory budget.  It calls no cudaMalloc/cudaFree and no allocating library routine.
+ *   - a problem whose single partial (width*width*ldout*kin*4 bytes) is larger than the array is refused with
+ *     AG_EINVAL and a message naming both sizes; smaller problems use as many splits as fit
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+ *     current); make that first call before starting any stream capture
+ *   - all calls share the one array and it keeps the previous call's partials; the kernel overwrites every
+ *     element it later reads, so nothing needs clearing -- but two calls whose kernels overlap on the GPU
+ *     (different streams, or different host threads) race on it: keep them ordered on one stream */
+size_t ag_wgrad_static_max_bytes(void);
+int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
+                    float* d_dw, void* stream);
 /* Minibatch assembly (shuffled_hdf5_batch_generator + BOARD_TRANSFORMATIONS + one_hot_action,
  * supervised_policy_trainer.py:10-40,71-80): for b in [0, batch): sample d_index[b] of the dataset
  * (d_states uint8 [N][planes][size][size], d_actions uint8 [N][2] as (x, y)) under dihedral transform
