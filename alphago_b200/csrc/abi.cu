@@ -90,7 +90,6 @@ int ag_encode(const int8_t* d_board, const uint8_t* d_age, const int8_t* d_playe
     ag::enc::PlaneTable tab;
     int rc = ag::build_plane_table(h_features, n_features, &tab);
     if (rc) return rc;
-    if (tab.need_ladder) { set_error("ag_encode: ladder planes are not built yet"); return AG_EINVAL; }
     if (n == 0) return AG_OK;
     if (!d_board || !d_age || !d_player || !d_ko || !d_out) { set_error("ag_encode: null device pointer"); return AG_EINVAL; }
     return ag::encode_launch(d_board, d_age, d_player, d_ko, n, size, tab, d_out, (cudaStream_t)stream);

@@ -12,6 +12,8 @@
 //   warp 0    TMA producer (one elected lane)
 //   warp 1    TMEM allocation + UMMA issue (one elected lane)
 //   warps 2-5 epilogue: tcgen05.ld -> bias / ReLU / ReLU-gate -> bf16 -> global (pad rows skipped)
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "conv.cuh"
 #include "tcgen.cuh"
@@ -21,22 +23,28 @@ namespace ag {
 namespace {
 
 constexpr int kTileM = 128;
-constexpr int kStages = 4;
 constexpr int kABytes = kTileM * 128;  // 128 rows x 64 bf16
 constexpr int kThreads = 192;
 constexpr int kAccStride = 256;  // TMEM columns between the two accumulator buffers
 constexpr int kTmemCols = 512;
 
+constexpr int kMaxStages = 6;
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {  // streaming 16-byte load, no L1 allocation
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
 struct __align__(8) ConvBarriers {
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
     uint64_t acc_full[2];
     uint64_t acc_empty[2];
     uint32_t tmem_base;
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
-conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const ConvArgs p) {
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const ConvArgs p, const int kStages) {
     extern __shared__ __align__(1024) uint8_t smem[];
     // carve: stages x (A | B), then barriers, then bias
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
@@ -127,12 +135,27 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const __nv_bfloat16* gate = nullptr;
             if (p.gate)
                 gate = p.gate + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * p.gate_ld;
+            // the first chunk of the ReLU gate is fetched before waiting for the accumulator
+            uint4 gnext[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            if (gate && valid) {
+#pragma unroll
+                for (int g = 0; g < 4; g++)
+                    if (g * 8 < p.n) gnext[g] = ld_nc_v4(gate + g * 8);
+            }
             tc::mbar_wait(&bars->acc_full[buf], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride;
             for (int c0 = 0; c0 < p.n; c0 += 32) {
                 uint32_t r[32];
+                uint4 gcur[4];
+#pragma unroll
+                for (int g = 0; g < 4; g++) gcur[g] = gnext[g];
                 tc::tmem_ld32(taddr + c0, r);
+                if (gate && valid && c0 + 32 < p.n) {  // next chunk's ReLU gate: in flight while this chunk is processed
+#pragma unroll
+                    for (int g = 0; g < 4; g++)
+                        if (c0 + 32 + g * 8 < p.n) gnext[g] = ld_nc_v4(gate + c0 + 32 + g * 8);
+                }
                 tc::tmem_ld_wait();
                 if (valid) {
 #pragma unroll
@@ -146,8 +169,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                 for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
                             }
                             if (gate) {
-                                uint4 gv = *reinterpret_cast<const uint4*>(gate + c0 + g * 8);
-                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gv);
+                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gcur[g]);
 #pragma unroll
                                 for (int j = 0; j < 8; j++) v[j] = __bfloat162float(gb[j]) > 0.f ? v[j] : 0.f;
                             }
@@ -205,13 +227,24 @@ int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t col
     return AG_OK;
 }
 
-static size_t conv_smem_bytes(int n) { return 1024 + (size_t)kStages * (kABytes + n * 128) + sizeof(ConvBarriers) + 256 * sizeof(float); }
+static size_t conv_smem_bytes(int n, int stages) { return 1024 + (size_t)stages * (kABytes + n * 128) + sizeof(ConvBarriers) + 256 * sizeof(float); }
+
+// pipeline depth: as many stages as fit in 227 KB, at most kMaxStages (AG_CONV_STAGES overrides, for experiments)
+static int conv_stages(int n) {
+    static int forced = -1;
+    if (forced < 0) { const char* e = getenv("AG_CONV_STAGES"); forced = e ? atoi(e) : 0; }
+    int s = kMaxStages;
+    while (s > 2 && conv_smem_bytes(n, s) > 227 * 1024) s--;
+    if (forced >= 2 && forced <= s) s = forced;
+    return s;
+}
 
 int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvArgs& args, cudaStream_t stream) {
     if (args.n < 16 || args.n > 256 || args.n % 16 != 0) { set_error("conv: N=%d must be a multiple of 16 in [16,256]", args.n); return AG_EINVAL; }
     if (args.taps < 1 || args.taps > kConvMaxTaps || args.kchunks < 1) { set_error("conv: bad taps/kchunks"); return AG_EINVAL; }
     static size_t configured = 0;
-    size_t smem = conv_smem_bytes(args.n);
+    const int stages = conv_stages(args.n);
+    size_t smem = conv_smem_bytes(args.n, stages);
     if (smem > 227 * 1024) { set_error("conv: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -220,7 +253,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
     int tiles = (args.m_total + kTileM - 1) / kTileM;
     int grid = tiles < sm_count() ? tiles : sm_count();
     if (grid < 1) return AG_OK;
-    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, args);
+    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, args, stages);
     AG_LAUNCH_CHECK("conv_gemm_kernel");
     return AG_OK;
 }

@@ -21,6 +21,7 @@
 // the integer work in steps 2-5 is what the kernel spends its time on.
 #include "common.cuh"
 #include "encode.cuh"
+#include "ladder.cuh"
 
 namespace ag {
 namespace enc {
@@ -91,6 +92,7 @@ struct WarpMem {
     uint32_t lanebits[LW][32];    // lane-private 361-bit scratch set, [word][lane] (conflict-free)
     uint32_t codes[N_CODE][CODE_STRIDE / 4];  // per-point plane index per feature family, 0xFF = none
     int8_t col[NPAD];
+    uint32_t ncand;               // ladder candidates queued in liblist (reused once the codes are final)
 };
 
 __device__ __forceinline__ uint32_t find_root(volatile uint32_t* label, uint32_t p) {
@@ -140,6 +142,7 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
             CODE(C_LADESC, p) = 0xFF;
         }
         for (int w = 0; w < LW; w++) W.lanebits[w][lane] = 0;
+        if (lane == 0) W.ncand = 0;
         __syncwarp();
 
         // ---- 2. union-find over same-colour edges (+x and +y direction of every stone)
@@ -261,6 +264,47 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
             CODE(C_SENSIBLE, p) = c_sens;
         }
         __syncwarp();
+
+        // ---- 5. ladder planes: queue the (move, kind) pairs that touch a prey group, then one lane per query
+        if (tab.need_ladder) {
+            uint16_t* cand = &W.liblist[0][0];  // the liberty lists are dead from here on
+            uint32_t mine[24];                  // up to 12 points per lane x 2 kinds
+            int nmine = 0;
+            for (int p = lane; p < n; p += 32) {
+                if (CODE(C_CAPTURE, p) == 0xFF) continue;  // not a legal move
+                const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
+                bool cap = false, esc = false;
+                int nb[4], k = 0;
+                if (x > 0) nb[k++] = p - size;
+                if (x < size - 1) nb[k++] = p + size;
+                if (y > 0) nb[k++] = p - 1;
+                if (y < size - 1) nb[k++] = p + 1;
+                for (int j = 0; j < k; j++) {
+                    int cq = W.col[nb[j]];
+                    if (cq == 0) continue;
+                    int libs = W.cnt[label[nb[j]]] & 0xFFFF;
+                    if (cq == -me && libs == 2) cap = true;   // adjacent opponent group with two liberties
+                    if (cq == me && libs == 1) esc = true;    // adjacent own group in atari
+                }
+                if (cap) mine[nmine++] = (uint32_t)p;
+                if (esc) mine[nmine++] = (uint32_t)p | 0x200u;
+            }
+            __syncwarp();  // every lane is done reading cnt / liblist-era state
+            for (int i = 0; i < nmine; i++) cand[atomicAdd(&W.ncand, 1u)] = (uint16_t)mine[i];
+            __syncwarp();
+            const int ncand = (int)W.ncand;
+            if (lane < ncand) {
+                LadderBoard B;
+                LadderFrame fr[kLadderDepth + 2];
+                for (int p = 0; p < NPAD; p++) B.bd[p] = p < n ? W.col[p] : 0;
+                B.size = size; B.n = n; B.player = me; B.ko = ko; B.undo_top = 0;
+                for (int i = lane; i < ncand; i += 32) {
+                    const int kind = cand[i] >> 9, a = cand[i] & 0x1FF;
+                    if (ladder_query(B, fr, kind, a)) CODE(kind ? C_LADESC : C_LADCAP, a) = 0;
+                }
+            }
+            __syncwarp();
+        }
 
         // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (code[arr][p] == val).
         // A position's planes are one contiguous run of F*n bytes: a few head bytes up to the next

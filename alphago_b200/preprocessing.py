@@ -76,11 +76,7 @@ class Preprocess(object):
         rc = _lib.lib().ag_encode(C.c_void_p(board.data_ptr()), C.c_void_p(age.data_ptr()), C.c_void_p(player.data_ptr()),
                                   C.c_void_p(ko.data_ptr()), n, size, _lib.np_ptr(self._ids), len(self._ids),
                                   C.c_void_p(out.data_ptr()), _lib.current_stream())
-        if rc != 0:
-            msg = _lib.last_error()
-            if "ladder" in msg:
-                raise NotImplementedError(msg)  # as preprocessing.py:147-152
-            raise _lib.AlphaGoB200Error("ag_encode failed (%d): %s" % (rc, msg))
+        _lib.check(rc, "ag_encode")
         return out
 
     def encode_host(self, board, age, player, ko, size, device="cuda"):

@@ -193,7 +193,8 @@ class EncodeWorkload(object):
 # ------------------------------------------------------------------------------------------ train
 TRAIN_FLOP_PER_POSITION = 8.2380e9   # fwd 2.8015 + wgrad 2.8015 + dgrad 2.6352 GFLOP (192 filters, 48 planes)
 FWD3x3_FLOP_PER_POSITION = 2 * 361 * 9 * 192 * 192  # one 3x3 192->192 layer, algorithmic (no padding flops)
-TRAIN_FEATS = FEATS46[:-1] + ["zeros", "zeros", "zeros"]  # 48 planes; the two ladder planes are zero until the ladder kernel lands
+TRAIN_FEATS = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size", "liberties_after",
+               "ladder_capture", "ladder_escape", "sensibleness", "zeros"]  # the default 48 planes (preprocessing.py:211-214)
 
 
 class TrainWorkload(object):
@@ -298,7 +299,7 @@ class TrainWorkload(object):
                             "batch %d per GPU, device-side D4 augmentation, SGD lr decay" % self.batch,
                 "per_gpu_batch": self.batch, "planes": 48,
                 "l2": "each step touches ~1 GB of activations/gradients (> 126 MB L2); dataset of %d positions rotates" % self.dataset,
-                "note": "ladder planes are zero-filled until the ladder kernel lands"}
+                "data": "planes from the CUDA encoder on random-playout positions, labels uniform over legal moves"}
 
     def cpu_baseline(self):
         import torch
@@ -359,7 +360,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=["encode", "train"])
     ap.add_argument("--positions", type=int, default=16384)
     ap.add_argument("--batch", type=int, default=256)
-    ap.add_argument("--planes", type=int, default=46, choices=[46, 48])
+    ap.add_argument("--planes", type=int, default=48, choices=[46, 48])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-encoder", action="store_true")
     args = ap.parse_args()

@@ -147,3 +147,54 @@ def test_host_buffer_path_matches_device_path():
     host = pp.encode_host(b, a, pl, ko, 19)
     assert host.dtype == np.uint8 and host.shape == (777, 46, 19, 19)
     assert_same(host, og.encode_batch(b, a, pl, ko, 19, FEATS46, threads=os.cpu_count() or 1), FEATS46)
+
+
+# ---------------------------------------------------------------- ladder planes (build-owned spec)
+LADDER = ["ladder_capture", "ladder_escape"]
+
+
+def test_ladder_planes_match_python_spec_fixture(golden_dir):
+    """planes produced by oracle/ladder_spec.py on the reference's own GameState (tests/golden/ladder_spec.npz)"""
+    g = np.load(os.path.join(golden_dir, "ladder_spec.npz"))
+    for size in (19, 9, 7):
+        sel = np.flatnonzero(g["size"] == size)
+        n = size * size
+        b = g["board"][sel][:, :n]
+        a = np.where(b != 0, 7, 255).astype(np.uint8)
+        got = gpu_encode(LADDER, b, a, g["player"][sel], g["ko"][sel], size)
+        assert np.array_equal(got[:, 0].reshape(len(sel), n), g["capture"][sel][:, :n]), size
+        assert np.array_equal(got[:, 1].reshape(len(sel), n), g["escape"][sel][:, :n]), size
+
+
+def test_ladder_known_answers():
+    def board(breaker, to_move, chased=False):
+        st = go.GameState(9)
+        for m in [(2, 1), (1, 2), (3, 1)] + ([(2, 3)] if chased else []):
+            st.do_move(m, go.BLACK)
+        st.do_move((2, 2), go.WHITE)
+        if breaker:
+            st.do_move(breaker, go.WHITE)
+        st.current_player = to_move
+        return st
+    pp = Preprocess(LADDER)
+    for breaker, works in [(None, 1), ((6, 6), 0), ((7, 6), 0), ((0, 8), 1)]:
+        st = board(breaker, go.BLACK)
+        t = pp.state_to_tensor(st)[0]
+        assert t[0][2, 3] == works and t[0][3, 2] == 0 and t[1].sum() == 0
+        if breaker is None:
+            assert t[0].sum() == 1
+        b, a, pl, ko = st.pack()  # (a lone corner stone is itself ladder-capturable: compare whole planes with the spec)
+        assert np.array_equal(t, og.encode_batch(b[None], a[None], [pl], [ko], 9, LADDER)[0])
+    for breaker, escapes in [(None, 0), ((6, 6), 1)]:
+        t = pp.state_to_tensor(board(breaker, go.WHITE, chased=True))[0]
+        assert t[1][3, 2] == escapes
+
+
+@pytest.mark.parametrize("n,size,seed", [(3000, 19, 31), (1500, 9, 32), (600, 7, 33), (500, 13, 34)])
+def test_all_48_planes_match_oracle(n, size, seed):
+    b, a, pl, ko = go.playout_positions(seed, n, size=size, max_moves=size * size + 40, per_game=8)
+    want = og.encode_batch(b, a, pl, ko, size, DEFAULT_FEATURES, threads=os.cpu_count() or 1)
+    got = gpu_encode(DEFAULT_FEATURES, b, a, pl, ko, size)
+    assert got.shape == (n, 48, size, size)
+    assert_same(got, want, DEFAULT_FEATURES)
+    assert want[:, 44].sum() > 0 and want[:, 45].sum() > 0  # the fixture exercises both planes
