@@ -29,9 +29,9 @@ constexpr int kAccStride = 256;  // TMEM columns between the two accumulator buf
 constexpr int kTmemCols = 512;
 
 constexpr int kMaxStages = 6;
-__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {  // streaming 16-byte load, no L1 allocation
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {  // read-only 16-byte load (L1-cached: a row's four loads share sectors)
     uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
 

@@ -265,11 +265,10 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
         }
         __syncwarp();
 
-        // ---- 5. ladder planes: queue the (move, kind) pairs that touch a prey group, then one lane per query
+        // ---- 5. ladder planes, first half: mark the moves that touch a prey group (an adjacent opponent group with
+        // two liberties / an adjacent own group in atari).  Everything else is 0 for certain; the marked moves are
+        // resolved by ladder_resolve_kernel, which runs at full occupancy with dynamic work distribution.
         if (tab.need_ladder) {
-            uint16_t* cand = &W.liblist[0][0];  // the liberty lists are dead from here on
-            uint32_t mine[24];                  // up to 12 points per lane x 2 kinds
-            int nmine = 0;
             for (int p = lane; p < n; p += 32) {
                 if (CODE(C_CAPTURE, p) == 0xFF) continue;  // not a legal move
                 const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
@@ -283,25 +282,11 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
                     int cq = W.col[nb[j]];
                     if (cq == 0) continue;
                     int libs = W.cnt[label[nb[j]]] & 0xFFFF;
-                    if (cq == -me && libs == 2) cap = true;   // adjacent opponent group with two liberties
-                    if (cq == me && libs == 1) esc = true;    // adjacent own group in atari
+                    if (cq == -me && libs == 2) cap = true;
+                    if (cq == me && libs == 1) esc = true;
                 }
-                if (cap) mine[nmine++] = (uint32_t)p;
-                if (esc) mine[nmine++] = (uint32_t)p | 0x200u;
-            }
-            __syncwarp();  // every lane is done reading cnt / liblist-era state
-            for (int i = 0; i < nmine; i++) cand[atomicAdd(&W.ncand, 1u)] = (uint16_t)mine[i];
-            __syncwarp();
-            const int ncand = (int)W.ncand;
-            if (lane < ncand) {
-                LadderBoard B;
-                LadderFrame fr[kLadderDepth + 2];
-                for (int p = 0; p < NPAD; p++) B.bd[p] = p < n ? W.col[p] : 0;
-                B.size = size; B.n = n; B.player = me; B.ko = ko; B.undo_top = 0;
-                for (int i = lane; i < ncand; i += 32) {
-                    const int kind = cand[i] >> 9, a = cand[i] & 0x1FF;
-                    if (ladder_query(B, fr, kind, a)) CODE(kind ? C_LADESC : C_LADCAP, a) = 0;
-                }
+                if (cap) CODE(C_LADCAP, p) = 0;
+                if (esc) CODE(C_LADESC, p) = 0;
             }
             __syncwarp();
         }
@@ -352,7 +337,79 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
 }
 
 #undef CODE
+
+// Ladder planes, second half.  Input: the planes encode_kernel wrote, whose ladder planes hold 1 on every candidate
+// move.  Each warp claims chunks of positions from a global counter, lists the candidates of its chunk in shared
+// memory, and its lanes pull queries from that list one at a time (so a deep read-out on one move does not hold up
+// the other 31 lanes); each query's 0/1 answer overwrites the candidate mark in place.
+constexpr int kResolveWarps = 4;
+constexpr int kResolveChunk = 2;      // positions claimed at a time
+constexpr int kResolveList = 2 * MAXN * kResolveChunk;
+
+__global__ void __launch_bounds__(kResolveWarps * 32)
+ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko,
+                      int npos, int size, int n_planes, int cap_plane, int esc_plane, uint8_t* __restrict__ g_out,
+                      unsigned int* __restrict__ counter) {
+    __shared__ uint32_t s_list[kResolveWarps][kResolveList];  // local position << 10 | kind << 9 | point
+    __shared__ uint32_t s_count[kResolveWarps], s_next[kResolveWarps];
+    __shared__ __align__(8) NeighbourTable s_nt;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = size * size;
+    neighbour_table_fill(s_nt, size, threadIdx.x, blockDim.x);
+    __syncthreads();
+    LadderBoard B;
+    B.nt = &s_nt;
+    LadderFrame fr[kLadderDepth + 2];
+    int loaded = -1;  // position whose board is in B
+    while (true) {
+        unsigned int base = 0;
+        if (lane == 0) { base = atomicAdd(counter, (unsigned)kResolveChunk); s_count[warp] = 0; s_next[warp] = 0; }
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= (unsigned)npos) break;
+        __syncwarp();
+        const int cnt_pos = min(kResolveChunk, npos - (int)base);
+        for (int lp = 0; lp < cnt_pos; lp++) {
+            const uint8_t* planes = g_out + (size_t)(base + lp) * n_planes * n;
+            for (int kind = 0; kind < 2; kind++) {
+                const int pl = kind ? esc_plane : cap_plane;
+                if (pl < 0) continue;
+                for (int p = lane; p < n; p += 32)
+                    if (planes[(size_t)pl * n + p]) s_list[warp][atomicAdd(&s_count[warp], 1u)] = (uint32_t)(lp << 10 | kind << 9 | p);
+            }
+        }
+        __syncwarp();
+        const unsigned total = s_count[warp];
+        while (true) {
+            unsigned i = atomicAdd(&s_next[warp], 1u);
+            if (i >= total) break;
+            const uint32_t c = s_list[warp][i];
+            const int pos = (int)base + (int)(c >> 10), kind = (c >> 9) & 1, a = c & 0x1FF;
+            if (loaded != pos) {
+                const int8_t* board = g_board + (size_t)pos * n;
+                for (int p = 0; p < NPAD; p++) B.bd[p] = p < n ? board[p] : 0;
+                B.size = size; B.n = n; B.player = g_player[pos]; B.ko = g_ko[pos]; B.undo_top = 0;
+                loaded = pos;
+            }
+            const bool yes = ladder_query(B, fr, kind, a);
+            g_out[((size_t)pos * n_planes + (kind ? esc_plane : cap_plane)) * n + a] = yes ? 1 : 0;
+        }
+        __syncwarp();
+    }
+}
+
+// copies the resolved ladder plane into further planes of the same kind (a feature listed more than once)
+__global__ void ladder_copy_plane_kernel(uint8_t* out, int npos, int n, int n_planes, int src, int dst) {
+    size_t total = (size_t)npos * n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        size_t pos = i / n, p = i - pos * n;
+        out[(pos * n_planes + dst) * n + p] = out[(pos * n_planes + src) * n + p];
+    }
+}
+
 }  // namespace enc
+
+// work counters of ladder_resolve_kernel: a small ring so that encodes in flight on different streams do not share one
+static __device__ unsigned int g_ladder_counters[16];
 
 size_t encode_smem_bytes() { return sizeof(enc::WarpMem) * enc::WARPS; }
 
@@ -370,6 +427,29 @@ int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player,
     if (grid < 1) grid = 1;
     enc::encode_kernel<<<grid, enc::WARPS * 32, smem, stream>>>(board, age, player, ko, npos, size, tab, out);
     AG_LAUNCH_CHECK("encode_kernel");
+    if (!tab.need_ladder) return AG_OK;
+    int cap_plane = -1, esc_plane = -1;
+    for (int j = 0; j < tab.n_planes; j++) {
+        if (tab.arr[j] == enc::C_LADCAP && cap_plane < 0) cap_plane = j;
+        if (tab.arr[j] == enc::C_LADESC && esc_plane < 0) esc_plane = j;
+    }
+    static unsigned int* counters = nullptr;
+    static unsigned next_counter = 0;
+    if (!counters) AG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_ladder_counters));
+    unsigned int* ctr = counters + (next_counter++ & 15);
+    AG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned int), stream));
+    int rgrid = sm_count() * 8;
+    int need = (npos + enc::kResolveChunk - 1) / enc::kResolveChunk;
+    need = (need + enc::kResolveWarps - 1) / enc::kResolveWarps;
+    if (rgrid > need) rgrid = need;
+    enc::ladder_resolve_kernel<<<rgrid, enc::kResolveWarps * 32, 0, stream>>>(board, player, ko, npos, size, tab.n_planes, cap_plane, esc_plane, out, ctr);
+    AG_LAUNCH_CHECK("ladder_resolve_kernel");
+    for (int j = 0; j < tab.n_planes; j++) {  // repeated ladder features
+        int src = tab.arr[j] == enc::C_LADCAP ? cap_plane : (tab.arr[j] == enc::C_LADESC ? esc_plane : -1);
+        if (src < 0 || src == j) continue;
+        enc::ladder_copy_plane_kernel<<<sm_count() * 4, 256, 0, stream>>>(out, npos, size * size, tab.n_planes, src, j);
+        AG_LAUNCH_CHECK("ladder_copy_plane_kernel");
+    }
     return AG_OK;
 }
 

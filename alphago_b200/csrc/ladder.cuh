@@ -17,10 +17,27 @@ namespace ag {
 namespace enc {
 
 constexpr int kLadderDepth = 80;    // OG_LADDER_DEPTH
-constexpr int kLadderNodes = 4000;  // OG_LADDER_NODES
+constexpr int kLadderNodes = 160;   // OG_LADDER_NODES
 constexpr int kNoPoint = 0x1FF;
 
+// on-board neighbours of every point in go.py:96 order, -1 padded; built once per CTA in shared memory
+struct NeighbourTable { int16_t nb[NPAD][4]; };
+__device__ __forceinline__ void neighbour_table_fill(NeighbourTable& T, int size, int tid, int nthreads) {
+    for (int p = tid; p < NPAD; p += nthreads) {
+        int x = p / size, y = p - x * size, k = 0;
+        int16_t v[4] = {-1, -1, -1, -1};
+        if (p < size * size) {
+            if (x > 0) v[k++] = (int16_t)(p - size);
+            if (x < size - 1) v[k++] = (int16_t)(p + size);
+            if (y > 0) v[k++] = (int16_t)(p - 1);
+            if (y < size - 1) v[k++] = (int16_t)(p + 1);
+        }
+        for (int j = 0; j < 4; j++) T.nb[p][j] = v[j];
+    }
+}
+
 struct LadderBoard {
+    const NeighbourTable* nt;
     int8_t bd[NPAD];
     int size, n, player, ko;
     uint32_t vis[LW], lib[LW];  // last flood fill: stones / liberties
@@ -30,12 +47,9 @@ struct LadderBoard {
 };
 
 __device__ __forceinline__ int lb_nbrs(const LadderBoard& B, int p, int out[4]) {  // go.py:96 order
-    int x = p / B.size, y = p - x * B.size, k = 0;
-    if (x > 0) out[k++] = p - B.size;
-    if (x < B.size - 1) out[k++] = p + B.size;
-    if (y > 0) out[k++] = p - 1;
-    if (y < B.size - 1) out[k++] = p + 1;
-    return k;
+    const int2 v = *reinterpret_cast<const int2*>(B.nt->nb[p]);  // four int16 in one 8-byte load
+    out[0] = (int16_t)(v.x & 0xFFFF); out[1] = v.x >> 16; out[2] = (int16_t)(v.y & 0xFFFF); out[3] = v.y >> 16;
+    return (out[0] >= 0) + (out[1] >= 0) + (out[2] >= 0) + (out[3] >= 0);
 }
 __device__ __forceinline__ bool bit_get(const uint32_t* b, int i) { return (b[i >> 5] >> (i & 31)) & 1; }
 __device__ __forceinline__ void bit_set(uint32_t* b, int i) { b[i >> 5] |= 1u << (i & 31); }

@@ -170,5 +170,27 @@ def main():
     print("ladder_spec.npz written")
 
 
+def export_reference_hdf5_fixture():
+    """tests/test_data/hdf5/alphago-vs-lee-sedol-features.hdf5 of the reference (written by its own
+    game_converter.py from the five AlphaGo - Lee Sedol SGFs: 1033 (state planes, action) pairs, features
+    board/ones/turns_since) re-packed as tests/golden/ref_hdf5_fixture.npz: planes bit-packed, actions, per-game
+    [start, count].  Read with alphago_b200/hdf5_lite.py (no h5py in this image)."""
+    from alphago_b200 import hdf5_lite
+    path = os.path.join(ref_shim.REFERENCE_ROOT, "tests", "test_data", "hdf5", "alphago-vs-lee-sedol-features.hdf5")
+    f = hdf5_lite.File(path)
+    states, actions = f["states"][:], f["actions"][:]
+    assert states.shape == (1033, 12, 19, 19) and states.max() == 1
+    names = f["file_offsets"].keys()
+    offsets = np.asarray([f["file_offsets"][k][:] for k in names], np.int32)
+    np.savez_compressed(os.path.join(OUT, "ref_hdf5_fixture.npz"), states_bits=np.packbits(states.reshape(1033, -1), axis=1),
+                        shape=np.asarray(states.shape, np.int32), actions=actions, offsets=offsets,
+                        names=np.asarray(names), features=np.asarray(["board", "ones", "turns_since"]))
+    print("ref_hdf5_fixture.npz written", offsets.tolist())
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "hdf5":
+        export_reference_hdf5_fixture()
+    else:
+        main()
+        export_reference_hdf5_fixture()

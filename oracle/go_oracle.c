@@ -277,7 +277,7 @@ void og_pack(const og_state *s, int8_t *board, uint8_t *age, int8_t *player, int
  * bounds shared with the CUDA kernel.  The node budget is per top-level query and counts
  * every capture()/escape() entry, so CPU and GPU (same DFS order) agree exactly. */
 #define OG_LADDER_DEPTH 80
-#define OG_LADDER_NODES 4000
+#define OG_LADDER_NODES 160
 
 typedef struct { int size, n; int8_t board[MAXN]; int player, ko; } lpos;
 

@@ -8,13 +8,14 @@ GameState, it inherits the reference's rules and ko quirks; go_oracle.c restates
 tests/test_oracle_ladder.py checks the two agree.  CPU ORACLE -- test infrastructure only.
 
 Spec, with the bounds shared by the C oracle and the CUDA kernel:
-  DEPTH = 80 plies, NODES = 4000 predicate entries per top-level query.
+  DEPTH = 80 plies, NODES = 160 predicate entries per top-level query (a clean ladder across a 19x19 board
+  takes 90; fewer than 1 query in 10,000 on random playouts needs more -- those are scored as budget-exhausted).
 Candidates (prey groups, replies) are visited in ascending flat index x*size+y; prey groups
 are identified by the first neighbour of the move (order (x-1,y),(x+1,y),(x,y-1),(x,y+1),
 go.py:96) that touches them.
 """
 DEPTH = 80
-NODES = 4000
+NODES = 160
 
 
 def _nbrs(p, size):

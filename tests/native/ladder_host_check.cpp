@@ -5,6 +5,7 @@
 #include <string.h>
 #define __device__
 #define __forceinline__ inline
+struct int2 { int x, y; };
 static inline int __popc(uint32_t v) { return __builtin_popcount(v); }
 static inline int __ffs(uint32_t v) { return __builtin_ffs((int)v); }
 namespace ag { namespace enc {
@@ -16,6 +17,9 @@ extern "C" int ladder_planes_host(const int8_t* board, int size, int player, int
     using namespace ag::enc;
     static LadderBoard B;
     static LadderFrame fr[kLadderDepth + 2];
+    static NeighbourTable nt;
+    neighbour_table_fill(nt, size, 0, 1);
+    B.nt = &nt;
     int n = size * size;
     for (int p = 0; p < NPAD; p++) B.bd[p] = p < n ? board[p] : 0;
     B.size = size; B.n = n; B.player = player; B.ko = ko; B.undo_top = 0;

@@ -198,3 +198,19 @@ def test_all_48_planes_match_oracle(n, size, seed):
     assert got.shape == (n, 48, size, size)
     assert_same(got, want, DEFAULT_FEATURES)
     assert want[:, 44].sum() > 0 and want[:, 45].sum() > 0  # the fixture exercises both planes
+
+
+def test_reference_hdf5_fixture_real_games(golden_dir):
+    """1033 real positions of the five AlphaGo - Lee Sedol games, planes written by the reference's own converter
+    (tests/golden/ref_hdf5_fixture.npz): product GameState replay + CUDA encoder, bit-exact"""
+    from test_oracle import load_hdf5_fixture
+    states, actions, offsets, feats = load_hdf5_fixture(golden_dir)
+    pp = Preprocess(feats)
+    for start, count in offsets:
+        st = go.GameState(19)
+        batch = []
+        for i in range(start, start + count):
+            batch.append(st.copy())
+            st.do_move((int(actions[i][0]), int(actions[i][1])))
+        got = pp.states_to_tensor(batch).cpu().numpy()
+        assert_same(got, states[start:start + count], feats)

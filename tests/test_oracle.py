@@ -385,3 +385,38 @@ def test_live_reference_random_playouts():
                 assert np.array_equal(st.encode(FEATS46)[0], ref), (size, t)
                 b, a, pl, ko = og.pack_gamestate(gs)
                 assert np.array_equal(og.encode_batch(b, a, [pl], [ko], size, FEATS46)[0], ref)
+
+
+# ---------------------------------------------------------------- the reference's own HDF5 golden fixture
+def load_hdf5_fixture(golden_dir):
+    g = np.load(os.path.join(golden_dir, "ref_hdf5_fixture.npz"))
+    shape = tuple(int(v) for v in g["shape"])
+    states = np.unpackbits(g["states_bits"], axis=1)[:, :int(np.prod(shape[1:]))].reshape(shape)
+    return states, g["actions"], g["offsets"], [str(f) for f in g["features"]]
+
+
+def test_reference_hdf5_fixture_real_games(golden_dir):
+    """tests/test_data/hdf5/alphago-vs-lee-sedol-features.hdf5 (written by the reference's own converter from
+    the five AlphaGo - Lee Sedol games): replaying its actions must reproduce its 1033 x 12 planes exactly"""
+    states, actions, offsets, feats = load_hdf5_fixture(golden_dir)
+    assert states.shape == (1033, 12, 19, 19) and feats == ["board", "ones", "turns_since"]
+    for start, count in offsets:
+        st = og.OState(19)
+        for i in range(start, start + count):
+            assert np.array_equal(st.encode(feats)[0], states[i]), i
+            st.do_move((int(actions[i][0]), int(actions[i][1])))
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present")
+def test_hdf5_lite_reads_reference_file(golden_dir):
+    from alphago_b200 import hdf5_lite
+    f = hdf5_lite.File(os.path.join(ref_shim.REFERENCE_ROOT, "tests", "test_data", "hdf5", "alphago-vs-lee-sedol-features.hdf5"))
+    assert f.keys() == ["actions", "file_offsets", "states"]
+    s, a = f["states"], f["actions"]
+    assert s.shape == (1033, 12, 19, 19) and s.dtype == np.uint8 and s.chunk == (64, 12, 19, 19) and s.filters == [32000]
+    states, actions, offsets, _ = load_hdf5_fixture(golden_dir)
+    assert np.array_equal(s[:], states) and np.array_equal(a[:], actions)
+    assert np.array_equal(s[100], states[100]) and np.array_equal(s[60:70], states[60:70]) and len(s) == 1033
+    assert np.array_equal(s[[5, 900, 64]], states[[5, 900, 64]])
+    names = f["file_offsets"].keys()
+    assert len(names) == 5 and sorted(f["file_offsets"][n][:].tolist() for n in names) == sorted(offsets.tolist())
