@@ -194,6 +194,163 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
 }
 
+// ---- CTA-pair variant: one UMMA of M = 256 per cluster of two CTAs (cta_group::2).  Each CTA stages its own 128 pixel
+// rows of A and HALF of the weight slice (N/2 rows); the tensor cores of both SMs read the two halves of B from each
+// other's shared memory, so per output row the B traffic through shared memory halves.  The leader CTA owns the
+// smem-full and accumulator-empty barriers and issues the UMMAs; commits are multicast to both CTAs.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_bh, const ConvArgs p,
+                      const int kStages) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    const int half_n = p.n / 2;
+    const int b_bytes = half_n * 128;
+    const int stage_bytes = kABytes + b_bytes;
+    ConvBarriers* bars = reinterpret_cast<ConvBarriers*>(base + kStages * stage_bytes);
+    float* s_bias = reinterpret_cast<float*>(bars + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int n_pairs = (p.m_total + 2 * kTileM - 1) / (2 * kTileM);
+    const int n_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
+    const int kblocks = p.taps * p.kchunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 256); }
+        tc::fence_mbar_init();
+        tc::tma_prefetch_desc(&tmap_a);
+        tc::tma_prefetch_desc(&tmap_bh);
+    }
+    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
+    if (warp == 1) tc::tmem_alloc_pair(&bars->tmem_base, kTmemCols);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // both CTAs' barriers exist before anyone signals across the pair
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int pair = cluster_id; pair < n_pairs; pair += n_clusters) {
+                const int m0 = pair * 2 * kTileM + (int)rank * kTileM;
+                for (int t = 0; t < p.taps; t++) {
+                    const int arow = m0 + p.off[t];
+                    for (int kc = 0; kc < p.kchunks; kc++) {
+                        tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                        uint8_t* sa = base + stage * stage_bytes;
+                        if (leader) tc::mbar_expect_tx(&bars->full[stage], (uint32_t)(2 * stage_bytes));
+                        tc::tma_load_2d_pair(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
+                        tc::tma_load_2d_pair(sa + kABytes, &tmap_bh, &bars->full[stage], kc * 64, t * p.b_tap_rows + (int)rank * half_n);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            const uint32_t idesc = tc::idesc_bf16(2 * kTileM, p.n, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
+                const int buf = it & 1;
+                tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t d_tmem = tmem_base + buf * kAccStride;
+                for (int kb = 0; kb < kblocks; kb++) {
+                    tc::mbar_wait(&bars->full[stage], phase);
+                    tc::fence_after_sync();
+                    const uint32_t sa = tc::smem_u32(base + stage * stage_bytes);
+                    const uint64_t adesc = tc::desc_kmajor_sw128(sa);
+                    const uint64_t bdesc = tc::desc_kmajor_sw128(sa + kABytes);
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    tc::umma_commit_pair(&bars->empty[stage]);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                tc::umma_commit_pair(&bars->acc_full[buf]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const uint32_t empty_remote0 = tc::map_to_cta(&bars->acc_empty[0], 0), empty_remote1 = tc::map_to_cta(&bars->acc_empty[1], 0);
+        int it = 0;
+        for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
+            const int buf = it & 1;
+            const int m = pair * 2 * kTileM + (int)rank * kTileM + q * 32 + lane;
+            const int img = m / p.in.img_stride;
+            const int rem = m - img * p.in.img_stride;
+            const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
+            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size;
+            const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
+            __nv_bfloat16* dst = p.out + orow * p.out_ld;
+            const __nv_bfloat16* gate = nullptr;
+            if (p.gate)
+                gate = p.gate + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * p.gate_ld;
+            uint4 gnext[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+            if (gate && valid) {
+#pragma unroll
+                for (int g = 0; g < 4; g++)
+                    if (g * 8 < p.n) gnext[g] = ld_nc_v4(gate + g * 8);
+            }
+            tc::mbar_wait(&bars->acc_full[buf], (it >> 1) & 1);
+            tc::fence_after_sync();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride;
+            for (int c0 = 0; c0 < p.n; c0 += 32) {
+                uint32_t r[32];
+                uint4 gcur[4];
+#pragma unroll
+                for (int g = 0; g < 4; g++) gcur[g] = gnext[g];
+                tc::tmem_ld32(taddr + c0, r);
+                if (gate && valid && c0 + 32 < p.n) {
+#pragma unroll
+                    for (int g = 0; g < 4; g++)
+                        if (c0 + 32 + g * 8 < p.n) gnext[g] = ld_nc_v4(gate + c0 + 32 + g * 8);
+                }
+                tc::tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int g = 0; g < 4; g++) {
+                        if (c0 + g * 8 < p.n) {
+                            float v[8];
+#pragma unroll
+                            for (int j = 0; j < 8; j++) v[j] = __uint_as_float(r[g * 8 + j]) + s_bias[c0 + g * 8 + j];
+                            if (p.relu) {
+#pragma unroll
+                                for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
+                            }
+                            if (gate) {
+                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gcur[g]);
+#pragma unroll
+                                for (int j = 0; j < 8; j++) v[j] = __bfloat162float(gb[j]) > 0.f ? v[j] : 0.f;
+                            }
+                            uint4 o;
+                            __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                            for (int j = 0; j < 4; j++) ob[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            *reinterpret_cast<uint4*>(dst + c0 + g * 8) = o;
+                        }
+                    }
+                }
+            }
+            tc::fence_before_sync();
+            tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // the peer's smem and barriers stay alive until the leader's last UMMA / arrival is done
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -239,9 +396,37 @@ static int conv_stages(int n) {
     return s;
 }
 
-int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvArgs& args, cudaStream_t stream) {
+static size_t conv_pair_smem_bytes(int n, int stages) { return 1024 + (size_t)stages * (kABytes + (n / 2) * 128) + sizeof(ConvBarriers) + 256 * sizeof(float); }
+
+static bool conv_pair_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("AG_CONV_PAIR"); on = e ? atoi(e) : 1; }
+    return on != 0;
+}
+
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const ConvArgs& args,
+                     cudaStream_t stream) {
     if (args.n < 16 || args.n > 256 || args.n % 16 != 0) { set_error("conv: N=%d must be a multiple of 16 in [16,256]", args.n); return AG_EINVAL; }
     if (args.taps < 1 || args.taps > kConvMaxTaps || args.kchunks < 1) { set_error("conv: bad taps/kchunks"); return AG_EINVAL; }
+    const int tiles = (args.m_total + kTileM - 1) / kTileM;
+    if (tiles < 1) return AG_OK;
+    // CTA pairs: N/2 rows of weights per CTA must be whole 8-row swizzle groups, and there must be work for a pair
+    if (tmap_b_half && conv_pair_enabled() && args.n % 32 == 0 && tiles >= 2) {
+        static size_t configured2 = 0;
+        int stages = kMaxStages;
+        while (stages > 2 && conv_pair_smem_bytes(args.n, stages) > 227 * 1024) stages--;
+        size_t smem = conv_pair_smem_bytes(args.n, stages);
+        if (smem > configured2) {
+            AG_CUDA(cudaFuncSetAttribute(conv_gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured2 = smem;
+        }
+        int pairs = (tiles + 1) / 2;
+        int clusters = sm_count() / 2;
+        if (clusters > pairs) clusters = pairs;
+        conv_gemm_pair_kernel<<<2 * clusters, kThreads, smem, stream>>>(tmap_a, *tmap_b_half, args, stages);
+        AG_LAUNCH_CHECK("conv_gemm_pair_kernel");
+        return AG_OK;
+    }
     static size_t configured = 0;
     const int stages = conv_stages(args.n);
     size_t smem = conv_smem_bytes(args.n, stages);
@@ -250,9 +435,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         AG_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    int tiles = (args.m_total + kTileM - 1) / kTileM;
     int grid = tiles < sm_count() ? tiles : sm_count();
-    if (grid < 1) return AG_OK;
     conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, args, stages);
     AG_LAUNCH_CHECK("conv_gemm_kernel");
     return AG_OK;

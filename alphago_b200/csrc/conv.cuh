@@ -44,6 +44,8 @@ struct ConvArgs {
 int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows);
 
 // D[m, :] = sum_t sum_k A[m + off[t], k] * B[t][:, k]   (+bias, ReLU / gate), bf16 in, fp32 accumulate
-int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvArgs& args, cudaStream_t stream);
+// tmap_b_half (optional): the same B tensor with a box of N/2 rows; when given (and N % 32 == 0) the CTA-pair kernel runs
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const ConvArgs& args,
+                     cudaStream_t stream);
 
 }  // namespace ag
