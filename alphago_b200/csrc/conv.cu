@@ -53,7 +53,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     ConvBarriers* bars = reinterpret_cast<ConvBarriers*>(base + kStages * stage_bytes);
     float* s_bias = reinterpret_cast<float*>(bars + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
     const int n_tiles = (p.m_total + kTileM - 1) / kTileM;
     const int kblocks = p.taps * p.kchunks;
 
@@ -72,40 +72,44 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == 0) {
-        // ===== TMA producer
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int m0 = tile * kTileM;
-                for (int t = 0; t < p.taps; t++) {
-                    const int arow = m0 + p.off[t];
-                    for (int kc = 0; kc < p.kchunks; kc++) {
-                        tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+        // ===== TMA producer: the whole warp walks the loop (uniform control flow), one elected lane issues
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int m0 = tile * kTileM;
+            for (int t = 0; t < p.taps; t++) {
+                const int arow = m0 + p.off[t];
+                for (int kc = 0; kc < p.kchunks; kc++) {
+                    tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                    if (tc::elect_one()) {
                         uint8_t* sa = base + stage * stage_bytes;
-                        tc::mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
-                        tc::tma_load_2d(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
-                        tc::tma_load_2d(sa + kABytes, &tmap_b, &bars->full[stage], kc * 64, t * p.b_tap_rows);
-                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        const uint32_t tx = ((p.debug & 1) ? 0 : kABytes) + ((p.debug & 2) ? 0 : b_bytes);
+                        if (tx) tc::mbar_expect_tx(&bars->full[stage], tx); else tc::mbar_arrive(&bars->full[stage]);
+                        if (!(p.debug & 1)) tc::tma_load_2d(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
+                        if (!(p.debug & 2)) tc::tma_load_2d(sa + kABytes, &tmap_b, &bars->full[stage], kc * 64, t * p.b_tap_rows);
                     }
+                    __syncwarp();
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== UMMA issuer
-        if (lane == 0) {
-            const uint32_t idesc = tc::idesc_bf16(kTileM, p.n, 0, 0);
-            int stage = 0;
-            uint32_t phase = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
-                const int buf = it & 1;
-                tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        // ===== UMMA issuer: warp-wide loop, the UMMAs and commits come from one elected lane (keeps every operand
+        // in uniform registers: a divergent single-lane loop makes the compiler wrap each UMMA in a uniformity loop)
+        const uint32_t idesc = tc::idesc_bf16(kTileM, p.n, 0, 0);
+        int stage = 0;
+        uint32_t phase = 0;
+        int it = 0;
+        bool ready = false;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+            const int buf = it & 1;
+            tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+            tc::fence_after_sync();
+            const uint32_t d_tmem = tmem_base + buf * kAccStride;
+            for (int kb = 0; kb < kblocks; kb++) {
+                if (!ready) tc::mbar_wait(&bars->full[stage], phase);
                 tc::fence_after_sync();
-                const uint32_t d_tmem = tmem_base + buf * kAccStride;
-                for (int kb = 0; kb < kblocks; kb++) {
-                    tc::mbar_wait(&bars->full[stage], phase);
-                    tc::fence_after_sync();
+                if (tc::elect_one()) {
                     const uint32_t sa = tc::smem_u32(base + stage * stage_bytes);
                     const uint64_t adesc = tc::desc_kmajor_sw128(sa);
                     const uint64_t bdesc = tc::desc_kmajor_sw128(sa + kABytes);
@@ -113,9 +117,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     for (int k = 0; k < 4; k++)  // 4 x K=16 inside the 64-channel slice: +32 B each
                         tc::umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                     tc::umma_commit(&bars->empty[stage]);  // frees the smem slot when these MMAs retire
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    if (kb == kblocks - 1) tc::umma_commit(&bars->acc_full[buf]);
                 }
-                tc::umma_commit(&bars->acc_full[buf]);
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                ready = tc::mbar_try_wait(&bars->full[stage], phase);  // peek at the next slice while these UMMAs run
             }
         }
     } else {
@@ -129,7 +135,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const int img = m / p.in.img_stride;
             const int rem = m - img * p.in.img_stride;
             const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
-            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size;
+            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size && !(p.debug & 4);
             const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
             __nv_bfloat16* dst = p.out + orow * p.out_ld;
             const __nv_bfloat16* gate = nullptr;
@@ -209,7 +215,7 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     ConvBarriers* bars = reinterpret_cast<ConvBarriers*>(base + kStages * stage_bytes);
     float* s_bias = reinterpret_cast<float*>(bars + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t rank = tc::cluster_ctarank();
     const bool leader = rank == 0;
     const int n_pairs = (p.m_total + 2 * kTileM - 1) / (2 * kTileM);
@@ -232,48 +238,55 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int pair = cluster_id; pair < n_pairs; pair += n_clusters) {
-                const int m0 = pair * 2 * kTileM + (int)rank * kTileM;
-                for (int t = 0; t < p.taps; t++) {
-                    const int arow = m0 + p.off[t];
-                    for (int kc = 0; kc < p.kchunks; kc++) {
-                        tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int pair = cluster_id; pair < n_pairs; pair += n_clusters) {
+            const int m0 = pair * 2 * kTileM + (int)rank * kTileM;
+            for (int t = 0; t < p.taps; t++) {
+                const int arow = m0 + p.off[t];
+                for (int kc = 0; kc < p.kchunks; kc++) {
+                    tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                    if (tc::elect_one()) {
                         uint8_t* sa = base + stage * stage_bytes;
-                        if (leader) tc::mbar_expect_tx(&bars->full[stage], (uint32_t)(2 * stage_bytes));
-                        tc::tma_load_2d_pair(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
-                        tc::tma_load_2d_pair(sa + kABytes, &tmap_bh, &bars->full[stage], kc * 64, t * p.b_tap_rows + (int)rank * half_n);
-                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        const uint32_t tx = ((p.debug & 1) ? 0 : kABytes) + ((p.debug & 2) ? 0 : b_bytes);
+                        if (leader) { if (tx) tc::mbar_expect_tx(&bars->full[stage], 2 * tx); else tc::mbar_arrive(&bars->full[stage]); }
+                        if (!(p.debug & 1)) tc::tma_load_2d_pair(sa, &tmap_a, &bars->full[stage], kc * 64, arow);
+                        if (!(p.debug & 2)) tc::tma_load_2d_pair(sa + kABytes, &tmap_bh, &bars->full[stage], kc * 64, t * p.b_tap_rows + (int)rank * half_n);
                     }
+                    __syncwarp();
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
+        if (leader) {
             const uint32_t idesc = tc::idesc_bf16(2 * kTileM, p.n, 0, 0);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
+            bool ready = false;
             for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
                 const int buf = it & 1;
                 tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
                 tc::fence_after_sync();
                 const uint32_t d_tmem = tmem_base + buf * kAccStride;
                 for (int kb = 0; kb < kblocks; kb++) {
-                    tc::mbar_wait(&bars->full[stage], phase);
+                    if (!ready) tc::mbar_wait(&bars->full[stage], phase);
                     tc::fence_after_sync();
-                    const uint32_t sa = tc::smem_u32(base + stage * stage_bytes);
-                    const uint64_t adesc = tc::desc_kmajor_sw128(sa);
-                    const uint64_t bdesc = tc::desc_kmajor_sw128(sa + kABytes);
+                    if (tc::elect_one()) {
+                        const uint32_t sa = tc::smem_u32(base + stage * stage_bytes);
+                        const uint64_t adesc = tc::desc_kmajor_sw128(sa);
+                        const uint64_t bdesc = tc::desc_kmajor_sw128(sa + kABytes);
 #pragma unroll
-                    for (int k = 0; k < 4; k++)
-                        tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    tc::umma_commit_pair(&bars->empty[stage]);
+                        for (int k = 0; k < 4; k++)
+                            tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        tc::umma_commit_pair(&bars->empty[stage]);
+                        if (kb == kblocks - 1) tc::umma_commit_pair(&bars->acc_full[buf]);
+                    }
+                    __syncwarp();
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    ready = tc::mbar_try_wait(&bars->full[stage], phase);
                 }
-                tc::umma_commit_pair(&bars->acc_full[buf]);
             }
         }
     } else {
@@ -286,7 +299,7 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
             const int img = m / p.in.img_stride;
             const int rem = m - img * p.in.img_stride;
             const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
-            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size;
+            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size && !(p.debug & 4);
             const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
             __nv_bfloat16* dst = p.out + orow * p.out_ld;
             const __nv_bfloat16* gate = nullptr;
@@ -408,6 +421,10 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
                      cudaStream_t stream) {
     if (args.n < 16 || args.n > 256 || args.n % 16 != 0) { set_error("conv: N=%d must be a multiple of 16 in [16,256]", args.n); return AG_EINVAL; }
     if (args.taps < 1 || args.taps > kConvMaxTaps || args.kchunks < 1) { set_error("conv: bad taps/kchunks"); return AG_EINVAL; }
+    static int debug = -1;
+    if (debug < 0) { const char* e = getenv("AG_CONV_DEBUG"); debug = e ? atoi(e) : 0; }
+    ConvArgs dargs = args;
+    dargs.debug = debug;
     const int tiles = (args.m_total + kTileM - 1) / kTileM;
     if (tiles < 1) return AG_OK;
     // CTA pairs: N/2 rows of weights per CTA must be whole 8-row swizzle groups, and there must be work for a pair
@@ -423,7 +440,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         int pairs = (tiles + 1) / 2;
         int clusters = sm_count() / 2;
         if (clusters > pairs) clusters = pairs;
-        conv_gemm_pair_kernel<<<2 * clusters, kThreads, smem, stream>>>(tmap_a, *tmap_b_half, args, stages);
+        conv_gemm_pair_kernel<<<2 * clusters, kThreads, smem, stream>>>(tmap_a, *tmap_b_half, dargs, stages);
         AG_LAUNCH_CHECK("conv_gemm_pair_kernel");
         return AG_OK;
     }
@@ -436,7 +453,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         configured = smem;
     }
     int grid = tiles < sm_count() ? tiles : sm_count();
-    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, args, stages);
+    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, dargs, stages);
     AG_LAUNCH_CHECK("conv_gemm_kernel");
     return AG_OK;
 }

@@ -37,6 +37,7 @@ struct ConvArgs {
     __nv_bfloat16* out;   // rows in dst layout, out_ld wide
     int out_ld;
     int relu;
+    int debug;            // measurement only (AG_CONV_DEBUG): 1 = skip A loads, 2 = skip B loads, 4 = skip epilogue memory traffic
 };
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no libcuda link dependency).

@@ -40,7 +40,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     const int xchunks = p.kin / 64;
     const int stage_bytes = (2 + xchunks) * kChunkBytes;
     WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
     const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const int kb_total = (p.m_total + 63) / 64;
@@ -62,21 +62,21 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // the two (tap, co-chunk) halves of this CTA's 128 dW rows
-            int shift[2], col[2];
-            bool live[2];
-            for (int h = 0; h < 2; h++) {
-                int c = tile * 2 + h;
-                live[h] = c < nchunks;
-                int t = live[h] ? c / cochunks : 0;
-                shift[h] = p.off[t];
-                col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
-            }
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kb = kb0; kb < kb1; kb++) {
-                tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+        // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
+        int shift[2], col[2];
+        bool live[2];
+        for (int h = 0; h < 2; h++) {  // the two (tap, co-chunk) halves of this CTA's 128 dW rows
+            int c = tile * 2 + h;
+            live[h] = c < nchunks;
+            int t = live[h] ? c / cochunks : 0;
+            shift[h] = p.off[t];
+            col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
+        }
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = kb0; kb < kb1; kb++) {
+            tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+            if (tc::elect_one()) {
                 uint8_t* s = base + stage * stage_bytes;
                 tc::mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
                 const int m0 = kb * 64;
@@ -84,17 +84,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     tc::tma_load_2d(s + h * kChunkBytes, &tmap_g, &bars->full[stage], col[h], live[h] ? m0 - shift[h] : 0x40000000);
                 for (int c = 0; c < xchunks; c++)
                     tc::tma_load_2d(s + (2 + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, m0);
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
+            __syncwarp();
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = tc::idesc_bf16(128, p.kin, 1, 1);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kb = kb0; kb < kb1; kb++) {
-                tc::mbar_wait(&bars->full[stage], phase);
-                tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_bf16(128, p.kin, 1, 1);
+        int stage = 0;
+        uint32_t phase = 0;
+        bool ready = false;
+        for (int kb = kb0; kb < kb1; kb++) {
+            if (!ready) tc::mbar_wait(&bars->full[stage], phase);
+            tc::fence_after_sync();
+            if (tc::elect_one()) {
                 const uint32_t s = tc::smem_u32(base + stage * stage_bytes);
                 const uint64_t adesc = tc::desc_mnmajor_sw128(s, kChunkBytes);
                 const uint64_t bdesc = tc::desc_mnmajor_sw128(s + 2 * kChunkBytes, kChunkBytes);
@@ -102,9 +104,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                 for (int k = 0; k < 4; k++)  // 16 pixel rows per UMMA: +2048 B
                     tc::umma_bf16(tmem_base, adesc + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
                 tc::umma_commit(&bars->empty[stage]);
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                if (kb == kb1 - 1) tc::umma_commit(&bars->acc_full);
             }
-            tc::umma_commit(&bars->acc_full);
+            __syncwarp();
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            ready = tc::mbar_try_wait(&bars->full[stage], phase);  // peek at the next slice while these UMMAs run
         }
     } else {
         const int q = warp & 3;
