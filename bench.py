@@ -286,8 +286,13 @@ class TrainWorkload(object):
         ach = self.batch * TRAIN_FLOP_PER_POSITION / (ms_per_step * 1e-3) / 1e12
         k = self.kernel_rooflines(pk)
         dom = k["conv_gemm_kernel(fwd 3x3)"]
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
+        if os.path.exists(tp):  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
+            traffic = next(iter(json.load(open(tp)).values()))["dram_bytes_per_launch"]
         return {"bound": "tensor", "achieved": dom["tflops"], "peak": pk["tensor_burst"], "unit": "TFLOP/s",
-                "frac": dom["frac_of_burst_peak"], "traffic": None, "kernel": "ag::conv_gemm_kernel (3x3 192->192 forward, layer 6, timed alone)",
+                "frac": dom["frac_of_burst_peak"], "traffic": traffic,
+                "kernel": "ag::conv_gemm_pair_kernel (3x3 192->192 forward, layer 6, cta_group::2, timed alone)",
                 "peak_source": pk["source"] + " (cuBLAS bf16 burst, kernel timed alone)",
                 "algorithmic_flops_per_launch": self.batch * FWD3x3_FLOP_PER_POSITION,
                 "whole_step": {"achieved": round(ach, 1), "peak": pk["tensor_sustained"], "frac": round(ach / pk["tensor_sustained"], 4),
@@ -323,31 +328,57 @@ class TrainWorkload(object):
                           "the reference's Keras 1.0/Theano 0.8 path is unavailable on this box" % (steps, bs, dt)}
 
 
-def reference_arm(args, rank):
-    """CPU implementation of the path on the host cores: the oracle port (the reference's Python
-    cannot travel to the GPU box and its Keras/Theano stack is not installable)."""
+def reference_arm(args, rank, workload):
+    """The reference arm: the reference's own CPU algorithm for the path on the host cores, same metric/config as our
+    arm.  The reference's Python (8 ms/position encoder) cannot travel to the GPU box and its Keras 1.0/Theano 0.8
+    stack is not installable, so this is the oracle port: oracle/go_oracle.c (OpenMP over all cores) for `encode`,
+    the fp32 torch-CPU restatement of the network (oracle/nn_oracle.py, all cores) for `train`.  Each step is a
+    bounded sample of the workload."""
     if rank != 0:
         return
     import numpy as np
     from oracle import go_oracle as og
     cores = os.cpu_count() or 1
-    feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
-    sample = 1024
-    b, a, pl, ko = og.playout_positions(1000, sample, size=19, max_moves=400, per_game=16)
-    for _ in range(args.warmup):
-        og.encode_batch(b[:128], a[:128], pl[:128], ko[:128], 19, feats, threads=cores)
-    t = time.time()
-    for _ in range(args.steps):
-        og.encode_batch(b, a, pl, ko, 19, feats, threads=cores)
-    dt = time.time() - t
-    v = round(args.steps * sample / dt, 1)
-    line = {"impl": "reference", "metric": EncodeWorkload.metric, "value": v, "unit": EncodeWorkload.unit, "n_gpus": args.gpus,
+    if workload == "encode":
+        feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
+        sample = 1024
+        b, a, pl, ko = og.playout_positions(1000, sample, size=19, max_moves=400, per_game=16)
+        for _ in range(args.warmup):
+            og.encode_batch(b[:128], a[:128], pl[:128], ko[:128], 19, feats, threads=cores)
+        t = time.time()
+        for _ in range(args.steps):
+            og.encode_batch(b, a, pl, ko, 19, feats, threads=cores)
+        dt = time.time() - t
+        metric, dtype = EncodeWorkload.metric, "u8"
+        cfg = {"workload": "feature-plane encoder on host cores, %d of the 16384 positions per step, %d planes" % (sample, og.output_dim(feats))}
+        how = "%d positions per step, C oracle (oracle/go_oracle.c) with OpenMP over all host cores" % sample
+    else:
+        import torch
+        from oracle import nn_oracle as no
+        torch.set_num_threads(cores)
+        sample = 16
+        params = no.make_params(48, [192] * 12, [5] + [3] * 11, seed=1)
+        rng = np.random.RandomState(0)
+        b, a, pl, ko = og.playout_positions(500, sample, size=19, max_moves=400, per_game=16)
+        x = og.encode_batch(b, a, pl, ko, 19, og.DEFAULT_FEATURES, threads=cores)
+        y = rng.randint(0, 361, sample)
+        for _ in range(args.warmup):
+            no.loss_and_grads(params, x[:2], y[:2])
+        t = time.time()
+        for _ in range(args.steps):
+            _, _, grads, _ = no.loss_and_grads(params, x, y)
+            params, _ = no.sgd_update(params, grads, 0.003)
+        dt = time.time() - t
+        metric, dtype = TrainWorkload.metric, "f32"
+        cfg = {"workload": "AlphaGo SL policy net (13 convs, 192 filters, 48 planes) training step on host cores, "
+                           "%d of the 256 positions per step" % sample}
+        how = "%d positions per step, fp32 torch-CPU restatement of the same net and SGD step, all host cores" % sample
+    v = round(args.steps * sample / dt, 2)
+    line = {"impl": "reference", "metric": metric, "value": v, "unit": "positions/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "feature-plane encoder on host cores, %d-position sample per step, %d planes" % (sample, og.output_dim(feats))},
-            "cpu_baseline": {"value": v, "unit": EncodeWorkload.unit, "cores": cores, "kind": "port",
-                             "sample": "%d positions per step, C oracle with OpenMP over all host cores" % sample},
-            "e2e": {"value": v, "unit": EncodeWorkload.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "scaling": "weak", "vs_baseline": None, "dtype": dtype, "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": v, "unit": "positions/s", "cores": cores, "kind": "port", "sample": how},
+            "e2e": {"value": v, "unit": "positions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
@@ -373,7 +404,7 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     if args.impl == "reference":
-        reference_arm(args, rank)
+        reference_arm(args, rank, workload)
         return
 
     import torch
