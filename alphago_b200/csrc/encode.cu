@@ -352,13 +352,12 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restri
                       unsigned int* __restrict__ counter) {
     __shared__ uint32_t s_list[kResolveWarps][kResolveList];  // local position << 10 | kind << 9 | point
     __shared__ uint32_t s_count[kResolveWarps], s_next[kResolveWarps];
-    __shared__ __align__(8) NeighbourTable s_nt;
+    __shared__ BoardMasks s_masks;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = size * size;
-    neighbour_table_fill(s_nt, size, threadIdx.x, blockDim.x);
+    if (threadIdx.x == 0) board_masks_fill(s_masks, size);
     __syncthreads();
     LadderBoard B;
-    B.nt = &s_nt;
     LadderFrame fr[kLadderDepth + 2];
     int loaded = -1;  // position whose board is in B
     while (true) {
@@ -385,9 +384,7 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restri
             const uint32_t c = s_list[warp][i];
             const int pos = (int)base + (int)(c >> 10), kind = (c >> 9) & 1, a = c & 0x1FF;
             if (loaded != pos) {
-                const int8_t* board = g_board + (size_t)pos * n;
-                for (int p = 0; p < NPAD; p++) B.bd[p] = p < n ? board[p] : 0;
-                B.size = size; B.n = n; B.player = g_player[pos]; B.ko = g_ko[pos]; B.undo_top = 0;
+                lb_load(B, g_board + (size_t)pos * n, size, g_player[pos], g_ko[pos], &s_masks);
                 loaded = pos;
             }
             const bool yes = ladder_query(B, fr, kind, a);
