@@ -407,6 +407,14 @@ def main():
         reference_arm(args, rank, workload)
         return
 
+    # libraries (NCCL's version banner, torchrun notices) write to stdout: keep fd 1 for the one JSON line
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
+
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
@@ -491,7 +499,7 @@ def main():
             ems = f0.elapsed_time(f1) / 50
             line["encoder"] = {"metric": ew.metric, "value": round(ew.n / (ems * 1e-3), 1), "unit": ew.unit, "ms_per_step": round(ems, 4),
                                "config": ew.config(), "roofline": ew.roofline(ems, pk)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
