@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
 // memory, and its lanes pull queries from that list one at a time (so a deep read-out on one move does not hold up
 // the other 31 lanes); each query's 0/1 answer overwrites the candidate mark in place.
 constexpr int kResolveWarps = 4;
-constexpr int kResolveChunk = 2;      // positions claimed at a time
+constexpr int kResolveChunk = 1;      // positions claimed at a time (measured: 1-2 best; the tail is a few deep read-outs)
 constexpr int kResolveList = 2 * MAXN * kResolveChunk;
 
 __global__ void __launch_bounds__(kResolveWarps * 32)
