@@ -482,7 +482,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
     net->grad_count = gcount;
     rc = dev_alloc(&net->grads, gcount);
     net->wgrad_scratch_floats = scratch;
-    if (!rc) rc = dev_alloc(&net->wgrad_scratch, scratch, false);
+    if (!rc) rc = dev_alloc(&net->wgrad_scratch, scratch + (size_t)kWgradMaxSplits * 256, false);  // + bias-column partials
     if (!rc) rc = dev_alloc(&net->x0, (size_t)max_batch * net->lay_in.img_stride * net->L[0].kin);
     if (!rc && !same_layout) rc = dev_alloc(&net->x0_grad, (size_t)max_batch * net->lay_in.img_stride * net->L[0].ldout);
     size_t gmax = 0;
@@ -734,18 +734,21 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     ConvLayer& c = net->L[layer];
     const bf16* G = (layer == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[layer & 1];
     const size_t rows = (size_t)n * c.lin.img_stride;
-    // bias gradient
-    colsum_stage1_kernel<<<net->colsum_blocks, 256, 0, st>>>(G, rows, c.ldout, net->colsum_part);
-    AG_LAUNCH_CHECK("colsum_stage1_kernel");
-    colsum_stage2_kernel<<<(c.ldout + 7) / 8, 256, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
-    AG_LAUNCH_CHECK("colsum_stage2_kernel");
     // weight gradient
     WgradArgs w;
     memset(&w, 0, sizeof(w));
     w.m_total = (int)rows; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
     w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
-    int rc = wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, st);
+    const bool fused_bias = c.kin + 16 <= 256;  // the bias gradient rides in the weight-gradient GEMM as an extra column of ones
+    w.bias_scratch = fused_bias ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
+    int rc = wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, fused_bias ? c.gb : nullptr, st);
     if (rc) return rc;
+    if (!fused_bias) {
+        colsum_stage1_kernel<<<net->colsum_blocks, 256, 0, st>>>(G, rows, c.ldout, net->colsum_part);
+        AG_LAUNCH_CHECK("colsum_stage1_kernel");
+        colsum_stage2_kernel<<<(c.ldout + 7) / 8, 256, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
+        AG_LAUNCH_CHECK("colsum_stage2_kernel");
+    }
     if (layer == 0) return AG_OK;
     // data gradient into the layer below
     ConvLayer& below = net->L[layer - 1];
@@ -832,7 +835,8 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         memset(&w, 0, sizeof(w));
         w.m_total = n * c.lin.img_stride; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
         w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
-        return wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, st);
+        w.bias_scratch = c.kin + 16 <= 256 ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
+        return wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, w.bias_scratch ? c.gb : nullptr, st);
     }
     if (mode == 1 && layer > 0 && !(layer == 1 && net->x0_grad)) {
         ConvLayer& below = net->L[layer - 1];

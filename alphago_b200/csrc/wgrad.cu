@@ -38,7 +38,10 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
     const int xchunks = p.kin / 64;
-    const int stage_bytes = (2 + xchunks) * kChunkBytes;
+    const bool with_bias = p.bias_scratch != nullptr;
+    const int tx_bytes = (2 + xchunks) * kChunkBytes;                      // what TMA brings per stage
+    const int stage_bytes = tx_bytes + (with_bias ? kChunkBytes : 0);      // + a chunk of ones: B column kin = 1 for every row
+    const int umma_n = p.kin + (with_bias ? 16 : 0);
     WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
@@ -56,6 +59,13 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         tc::tma_prefetch_desc(&tmap_x);
     }
     if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
+    if (with_bias) {  // the ones chunk of every stage (all elements equal, so the swizzle does not matter)
+        for (int s = 0; s < kStages; s++) {
+            uint32_t* ones = reinterpret_cast<uint32_t*>(base + s * stage_bytes + tx_bytes);
+            for (int i = threadIdx.x; i < kChunkBytes / 4; i += kThreads) ones[i] = 0x3F803F80u;  // bf16 1.0 x2
+        }
+        tc::fence_proxy_async();  // generic-proxy writes, read by the tensor core
+    }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -78,7 +88,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             tc::mbar_wait(&bars->empty[stage], phase ^ 1);
             if (tc::elect_one()) {
                 uint8_t* s = base + stage * stage_bytes;
-                tc::mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
+                tc::mbar_expect_tx(&bars->full[stage], (uint32_t)tx_bytes);
                 const int m0 = kb * 64;
                 for (int h = 0; h < 2; h++)  // a dead half reads far out of bounds -> zeros
                     tc::tma_load_2d(s + h * kChunkBytes, &tmap_g, &bars->full[stage], col[h], live[h] ? m0 - shift[h] : 0x40000000);
@@ -89,7 +99,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
-        const uint32_t idesc = tc::idesc_bf16(128, p.kin, 1, 1);
+        const uint32_t idesc = tc::idesc_bf16(128, umma_n, 1, 1);
         int stage = 0;
         uint32_t phase = 0;
         bool ready = false;
@@ -137,6 +147,15 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             }
         }
+        if (with_bias) {
+            // column kin of the centre tap's rows is sum_m G[m][co]: the bias gradient (warp-uniform branch: a warp's 32 rows share a chunk)
+            const int t = valid ? chunk / cochunks : -1;
+            if (t == p.taps / 2) {
+                uint32_t v[32];
+                if (kb1 > kb0) { tc::tmem_ld32(taddr + p.kin, v); tc::tmem_ld_wait(); } else v[0] = 0;
+                p.bias_scratch[(size_t)split * p.ldout + (chunk - t * cochunks) * 64 + (r & 63)] = __uint_as_float(v[0]);
+            }
+        }
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -147,7 +166,15 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
 }
 
 // dW[i] = sum_s scratch[s][i], fixed order
-__global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits) {
+__global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits,
+                                    const float* __restrict__ bias_scratch, float* __restrict__ db, int ldout) {
+    if (db && blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < ldout; c += blockDim.x) {
+            float t = 0.f;
+            for (int s = 0; s < splits; s++) t += bias_scratch[(size_t)s * ldout + c];
+            db[c] = t;
+        }
+    }
     const float4* s4 = reinterpret_cast<const float4*>(scratch);
     float4* d4 = reinterpret_cast<float4*>(dw);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count4; i += (size_t)gridDim.x * blockDim.x) {
@@ -162,7 +189,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __
 
 }  // namespace
 
-size_t wgrad_smem_bytes(int kin) { return 1024 + (size_t)kStages * (2 + kin / 64) * kChunkBytes + sizeof(WgradBarriers) + 64; }
+size_t wgrad_smem_bytes(int kin, bool with_bias) { return 1024 + (size_t)kStages * (2 + kin / 64 + (with_bias ? 1 : 0)) * kChunkBytes + sizeof(WgradBarriers) + 64; }
 
 int wgrad_plan_splits(int taps, int ldout, int m_total) {
     // CTAs = tiles * splits should fill whole waves of the SMs: one wave if that keeps >= 85 % of them busy,
@@ -180,7 +207,7 @@ int wgrad_plan_splits(int taps, int ldout, int m_total) {
     return s;
 }
 
-int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, cudaStream_t stream) {
+int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, float* db, cudaStream_t stream) {
     if (args.kin % 64 != 0 || args.kin < 64 || args.kin > 256 || args.ldout % 64 != 0) {
         set_error("wgrad: channel counts must be padded to 64 (kin=%d <= 256, ldout=%d)", args.kin, args.ldout);
         return AG_EINVAL;
@@ -189,7 +216,9 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
     args.tiles = (chunks + 1) / 2;
     if (args.splits < 1) args.splits = 1;
     static size_t configured = 0;
-    size_t smem = wgrad_smem_bytes(args.kin);
+    if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
+    if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
+    size_t smem = wgrad_smem_bytes(args.kin, args.bias_scratch != nullptr);
     if (smem > 227 * 1024) { set_error("wgrad: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -200,7 +229,7 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
     size_t count4 = (size_t)args.taps * args.ldout * args.kin / 4;
     int grid = (int)((count4 + 255) / 256);
     if (grid > sm_count() * 8) grid = sm_count() * 8;
-    wgrad_reduce_kernel<<<grid, 256, 0, stream>>>(args.scratch, dw, count4, args.splits);
+    wgrad_reduce_kernel<<<grid, 256, 0, stream>>>(args.scratch, dw, count4, args.splits, args.bias_scratch, args.bias_scratch ? db : nullptr, args.ldout);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
     return AG_OK;
 }
@@ -249,7 +278,7 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
     rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
     if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
     if (rc) return rc;
-    return ag::wgrad_launch(tg, tx, a, d_dw, (cudaStream_t)stream);
+    return ag::wgrad_launch(tg, tx, a, d_dw, nullptr, (cudaStream_t)stream);
 }
 
 }  // extern "C"
@@ -312,7 +341,7 @@ int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout,
     rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
     if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
     if (rc) return rc;
-    return ag::wgrad_launch(tg, tx, a, d_dw, (cudaStream_t)stream);
+    return ag::wgrad_launch(tg, tx, a, d_dw, nullptr, (cudaStream_t)stream);
 }
 
 }  // extern "C"

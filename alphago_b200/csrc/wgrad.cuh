@@ -19,12 +19,14 @@ struct WgradArgs {
     int splits;    // split-K factor
     int tiles;     // filled by wgrad_launch
     float* scratch;  // [splits][taps*ldout][kin] fp32
+    float* bias_scratch;  // nullptr, or [splits][ldout] fp32: column sums of G (the bias gradient) ride along as one more B column
 };
 
-size_t wgrad_smem_bytes(int kin);
+size_t wgrad_smem_bytes(int kin, bool with_bias);
 int wgrad_plan_splits(int taps, int ldout, int m_total);
 // tmap_g: G [m_total rows][ldout], tmap_x: X [m_total rows][kin], both with box [64][64] and EXACTLY
 // m_total rows (rows past the batch must read as zeros).  dw: [taps][ldout][kin] fp32.
-int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, cudaStream_t stream);
+// db (optional, needs args.bias_scratch and kin <= 240): [ldout] fp32 bias gradient = sum over all rows of G
+int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, float* db, cudaStream_t stream);
 
 }  // namespace ag

@@ -97,3 +97,42 @@ def test_value_net_surface():
     vals = v.batch_eval_state([gs, go.GameState()])
     assert len(vals) == 2 and abs(vals[0] - val) < 1e-6
     assert len(v.model.get_weights()) == 2 * 4 + 4
+
+
+def test_config0_real_positions_batch16_vs_oracle(golden_dir):
+    """BASELINE configs[0]: default 48-plane Preprocess + CNNPolicy with the reference defaults (12 layers, 128 filters)
+    on positions of the AlphaGo - Lee Sedol games (tests/test_data SGFs, via the reference's own HDF5 fixture), batch 16:
+    batch_eval_state against the CPU oracle (oracle encoder + fp32 / bf16-emulating network restatement)."""
+    from test_oracle import load_hdf5_fixture
+    _, actions, offsets, _ = load_hdf5_fixture(golden_dir)
+    policy = CNNPolicy(["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size", "liberties_after",
+                        "ladder_capture", "ladder_escape", "sensibleness", "zeros"], seed=11)
+    assert policy.preprocessor.output_dim == 48 and policy.model.filters == [128] * 12
+    w = policy.model.get_weights()
+    w[-2] = w[-2] * 40  # sharpen the random-init head so the distribution is not flat
+    policy.model.set_weights(w)
+    st = go.GameState(19)
+    states = []
+    start, count = offsets[0]
+    for i in range(start, start + 160):
+        st.do_move((int(actions[i][0]), int(actions[i][1])))
+        if i % 10 == 9:
+            states.append(st.copy())
+    assert len(states) == 16
+    got = policy.batch_eval_state(states)
+    packed = [s.pack() for s in states]
+    planes = og.encode_batch(np.stack([p[0] for p in packed]), np.stack([p[1] for p in packed]), [p[2] for p in packed],
+                             [p[3] for p in packed], 19, og.DEFAULT_FEATURES)
+    assert np.array_equal(policy.preprocessor.states_to_tensor(states).cpu().numpy(), planes)
+    params = {"convs": [(no.keras_to_xcorr(w[2 * i]), w[2 * i + 1]) for i in range(12)], "head_w": w[24].reshape(-1),
+              "head_b": w[25], "pos_bias": None}
+    em = no.forward(params, planes, emulate_bf16=True)["probs"].numpy()
+    fp = no.forward(params, planes)["probs"].numpy()
+    for k, s in enumerate(states):
+        legal = s.get_legal_moves()
+        idx = [x * 19 + y for x, y in legal]
+        for ref, tol in ((em, 1e-2), (fp, 5e-2)):
+            want = ref[k][idx] / ref[k][idx].sum()
+            have = np.asarray([p for _, p in got[k]])
+            assert [m for m, _ in got[k]] == legal
+            assert np.abs(have - want).max() <= tol * want.max(), (k, tol)
