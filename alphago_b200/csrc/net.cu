@@ -286,28 +286,46 @@ __global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restr
 
 // SGD with momentum (Keras 1.0 SGD.get_updates: v = momentum*v - lr*g; w += v), one launch per layer.
 // Refreshes the bf16 operand copies: wf [tap][co][ci] (forward) and wb [tap][ci][co] (data gradient).
-__global__ void sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, size_t count, int taps,
-                                int ldout, int kin, float lr, float momentum, float gscale, bf16* __restrict__ wf, bf16* __restrict__ wb,
-                                float* __restrict__ b, float* __restrict__ bvel, const float* __restrict__ gb, int nbias) {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count + nbias; i += (size_t)gridDim.x * blockDim.x) {
-        if (i < count) {
-            float v = momentum * vel[i] - lr * g[i] * gscale;
-            vel[i] = v;
-            float nw = w[i] + v;
+// One CTA per 32x32 (co, ci) tile of one tap: coalesced fp32 update along ci, the bf16 tile goes through shared memory
+// so the transposed copy wb is written coalesced along co as well.  ldout and kin are multiples of 64.
+__global__ void __launch_bounds__(256)
+sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, int taps, int ldout, int kin, float lr,
+                float momentum, float gscale, bf16* __restrict__ wf, bf16* __restrict__ wb, float* __restrict__ b,
+                float* __restrict__ bvel, const float* __restrict__ gb, int nbias) {
+    __shared__ bf16 tile[32][33];
+    const int tiles_ci = kin / 32, tiles_co = ldout / 32;
+    const int n_tiles = taps * tiles_co * tiles_ci;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int tidx = blockIdx.x; tidx < n_tiles; tidx += gridDim.x) {
+        const int t = tidx / (tiles_co * tiles_ci);
+        const int rem = tidx - t * tiles_co * tiles_ci;
+        const int co0 = (rem / tiles_ci) * 32, ci0 = (rem % tiles_ci) * 32;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int co = co0 + ty + 8 * k;
+            const size_t i = ((size_t)t * ldout + co) * kin + ci0 + tx;
+            float v = -lr * g[i] * gscale;
+            if (momentum != 0.f) { v += momentum * vel[i]; vel[i] = v; }  // plain SGD never touches the velocity
+            const float nw = w[i] + v;
             w[i] = nw;
-            bf16 h = __float2bfloat16(nw);
+            const bf16 h = __float2bfloat16(nw);
             wf[i] = h;
-            if (wb) {
-                int ci = (int)(i % kin);
-                size_t r = i / kin;
-                int co = (int)(r % ldout);
-                int t = (int)(r / ldout);
-                wb[((size_t)t * kin + ci) * ldout + co] = h;
+            tile[ty + 8 * k][tx] = h;
+        }
+        if (wb) {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int ci = ci0 + ty + 8 * k;
+                wb[((size_t)t * kin + ci) * ldout + co0 + tx] = tile[tx][ty + 8 * k];
             }
-        } else {
-            size_t j = i - count;
-            float v = momentum * bvel[j] - lr * gb[j] * gscale;
-            bvel[j] = v;
+            __syncthreads();
+        }
+    }
+    if (blockIdx.x == 0) {
+        for (int j = threadIdx.x; j < nbias; j += blockDim.x) {
+            float v = -lr * gb[j] * gscale;
+            if (momentum != 0.f) { v += momentum * bvel[j]; bvel[j] = v; }
             b[j] += v;
         }
     }
@@ -788,8 +806,9 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
     cudaStream_t st = (cudaStream_t)stream;
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
-        sgd_conv_kernel<<<grid_for(c.wcount + c.ldout, 256), 256, 0, st>>>(c.w, c.vw, c.gw, c.wcount, c.taps, c.ldout, c.kin, lr, momentum,
-                                                                         grad_scale, c.wf, c.wb, c.b, c.vb, c.gb, c.ldout);
+        int tiles = c.taps * (c.ldout / 32) * (c.kin / 32);
+        sgd_conv_kernel<<<tiles < sm_count() * 8 ? tiles : sm_count() * 8, 256, 0, st>>>(c.w, c.vw, c.gw, c.taps, c.ldout, c.kin, lr, momentum,
+                                                                                        grad_scale, c.wf, c.wb, c.b, c.vb, c.gb, c.ldout);
         AG_LAUNCH_CHECK("sgd_conv_kernel");
     }
     sgd_flat_kernel<<<1, 256, 0, st>>>(net->hw, net->vhw, net->g_hw, 256, lr, momentum, grad_scale);
