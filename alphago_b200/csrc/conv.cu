@@ -11,7 +11,7 @@
 // tile i+1), K streamed in 64-channel slices through a 4-stage TMA->smem ring.
 //   warp 0    TMA producer (one elected lane)
 //   warp 1    TMEM allocation + UMMA issue (one elected lane)
-//   warps 2-5 epilogue: tcgen05.ld -> bias / ReLU / ReLU-gate -> bf16 -> global (pad rows skipped)
+//   warps 2-5 epilogue: tcgen05.ld -> bias / ReLU (+bitmask) / ReLU-gate (bitmask) -> bf16 -> global (pad rows skipped)
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -42,6 +42,75 @@ struct __align__(8) ConvBarriers {
     uint64_t acc_empty[2];
     uint32_t tmem_base;
 };
+
+// Epilogue of one accumulator tile, one GEMM row per thread: tcgen05.ld -> bias / ReLU (+ its bitmask) / ReLU gate -> bf16
+// -> global.  Rows that decode to pad slots produce no output.  The gate is the forward pass's ReLU bitmask of the
+// layer below (32 bytes per row instead of the bf16 activations' 2*ld), fetched before waiting for the accumulator.
+__device__ __forceinline__ void epilogue_tile(const ConvArgs& p, const float* s_bias, const int m, const uint32_t taddr,
+                                              uint64_t* acc_full, const uint32_t parity) {
+    const int img = m / p.in.img_stride;
+    const int rem = m - img * p.in.img_stride;
+    const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
+    const bool valid = m < p.m_total && x < p.in.size && y < p.in.size && !(p.debug & 4);
+    const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
+    __nv_bfloat16* dst = p.out + orow * p.out_ld;
+    uint32_t* mrow = p.mask_out ? p.mask_out + orow * kConvMaskWords : nullptr;
+    uint32_t mk[kConvMaskWords];
+#pragma unroll
+    for (int i = 0; i < kConvMaskWords; i++) mk[i] = 0xffffffffu;
+    if (p.gate_mask && valid) {
+        const uint32_t* g = p.gate_mask + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * kConvMaskWords;
+        const uint4 lo = ld_nc_v4(g);
+        mk[0] = lo.x; mk[1] = lo.y; mk[2] = lo.z; mk[3] = lo.w;
+        if (p.n > 128) {
+            const uint4 hi = ld_nc_v4(g + 4);
+            mk[4] = hi.x; mk[5] = hi.y; mk[6] = hi.z; mk[7] = hi.w;
+        }
+    }
+    tc::mbar_wait(acc_full, parity);
+    tc::fence_after_sync();
+    for (int c0 = 0; c0 < p.n; c0 += 32) {
+        uint32_t r[32];
+        tc::tmem_ld32(taddr + c0, r);
+        const uint32_t mcur = mk[0];  // this chunk's gate word; the rest shift down (keeps the array in registers)
+#pragma unroll
+        for (int i = 0; i + 1 < kConvMaskWords; i++) mk[i] = mk[i + 1];
+        tc::tmem_ld_wait();
+        if (valid) {
+            uint32_t mbits = 0;
+#pragma unroll
+            for (int g = 0; g < 4; g++) {  // 8 channels -> one 16-byte store
+                if (c0 + g * 8 < p.n) {
+                    float v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) v[j] = __uint_as_float(r[g * 8 + j]) + s_bias[c0 + g * 8 + j];
+                    if (p.relu) {
+#pragma unroll
+                        for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; j++) v[j] = ((mcur >> (g * 8 + j)) & 1u) ? v[j] : 0.f;
+                    uint4 o;
+                    __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                    for (int j = 0; j < 4; j++) ob[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                    *reinterpret_cast<uint4*>(dst + c0 + g * 8) = o;
+                    // the mask records what was STORED (bf16 > 0), so the backward gate agrees with the activations bit for bit
+                    if (mrow) {
+                        const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const uint32_t w = ow[j] & 0x7fff7fffu;
+                            mbits |= ((w & 0xffffu) ? 1u : 0u) << (g * 8 + 2 * j);
+                            mbits |= ((w >> 16) ? 1u : 0u) << (g * 8 + 2 * j + 1);
+                        }
+                    }
+                }
+            }
+            if (mrow) mrow[c0 >> 5] = mbits;
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const ConvArgs p, const int kStages) {
@@ -130,64 +199,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         int it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
             const int buf = it & 1;
-            const int m = tile * kTileM + q * 32 + lane;
-            // decode the GEMM row into (image, x, y); pad slots produce no output
-            const int img = m / p.in.img_stride;
-            const int rem = m - img * p.in.img_stride;
-            const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
-            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size && !(p.debug & 4);
-            const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
-            __nv_bfloat16* dst = p.out + orow * p.out_ld;
-            const __nv_bfloat16* gate = nullptr;
-            if (p.gate)
-                gate = p.gate + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * p.gate_ld;
-            // the first chunk of the ReLU gate is fetched before waiting for the accumulator
-            uint4 gnext[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-            if (gate && valid) {
-#pragma unroll
-                for (int g = 0; g < 4; g++)
-                    if (g * 8 < p.n) gnext[g] = ld_nc_v4(gate + g * 8);
-            }
-            tc::mbar_wait(&bars->acc_full[buf], (it >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride;
-            for (int c0 = 0; c0 < p.n; c0 += 32) {
-                uint32_t r[32];
-                uint4 gcur[4];
-#pragma unroll
-                for (int g = 0; g < 4; g++) gcur[g] = gnext[g];
-                tc::tmem_ld32(taddr + c0, r);
-                if (gate && valid && c0 + 32 < p.n) {  // next chunk's ReLU gate: in flight while this chunk is processed
-#pragma unroll
-                    for (int g = 0; g < 4; g++)
-                        if (c0 + 32 + g * 8 < p.n) gnext[g] = ld_nc_v4(gate + c0 + 32 + g * 8);
-                }
-                tc::tmem_ld_wait();
-                if (valid) {
-#pragma unroll
-                    for (int g = 0; g < 4; g++) {  // 8 channels -> one 16-byte store
-                        if (c0 + g * 8 < p.n) {
-                            float v[8];
-#pragma unroll
-                            for (int j = 0; j < 8; j++) v[j] = __uint_as_float(r[g * 8 + j]) + s_bias[c0 + g * 8 + j];
-                            if (p.relu) {
-#pragma unroll
-                                for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
-                            }
-                            if (gate) {
-                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gcur[g]);
-#pragma unroll
-                                for (int j = 0; j < 8; j++) v[j] = __bfloat162float(gb[j]) > 0.f ? v[j] : 0.f;
-                            }
-                            uint4 o;
-                            __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-                            for (int j = 0; j < 4; j++) ob[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                            *reinterpret_cast<uint4*>(dst + c0 + g * 8) = o;
-                        }
-                    }
-                }
-            }
+            epilogue_tile(p, s_bias, tile * kTileM + q * 32 + lane, tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride,
+                          &bars->acc_full[buf], (it >> 1) & 1);
             tc::fence_before_sync();
             tc::mbar_arrive(&bars->acc_empty[buf]);
         }
@@ -295,62 +308,8 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
         int it = 0;
         for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
             const int buf = it & 1;
-            const int m = pair * 2 * kTileM + (int)rank * kTileM + q * 32 + lane;
-            const int img = m / p.in.img_stride;
-            const int rem = m - img * p.in.img_stride;
-            const int x = rem / p.in.row_stride, y = rem - x * p.in.row_stride;
-            const bool valid = m < p.m_total && x < p.in.size && y < p.in.size && !(p.debug & 4);
-            const size_t orow = (size_t)img * p.dst.img_stride + (size_t)x * p.dst.row_stride + y;
-            __nv_bfloat16* dst = p.out + orow * p.out_ld;
-            const __nv_bfloat16* gate = nullptr;
-            if (p.gate)
-                gate = p.gate + ((size_t)img * p.gate_layout.img_stride + (size_t)x * p.gate_layout.row_stride + y) * p.gate_ld;
-            uint4 gnext[4] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-            if (gate && valid) {
-#pragma unroll
-                for (int g = 0; g < 4; g++)
-                    if (g * 8 < p.n) gnext[g] = ld_nc_v4(gate + g * 8);
-            }
-            tc::mbar_wait(&bars->acc_full[buf], (it >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride;
-            for (int c0 = 0; c0 < p.n; c0 += 32) {
-                uint32_t r[32];
-                uint4 gcur[4];
-#pragma unroll
-                for (int g = 0; g < 4; g++) gcur[g] = gnext[g];
-                tc::tmem_ld32(taddr + c0, r);
-                if (gate && valid && c0 + 32 < p.n) {
-#pragma unroll
-                    for (int g = 0; g < 4; g++)
-                        if (c0 + 32 + g * 8 < p.n) gnext[g] = ld_nc_v4(gate + c0 + 32 + g * 8);
-                }
-                tc::tmem_ld_wait();
-                if (valid) {
-#pragma unroll
-                    for (int g = 0; g < 4; g++) {
-                        if (c0 + g * 8 < p.n) {
-                            float v[8];
-#pragma unroll
-                            for (int j = 0; j < 8; j++) v[j] = __uint_as_float(r[g * 8 + j]) + s_bias[c0 + g * 8 + j];
-                            if (p.relu) {
-#pragma unroll
-                                for (int j = 0; j < 8; j++) v[j] = fmaxf(v[j], 0.f);
-                            }
-                            if (gate) {
-                                const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gcur[g]);
-#pragma unroll
-                                for (int j = 0; j < 8; j++) v[j] = __bfloat162float(gb[j]) > 0.f ? v[j] : 0.f;
-                            }
-                            uint4 o;
-                            __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-                            for (int j = 0; j < 4; j++) ob[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                            *reinterpret_cast<uint4*>(dst + c0 + g * 8) = o;
-                        }
-                    }
-                }
-            }
+            epilogue_tile(p, s_bias, pair * 2 * kTileM + (int)rank * kTileM + q * 32 + lane,
+                          tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride, &bars->acc_full[buf], (it >> 1) & 1);
             tc::fence_before_sync();
             tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
         }

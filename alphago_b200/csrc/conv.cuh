@@ -21,6 +21,7 @@ struct PixelLayout {
 };
 
 constexpr int kConvMaxTaps = 25;
+constexpr int kConvMaskWords = 8;  // 256 channels / 32: one 32-byte mask row per pixel row
 
 struct ConvArgs {
     int m_total;          // rows of the A matrix the GEMM covers (= images * in.img_stride)
@@ -31,9 +32,10 @@ struct ConvArgs {
     int b_tap_rows;       // rows of the B tensor per tap (tap t's matrix starts at row t*b_tap_rows)
     PixelLayout in, dst;  // row decode of the GEMM's M index, and where the result row goes
     const float* bias;    // [n] or nullptr
-    const __nv_bfloat16* gate;  // nullptr, or rows in gate_layout, gate_ld wide: result zeroed where gate <= 0 (ReLU backward)
+    // ReLU bookkeeping as bitmasks, kConvMaskWords uint32 per pixel row (bit c%32 of word c/32 = channel c was > 0):
+    uint32_t* mask_out;         // forward (relu): written for every output row, indexed like `out` (dst layout rows); may be nullptr
+    const uint32_t* gate_mask;  // ReLU backward: nullptr, or rows in gate_layout; the result is zeroed where the bit is clear
     PixelLayout gate_layout;
-    int gate_ld;
     __nv_bfloat16* out;   // rows in dst layout, out_ld wide
     int out_ld;
     int relu;

@@ -365,6 +365,7 @@ struct ConvLayer {
     float *gw, *gb;          // slices of the flat gradient buffer
     bf16 *wf, *wb;           // bf16 operand copies (wb null for layer 0)
     bf16* act;               // output activations [max_batch*lout.img_stride][ldout]
+    uint32_t* mask;          // ReLU bitmask of `act`, kConvMaskWords words per row (written by the forward conv, read by the data gradient above)
     int off_fwd[kConvMaxTaps], off_bwd[kConvMaxTaps];
     CUtensorMap tm_in, tm_wf, tm_g, tm_wb;      // forward A / B, dgrad A / B (full-size tensors)
     CUtensorMap tm_wf_half, tm_wb_half;         // B with a box of N/2 rows, for the CTA-pair kernel
@@ -516,6 +517,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         c.wb = nullptr;
         if (!rc && l > 0) rc = dev_alloc(&c.wb, c.wcount);
         if (!rc) rc = dev_alloc(&c.act, (size_t)max_batch * c.lout.img_stride * c.ldout);
+        if (!rc) rc = dev_alloc(&c.mask, (size_t)max_batch * c.lout.img_stride * kConvMaskWords);
         c.gw = net->grads + net->grad_offsets[l];
         c.gb = c.gw + c.wcount;
         if (rc) break;
@@ -560,7 +562,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
 
 void ag_net_destroy(ag_net* net) {
     if (!net) return;
-    for (auto& c : net->L) { cudaFree(c.w); cudaFree(c.b); cudaFree(c.vw); cudaFree(c.vb); cudaFree(c.wf); cudaFree(c.wb); cudaFree(c.act); }
+    for (auto& c : net->L) { cudaFree(c.w); cudaFree(c.b); cudaFree(c.vw); cudaFree(c.vb); cudaFree(c.wf); cudaFree(c.wb); cudaFree(c.act); cudaFree(c.mask); }
     float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
                   net->head_partial, net->colsum_part, net->wgrad_scratch, net->grads};
     for (float* p : f) cudaFree(p);
@@ -686,7 +688,7 @@ static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStrea
         a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
         memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
         a.in = c.lin; a.dst = c.lout;
-        a.bias = c.b; a.gate = nullptr; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
         int rc = conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, a, st);
         if (rc) return rc;
     }
@@ -777,11 +779,11 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
     a.in = c.lout;
     a.bias = nullptr; a.relu = 0;
-    a.gate = below.act; a.gate_ld = below.ldout; a.gate_layout = below.lout;
+    a.gate_mask = below.mask; a.gate_layout = below.lout;
     a.out_ld = below.ldout; a.b_tap_rows = c.kin;
     if (layer - 1 == 0 && net->x0_grad) {
         // the first layer's G lives in the INPUT layout so its weight gradient can pair it with x0; the gate
-        // (layer-0 activations) is still read in the mid layout
+        // (layer-0 ReLU mask) is still read in the mid layout
         a.dst = net->lay_in; a.out = net->x0_grad;
     } else {
         a.dst = c.lout; a.out = net->gbuf[(layer - 1) & 1];
@@ -845,7 +847,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
         memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
         a.in = c.lin; a.dst = c.lout;
-        a.bias = c.b; a.gate = nullptr; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
         return conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, a, st);
     }
     if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
@@ -865,7 +867,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         a.n = c.nin; a.taps = c.taps; a.kchunks = c.ldout / 64;
         memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
         a.in = c.lout; a.dst = c.lout;
-        a.gate = below.act; a.gate_ld = below.ldout; a.gate_layout = below.lout;
+        a.gate_mask = below.mask; a.gate_layout = below.lout;
         a.out = net->gbuf[(layer - 1) & 1]; a.out_ld = below.ldout; a.b_tap_rows = c.kin;
         return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, a, st);
     }
