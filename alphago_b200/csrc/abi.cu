@@ -7,6 +7,8 @@
 #include <atomic>
 
 #include "../../include/alphago_b200.h"
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "encode.cuh"
 #include "host_go.hpp"
@@ -27,6 +29,12 @@ int cuda_fail(cudaError_t e, const char* what) {
     return AG_ECUDA;
 }
 void count_launch(int n) { g_launches += n; }
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("AG_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
+
 int sm_count() {
     static int n = 0;
     if (n == 0) {

@@ -43,6 +43,8 @@ __device__ __forceinline__ void d4_dest(int t, int N, int x, int y, int& i, int&
 __global__ void __launch_bounds__(256)
 augment_kernel(const uint8_t* __restrict__ states, const uint8_t* __restrict__ actions, const int64_t* __restrict__ index,
                const uint8_t* __restrict__ transform, int planes, int size, uint8_t* __restrict__ out, int32_t* __restrict__ labels) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint16_t s_src[368];
     const int b = blockIdx.x, pts = size * size;
     const int t = transform[b] & 7;
@@ -86,7 +88,7 @@ extern "C" int ag_augment(const uint8_t* d_states, const uint8_t* d_actions, con
                           int batch, int planes, int size, uint8_t* d_out, int32_t* d_labels, void* stream) {
     if (batch < 0 || planes < 1 || size < 2 || size > 19) { ag::set_error("ag_augment: bad argument"); return AG_EINVAL; }
     if (batch == 0) return AG_OK;
-    ag::augment_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(d_states, d_actions, d_index, d_transform, planes, size, d_out, d_labels);
+    ag::launch_k(ag::augment_kernel, dim3(batch), dim3(256), 0, (cudaStream_t)stream, d_states, d_actions, d_index, d_transform, planes, size, d_out, d_labels);
     AG_LAUNCH_CHECK("augment_kernel");
     return AG_OK;
 }

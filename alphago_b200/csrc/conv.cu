@@ -126,6 +126,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int n_tiles = (p.m_total + kTileM - 1) / kTileM;
     const int kblocks = p.taps * p.kchunks;
 
+    pdl_trigger();
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
         for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 128); }
@@ -133,8 +134,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tc::tma_prefetch_desc(&tmap_a);
         tc::tma_prefetch_desc(&tmap_b);
     }
-    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
     if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
+    pdl_wait();  // set-up above overlaps the previous kernel; global memory (bias included) only from here on
+    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -235,6 +237,7 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     const int n_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
     const int kblocks = p.taps * p.kchunks;
 
+    pdl_trigger();
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
         for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 256); }
@@ -242,8 +245,9 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
         tc::tma_prefetch_desc(&tmap_a);
         tc::tma_prefetch_desc(&tmap_bh);
     }
-    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
     if (warp == 1) tc::tmem_alloc_pair(&bars->tmem_base, kTmemCols);
+    pdl_wait();
+    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
     tc::fence_before_sync();
     __syncthreads();
     tc::cluster_sync_all();  // both CTAs' barriers exist before anyone signals across the pair
@@ -399,7 +403,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         int pairs = (tiles + 1) / 2;
         int clusters = sm_count() / 2;
         if (clusters > pairs) clusters = pairs;
-        conv_gemm_pair_kernel<<<2 * clusters, kThreads, smem, stream>>>(tmap_a, *tmap_b_half, dargs, stages);
+        launch_k(conv_gemm_pair_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, tmap_a, *tmap_b_half, dargs, stages);
         AG_LAUNCH_CHECK("conv_gemm_pair_kernel");
         return AG_OK;
     }
@@ -412,7 +416,7 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         configured = smem;
     }
     int grid = tiles < sm_count() ? tiles : sm_count();
-    conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmap_a, tmap_b, dargs, stages);
+    launch_k(conv_gemm_kernel, dim3(grid), dim3(kThreads), smem, stream, tmap_a, tmap_b, dargs, stages);
     AG_LAUNCH_CHECK("conv_gemm_kernel");
     return AG_OK;
 }

@@ -26,6 +26,8 @@ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 // for the first conv layer; channels >= C and pad slots stay zero (buffer zero-filled once).
 __global__ void pack_input_kernel(const uint8_t* __restrict__ planes, int n, int C, int S, PixelLayout L, int ld,
                                   bf16* __restrict__ out) {
+    pdl_trigger();
+    pdl_wait();
     // one thread per (image, point, 8-channel group): reads 8 planes' bytes, writes 16 B
     const int groups = ld / 8;
     const int pts = S * S;
@@ -61,6 +63,8 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
                    const float* __restrict__ pos_bias, float* __restrict__ probs, const int32_t* __restrict__ labels,
                    float inv_batch, bf16* __restrict__ G, float* __restrict__ partial, float* __restrict__ loss_acc,
                    float* __restrict__ dlogits_out) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float s_logit[368];
     __shared__ float s_w[256];
     __shared__ float s_red[kHeadThreads / 32];
@@ -181,6 +185,8 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
 // sums the per-image head partials [n][625] -> grads: dw[ld], db[1], dpos[pts]
 __global__ void head_reduce_kernel(const float* __restrict__ partial, int n, int ld, int pts, float* __restrict__ dw,
                                    float* __restrict__ db, float* __restrict__ dpos) {
+    pdl_trigger();
+    pdl_wait();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 256 + 1 + 368) return;
     float s = 0.f;
@@ -195,6 +201,8 @@ __global__ void __launch_bounds__(256)
 value_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float* __restrict__ w, const float* __restrict__ bias,
                   const float* __restrict__ W1, const float* __restrict__ b1, const float* __restrict__ w2,
                   const float* __restrict__ b2, int hidden, float* __restrict__ out) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float s_v[368];
     __shared__ float s_w[256];
     __shared__ float s_red[8];
@@ -238,6 +246,8 @@ value_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float
 
 // bias gradient: db[c] = sum_m G[m][c]; two deterministic stages (row slabs, then a warp per channel over the slabs)
 __global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restrict__ G, size_t rows, int ld, float* __restrict__ part) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float s[256][9];
     const int groups = ld / 8, lanes = 256 / groups;
     const int g = threadIdx.x % groups, rl = threadIdx.x / groups;
@@ -275,6 +285,8 @@ __global__ void __launch_bounds__(256) colsum_stage1_kernel(const bf16* __restri
     }
 }
 __global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restrict__ part, int nblocks, int ld, int cout, float* __restrict__ db) {
+    pdl_trigger();
+    pdl_wait();
     const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (c >= cout) return;
     float t = 0.f;
@@ -292,6 +304,8 @@ __global__ void __launch_bounds__(256)
 sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, int taps, int ldout, int kin, float lr,
                 float momentum, float gscale, bf16* __restrict__ wf, bf16* __restrict__ wb, float* __restrict__ b,
                 float* __restrict__ bvel, const float* __restrict__ gb, int nbias) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ bf16 tile[32][33];
     const int tiles_ci = kin / 32, tiles_co = ldout / 32;
     const int n_tiles = taps * tiles_co * tiles_ci;
@@ -332,6 +346,8 @@ sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __r
 }
 __global__ void sgd_flat_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, size_t count, float lr,
                                 float momentum, float gscale) {
+    pdl_trigger();
+    pdl_wait();
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
         float v = momentum * vel[i] - lr * g[i] * gscale;
         vel[i] = v;
@@ -678,7 +694,7 @@ static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStrea
     const int S = net->board;
     ConvLayer& c0 = net->L[0];
     size_t work = (size_t)n * S * S * (c0.kin / 8);
-    pack_input_kernel<<<grid_for(work, 256), 256, 0, st>>>(d_planes, n, net->in_planes, S, net->lay_in, c0.kin, net->x0);
+    launch_k(pack_input_kernel, dim3(grid_for(work, 256)), dim3(256), 0, st, d_planes, n, net->in_planes, S, net->lay_in, c0.kin, net->x0);
     AG_LAUNCH_CHECK("pack_input_kernel");
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
@@ -705,11 +721,11 @@ int ag_net_forward(ag_net* net, const uint8_t* d_planes, int n, float* d_out, vo
     if (rc) return rc;
     ConvLayer& cl = net->L[net->n_conv - 1];
     if (net->head_kind == 0) {
-        policy_head_kernel<<<n, kHeadThreads, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
+        launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
                                                       d_out, nullptr, 0.f, nullptr, nullptr, nullptr, nullptr);
         AG_LAUNCH_CHECK("policy_head_kernel");
     } else {
-        value_head_kernel<<<n, 256, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->d1w, net->d1b, net->d2w, net->d2b,
+        launch_k(value_head_kernel, dim3(n), dim3(256), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->d1w, net->d1b, net->d2w, net->d2b,
                                              net->hidden, d_out);
         AG_LAUNCH_CHECK("value_head_kernel");
     }
@@ -733,10 +749,10 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
     ConvLayer& cl = net->L[last];
     bf16* G = (last == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[last & 1];
     if (last == 0 && net->x0_grad) { set_error("single-layer nets with a wide first filter are not trainable"); return AG_ESTATE; }
-    policy_head_kernel<<<n, kHeadThreads, 0, st>>>(cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
+    launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
                                                   d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr);
     AG_LAUNCH_CHECK("policy_head_kernel");
-    head_reduce_kernel<<<(625 + 127) / 128, 128, 0, st>>>(net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
+    launch_k(head_reduce_kernel, dim3((625 + 127) / 128), dim3(128), 0, st, net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
                                                         net->use_pos_bias ? net->g_hpos : nullptr);
     AG_LAUNCH_CHECK("head_reduce_kernel");
     return AG_OK;
@@ -764,9 +780,9 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     int rc = wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, fused_bias ? c.gb : nullptr, st);
     if (rc) return rc;
     if (!fused_bias) {
-        colsum_stage1_kernel<<<net->colsum_blocks, 256, 0, st>>>(G, rows, c.ldout, net->colsum_part);
+        launch_k(colsum_stage1_kernel, dim3(net->colsum_blocks), dim3(256), 0, st, G, rows, c.ldout, net->colsum_part);
         AG_LAUNCH_CHECK("colsum_stage1_kernel");
-        colsum_stage2_kernel<<<(c.ldout + 7) / 8, 256, 0, st>>>(net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
+        launch_k(colsum_stage2_kernel, dim3((c.ldout + 7) / 8), dim3(256), 0, st, net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
         AG_LAUNCH_CHECK("colsum_stage2_kernel");
     }
     if (layer == 0) return AG_OK;
@@ -809,16 +825,16 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
         int tiles = c.taps * (c.ldout / 32) * (c.kin / 32);
-        sgd_conv_kernel<<<tiles < sm_count() * 8 ? tiles : sm_count() * 8, 256, 0, st>>>(c.w, c.vw, c.gw, c.taps, c.ldout, c.kin, lr, momentum,
+        launch_k(sgd_conv_kernel, dim3(tiles < sm_count() * 8 ? tiles : sm_count() * 8), dim3(256), 0, st, c.w, c.vw, c.gw, c.taps, c.ldout, c.kin, lr, momentum,
                                                                                         grad_scale, c.wf, c.wb, c.b, c.vb, c.gb, c.ldout);
         AG_LAUNCH_CHECK("sgd_conv_kernel");
     }
-    sgd_flat_kernel<<<1, 256, 0, st>>>(net->hw, net->vhw, net->g_hw, 256, lr, momentum, grad_scale);
+    launch_k(sgd_flat_kernel, dim3(1), dim3(256), 0, st, net->hw, net->vhw, net->g_hw, 256, lr, momentum, grad_scale);
     AG_LAUNCH_CHECK("sgd_flat_kernel");
-    sgd_flat_kernel<<<1, 32, 0, st>>>(net->hb, net->vhb, net->g_hb, 1, lr, momentum, grad_scale);
+    launch_k(sgd_flat_kernel, dim3(1), dim3(32), 0, st, net->hb, net->vhb, net->g_hb, 1, lr, momentum, grad_scale);
     AG_LAUNCH_CHECK("sgd_flat_kernel");
     if (net->use_pos_bias) {
-        sgd_flat_kernel<<<1, 256, 0, st>>>(net->hpos, net->vhpos, net->g_hpos, (size_t)net->board * net->board, lr, momentum, grad_scale);
+        launch_k(sgd_flat_kernel, dim3(1), dim3(256), 0, st, net->hpos, net->vhpos, net->g_hpos, (size_t)net->board * net->board, lr, momentum, grad_scale);
         AG_LAUNCH_CHECK("sgd_flat_kernel");
     }
     net->iterations++;

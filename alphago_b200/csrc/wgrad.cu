@@ -51,6 +51,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     const int cochunks = p.ldout / 64;
     const int nchunks = p.taps * cochunks;
 
+    pdl_trigger();
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
         tc::mbar_init(&bars->acc_full, 1);
@@ -70,6 +71,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = bars->tmem_base;
+    pdl_wait();  // everything above overlapped the previous kernel's tail; G, X and the scratch are touched only from here on
 
     if (warp == 0) {
         // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
@@ -168,6 +170,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
 // dW[i] = sum_s scratch[s][i], fixed order
 __global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits,
                                     const float* __restrict__ bias_scratch, float* __restrict__ db, int ldout) {
+    pdl_trigger();
+    pdl_wait();
     if (db && blockIdx.x == 0) {
         for (int c = threadIdx.x; c < ldout; c += blockDim.x) {
             float t = 0.f;
@@ -224,12 +228,12 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    wgrad_kernel<<<args.tiles * args.splits, kThreads, smem, stream>>>(tmap_g, tmap_x, args);
+    launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, tmap_g, tmap_x, args);
     AG_LAUNCH_CHECK("wgrad_kernel");
     size_t count4 = (size_t)args.taps * args.ldout * args.kin / 4;
     int grid = (int)((count4 + 255) / 256);
     if (grid > sm_count() * 8) grid = sm_count() * 8;
-    wgrad_reduce_kernel<<<grid, 256, 0, stream>>>(args.scratch, dw, count4, args.splits, args.bias_scratch, args.bias_scratch ? db : nullptr, args.ldout);
+    launch_k(wgrad_reduce_kernel, dim3(grid), dim3(256), 0, stream, args.scratch, dw, count4, args.splits, args.bias_scratch, args.bias_scratch ? db : nullptr, args.ldout);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
     return AG_OK;
 }
