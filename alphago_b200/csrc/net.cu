@@ -456,7 +456,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         if (rc) return rc;
         rc = make_tmap_2d(&c.tm_wg_x, xin, rows, c.kin, 64);
         if (rc) return rc;
-        c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, (int)rows);
+        c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows);
         size_t need = (size_t)c.wgrad_splits * c.wcount;
         if (need > net->wgrad_scratch_floats) { set_error("wgrad scratch too small"); return AG_ESTATE; }
     }
@@ -506,7 +506,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         net->grad_offsets.push_back((long long)gcount);
         gcount += c.wcount + c.ldout;
         size_t rows_in = (size_t)max_batch * c.lin.img_stride;
-        int splits = wgrad_plan_splits(c.taps, c.ldout, (int)rows_in);
+        int splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows_in);
         if ((size_t)kWgradMaxSplits * c.wcount > scratch) scratch = (size_t)kWgradMaxSplits * c.wcount;
         (void)splits;
     }

@@ -10,6 +10,11 @@
 // flattened (tap, co) axis = two 64-channel chunks, each loaded with its own tap shift, and a
 // contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tap*co][ci] and
 // wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
+//
+// Narrow inputs (kin <= 128: the first layer, 48 planes -> kin = 64) would leave most of the UMMA's N = 256 unused
+// that way (an M = 128 UMMA costs the same ~128 cycles for any N <= 256), so they use the mirrored tiling
+// ("taps in N"): dW[tap][co][ci] = sum_m G[m][co] * X[m + shift(tap)][ci] with the CTA's 128 rows = two co chunks of
+// G (unshifted) and its N = up to 256/kin taps side by side, each X chunk loaded with its own tap shift.
 #include <string.h>
 
 #include "common.cuh"
@@ -38,18 +43,25 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
     const int xchunks = p.kin / 64;
-    const bool with_bias = p.bias_scratch != nullptr;
-    const int tx_bytes = (2 + xchunks) * kChunkBytes;                      // what TMA brings per stage
-    const int stage_bytes = tx_bytes + (with_bias ? kChunkBytes : 0);      // + a chunk of ones: B column kin = 1 for every row
-    const int umma_n = p.kin + (with_bias ? 16 : 0);
+    const int cochunks = p.ldout / 64;
+    const int nchunks = p.taps * cochunks;
+    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
+    const bool taps_in_n = p.tpg > 1;
+    const int cotiles = (cochunks + 1) / 2;
+    const int grp = taps_in_n ? tile / cotiles : 0, cpair = taps_in_n ? tile - grp * cotiles : 0;
+    const int nb = taps_in_n ? min(p.tpg, p.taps - grp * p.tpg) : 1;          // taps side by side in this CTA's B operand
+    const bool with_bias = p.bias_scratch != nullptr && (!taps_in_n || grp == p.groups - 1);  // the last group has room for the ones
+    const int b_chunks = nb * xchunks;
+    const int tx_bytes = (2 + b_chunks) * kChunkBytes;                     // what TMA brings per stage
+    // + a chunk of ones behind the X chunks: one more B column that is 1 for every pixel row
+    const int stage_bytes = (2 + (taps_in_n ? p.tpg * xchunks : xchunks + (p.bias_scratch ? 1 : 0))) * kChunkBytes;
+    const int acc_cols = b_chunks * 64;
+    const int umma_n = acc_cols + (with_bias ? 16 : 0);
     WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
-    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const int kb_total = (p.m_total + 63) / 64;
     const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
-    const int cochunks = p.ldout / 64;
-    const int nchunks = p.taps * cochunks;
 
     pdl_trigger();
     if (threadIdx.x == 0) {
@@ -77,12 +89,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
         int shift[2], col[2];
         bool live[2];
-        for (int h = 0; h < 2; h++) {  // the two (tap, co-chunk) halves of this CTA's 128 dW rows
-            int c = tile * 2 + h;
-            live[h] = c < nchunks;
-            int t = live[h] ? c / cochunks : 0;
-            shift[h] = p.off[t];
-            col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
+        for (int h = 0; h < 2; h++) {  // the two halves of this CTA's 128 dW rows: (tap, co-chunk), or co-chunk alone
+            if (taps_in_n) {
+                int c = cpair * 2 + h;
+                live[h] = c < cochunks;
+                shift[h] = 0;
+                col[h] = live[h] ? c * 64 : 0;
+            } else {
+                int c = tile * 2 + h;
+                live[h] = c < nchunks;
+                int t = live[h] ? c / cochunks : 0;
+                shift[h] = p.off[t];
+                col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
+            }
         }
         int stage = 0;
         uint32_t phase = 0;
@@ -94,8 +113,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                 const int m0 = kb * 64;
                 for (int h = 0; h < 2; h++)  // a dead half reads far out of bounds -> zeros
                     tc::tma_load_2d(s + h * kChunkBytes, &tmap_g, &bars->full[stage], col[h], live[h] ? m0 - shift[h] : 0x40000000);
-                for (int c = 0; c < xchunks; c++)
-                    tc::tma_load_2d(s + (2 + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, m0);
+                for (int j = 0; j < nb; j++) {
+                    const int xrow = taps_in_n ? m0 + p.off[grp * p.tpg + j] : m0;  // rows outside the tensor read as zeros
+                    for (int c = 0; c < xchunks; c++)
+                        tc::tma_load_2d(s + (2 + j * xchunks + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, xrow);
+                }
             }
             __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -125,16 +147,16 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     } else {
         const int q = warp & 3;
         const int r = q * 32 + lane;           // row of the 128-row tile
-        const int chunk = tile * 2 + (r >> 6);
-        const bool valid = chunk < nchunks;
-        // scratch row = tap*ldout + co  (chunk*64 + r%64 by construction)
+        const int chunk = (taps_in_n ? cpair : tile) * 2 + (r >> 6);
+        const bool valid = chunk < (taps_in_n ? cochunks : nchunks);
+        // scratch row = tap*ldout + co  (shifted-G tiling: chunk*64 + r%64 by construction; taps in N: the tap comes from the column)
         float* dst = p.scratch + ((size_t)split * p.taps * p.ldout + (size_t)chunk * 64 + (r & 63)) * p.kin;
         if (kb1 > kb0) {
             tc::mbar_wait(&bars->acc_full, 0);
             tc::fence_after_sync();
         }
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        for (int c0 = 0; c0 < p.kin; c0 += 32) {
+        for (int c0 = 0; c0 < acc_cols; c0 += 32) {
             uint32_t v[32];
             if (kb1 > kb0) {
                 tc::tmem_ld32(taddr + c0, v);
@@ -144,17 +166,23 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                 for (int j = 0; j < 32; j++) v[j] = 0;
             }
             if (valid) {
+                float* d = dst + c0;
+                if (taps_in_n) {  // column c0 = (tap within the group) * kin + ci
+                    const int j = c0 / p.kin;
+                    d = dst + (size_t)(grp * p.tpg + j) * p.ldout * p.kin + (c0 - j * p.kin);
+                }
 #pragma unroll
                 for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    *reinterpret_cast<uint4*>(d + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             }
         }
         if (with_bias) {
-            // column kin of the centre tap's rows is sum_m G[m][co]: the bias gradient (warp-uniform branch: a warp's 32 rows share a chunk)
-            const int t = valid ? chunk / cochunks : -1;
-            if (t == p.taps / 2) {
+            // the column behind the last X chunk is sum_m G[m][co]: the bias gradient.  Shifted-G tiling: taken from the centre
+            // tap's rows (no shift); taps in N: G is never shifted.  (warp-uniform branch: a warp's 32 rows share a chunk)
+            const int t = taps_in_n ? 0 : (valid ? chunk / cochunks : -1);
+            if (valid && (taps_in_n || t == p.taps / 2)) {
                 uint32_t v[32];
-                if (kb1 > kb0) { tc::tmem_ld32(taddr + p.kin, v); tc::tmem_ld_wait(); } else v[0] = 0;
+                if (kb1 > kb0) { tc::tmem_ld32(taddr + acc_cols, v); tc::tmem_ld_wait(); } else v[0] = 0;
                 p.bias_scratch[(size_t)split * p.ldout + (chunk - t * cochunks) * 64 + (r & 63)] = __uint_as_float(v[0]);
             }
         }
@@ -193,13 +221,32 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __
 
 }  // namespace
 
-size_t wgrad_smem_bytes(int kin, bool with_bias) { return 1024 + (size_t)kStages * (2 + kin / 64 + (with_bias ? 1 : 0)) * kChunkBytes + sizeof(WgradBarriers) + 64; }
+// Tiling choice: taps per B operand (1 = shifted-G tiling) and the CTA tiles of one split.  Taps in N needs a spare
+// 16 columns behind the last group's taps for the ones column, which every odd tap count (1x1, 3x3, 5x5) leaves.
+static int wgrad_tiling(int taps, int ldout, int kin, int* tpg, int* groups) {
+    int t = 256 / kin;
+    if (t >= 2 && taps >= 2 && taps % t != 0) {
+        *tpg = t;
+        *groups = (taps + t - 1) / t;
+        return ((ldout / 64 + 1) / 2) * *groups;
+    }
+    *tpg = 1;
+    *groups = taps;
+    return (taps * (ldout / 64) + 1) / 2;
+}
 
-int wgrad_plan_splits(int taps, int ldout, int m_total) {
+size_t wgrad_smem_bytes(int taps, int kin, bool with_bias) {
+    int tpg, groups;
+    wgrad_tiling(taps, 64, kin, &tpg, &groups);
+    int chunks = 2 + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0));
+    return 1024 + (size_t)kStages * chunks * kChunkBytes + sizeof(WgradBarriers) + 64;
+}
+
+int wgrad_plan_splits(int taps, int ldout, int kin, int m_total) {
     // CTAs = tiles * splits should fill whole waves of the SMs: one wave if that keeps >= 85 % of them busy,
     // else two.  Fewer, longer K slices also mean fewer fp32 partials to write and reduce.
-    int chunks = taps * (ldout / 64);
-    int tiles = (chunks + 1) / 2;
+    int tpg, groups;
+    int tiles = wgrad_tiling(taps, ldout, kin, &tpg, &groups);
     int kb = (m_total + 63) / 64;
     int sms = sm_count();
     int s1 = sms / tiles, s2 = 2 * sms / tiles;
@@ -216,13 +263,12 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
         set_error("wgrad: channel counts must be padded to 64 (kin=%d <= 256, ldout=%d)", args.kin, args.ldout);
         return AG_EINVAL;
     }
-    int chunks = args.taps * (args.ldout / 64);
-    args.tiles = (chunks + 1) / 2;
+    args.tiles = wgrad_tiling(args.taps, args.ldout, args.kin, &args.tpg, &args.groups);
     if (args.splits < 1) args.splits = 1;
     static size_t configured = 0;
     if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
     if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
-    size_t smem = wgrad_smem_bytes(args.kin, args.bias_scratch != nullptr);
+    size_t smem = wgrad_smem_bytes(args.taps, args.kin, args.bias_scratch != nullptr);
     if (smem > 227 * 1024) { set_error("wgrad: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -261,7 +307,7 @@ extern "C" {
 // bytes of scratch ag_wgrad wants for this problem (the split-K partials)
 size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows) {
     if (ag::wgrad_check(rows, ldout, kin, 1) || width < 1 || width > 5) return 0;
-    return (size_t)ag::wgrad_plan_splits(width * width, ldout, (int)rows) * width * width * ldout * kin * sizeof(float);
+    return (size_t)ag::wgrad_plan_splits(width * width, ldout, kin, (int)rows) * width * width * ldout * kin * sizeof(float);
 }
 
 int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride, float* d_scratch,
@@ -274,7 +320,7 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
     if (rc) return rc;
     a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
     const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
-    a.splits = ag::wgrad_plan_splits(a.taps, ldout, (int)rows);
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows);
     if ((size_t)a.splits * partial > scratch_bytes) a.splits = (int)(scratch_bytes / partial);
     if (a.splits < 1 || !d_scratch) { ag::set_error("ag_wgrad: scratch of %zu bytes is smaller than one partial (%zu bytes)", scratch_bytes, partial); return AG_EINVAL; }
     a.scratch = d_scratch;
@@ -337,7 +383,7 @@ int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout,
                       "use ag_wgrad with your own scratch", width, width, ldout, kin, partial, AG_WGRAD_STATIC_SCRATCH_BYTES);
         return AG_EINVAL;
     }
-    a.splits = ag::wgrad_plan_splits(a.taps, ldout, (int)rows);
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows);
     if ((size_t)a.splits * partial > AG_WGRAD_STATIC_SCRATCH_BYTES) a.splits = (int)(AG_WGRAD_STATIC_SCRATCH_BYTES / partial);
     rc = ag::wgrad_static_scratch_ptr(&a.scratch);
     if (rc) return rc;
