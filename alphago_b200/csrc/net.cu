@@ -386,7 +386,7 @@ struct ConvLayer {
     CUtensorMap tm_in, tm_wf, tm_g, tm_wb;      // forward A / B, dgrad A / B (full-size tensors)
     CUtensorMap tm_wf_half, tm_wb_half;         // B with a box of N/2 rows, for the CTA-pair kernel
     bool pair_fwd, pair_bwd;
-    CUtensorMap tm_wg_g, tm_wg_x;               // wgrad operands, exact batch rows (rebuilt when n changes)
+    WgradMaps tm_wg;                            // wgrad operands, exact batch rows (rebuilt when n changes)
     int wgrad_splits;
 };
 
@@ -452,9 +452,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         const bf16* xin = l == 0 ? net->x0 : net->L[l - 1].act;
         const bf16* g = (l == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[l & 1];
         uint64_t rows = (uint64_t)n * c.lin.img_stride;
-        int rc = make_tmap_2d(&c.tm_wg_g, g, rows, c.ldout, 64);
-        if (rc) return rc;
-        rc = make_tmap_2d(&c.tm_wg_x, xin, rows, c.kin, 64);
+        int rc = wgrad_make_maps(&c.tm_wg, g, xin, rows, c.ldout, c.kin, c.taps, c.off_fwd);
         if (rc) return rc;
         c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows);
         size_t need = (size_t)c.wgrad_splits * c.wcount;
@@ -777,7 +775,7 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
     const bool fused_bias = c.kin + 16 <= 256;  // the bias gradient rides in the weight-gradient GEMM as an extra column of ones
     w.bias_scratch = fused_bias ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
-    int rc = wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, fused_bias ? c.gb : nullptr, st);
+    int rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
     if (rc) return rc;
     if (!fused_bias) {
         launch_k(colsum_stage1_kernel, dim3(net->colsum_blocks), dim3(256), 0, st, G, rows, c.ldout, net->colsum_part);
@@ -873,7 +871,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         w.m_total = n * c.lin.img_stride; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
         w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
         w.bias_scratch = c.kin + 16 <= 256 ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
-        return wgrad_launch(c.tm_wg_g, c.tm_wg_x, w, c.gw, w.bias_scratch ? c.gb : nullptr, st);
+        return wgrad_launch(c.tm_wg, w, c.gw, w.bias_scratch ? c.gb : nullptr, st);
     }
     if (mode == 1 && layer > 0 && !(layer == 1 && net->x0_grad)) {
         ConvLayer& below = net->L[layer - 1];

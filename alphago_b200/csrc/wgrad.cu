@@ -6,8 +6,8 @@
 // G = gradient w.r.t. the layer's pre-activation output, X = the layer's input, both padded-pixel-
 // row matrices (conv.cuh) whose zero pad slots make the halo terms vanish.  The reduction index m
 // is the ROW index of both matrices, so both operands are MN-major: TMA brings [64 pixel rows][64
-// channels] boxes (128-byte swizzle) that the UMMA reads transposed.  A CTA owns 128 rows of the
-// flattened (tap, co) axis = two 64-channel chunks, each loaded with its own tap shift, and a
+// channels] boxes (128-byte swizzle) that the UMMA reads transposed.  A CTA owns two 128-row tiles of the
+// flattened (tap, co) axis = four 64-channel chunks, each loaded with its own tap shift, and a
 // contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tap*co][ci] and
 // wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
 //
@@ -15,6 +15,7 @@
 // that way (an M = 128 UMMA costs the same ~128 cycles for any N <= 256), so they use the mirrored tiling
 // ("taps in N"): dW[tap][co][ci] = sum_m G[m][co] * X[m + shift(tap)][ci] with the CTA's 128 rows = two co chunks of
 // G (unshifted) and its N = up to 256/kin taps side by side, each X chunk loaded with its own tap shift.
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -26,38 +27,66 @@ namespace ag {
 
 namespace {
 
-constexpr int kStages = 4;
+constexpr int kMaxStages = 6;
 constexpr int kChunkBytes = 64 * 128;  // [64 pixel rows][64 bf16]
 constexpr int kThreads = 192;
-constexpr int kTmemCols = 256;
+constexpr int kTmemCols = 512;
+constexpr int kAccStride = 256;  // TMEM columns between the CTA's two accumulators
+constexpr int kASlots = 4;       // 64-row slots of dW rows per CTA: two accumulators x two halves
+constexpr int kARegion = kASlots * kChunkBytes;  // bytes of a stage set aside for G
 
 struct __align__(8) WgradBarriers {
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
     uint64_t acc_full;
     uint32_t tmem_base;
 };
 
+// Per-CTA constants, worked out once by thread 0.
+struct WgradPlan {
+    int n_win;               // G boxes fetched per stage
+    int win_off[kASlots];    // byte offset of the box inside the stage
+    int win_col[kASlots];    // its G column (co chunk * 64)
+    int win_shift[kASlots];  // its first row is G row m0 - win_shift
+    int slot_off[kASlots];   // byte offset, inside the stage, of the slot's first pixel row; -1 = dead slot
+    int slot_row[kASlots];   // scratch row of the slot's first channel: tap*ldout + co chunk*64 (taps in N: co chunk*64)
+    int slot_bias[kASlots];  // co chunk*64 when the slot's ones column is the bias gradient, else -1
+    int lo[2], hi[2];        // slots behind rows 0-63 / 64-127 of each accumulator (hi = -1: dead half); lo has the lower address
+};
+
+// The kernel is bound by L2 -> shared-memory bandwidth, not by the tensor cores (a 128-row tile alone would need 16 KB
+// of G and 24 KB of X per 4 UMMAs; the chip's L2 delivers ~43 B per SM per cycle), so
+//   * a CTA owns TWO 128-row tiles that share the X operand: two accumulators in TMEM, 8 UMMAs per stage;
+//   * its four 64-row slots are consecutive TAPS of one co chunk (co-major order), and taps of one co chunk are the same
+//     G rows shifted by a few pixel rows: ONE box of 64 + span rows is fetched per co chunk ("window") and every slot's
+//     UMMA descriptor starts at its own row of it (128 B per row; the 128-byte swizzle is a function of the address, so
+//     a row-shifted start reads the right bytes).
 __global__ void __launch_bounds__(kThreads, 1)
-wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x, const WgradArgs p) {
+wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_gw, const __grid_constant__ CUtensorMap tmap_x,
+             const WgradArgs p, const int kStages) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
     const int xchunks = p.kin / 64;
     const int cochunks = p.ldout / 64;
-    const int nchunks = p.taps * cochunks;
     const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const bool taps_in_n = p.tpg > 1;
-    const int cotiles = (cochunks + 1) / 2;
-    const int grp = taps_in_n ? tile / cotiles : 0, cpair = taps_in_n ? tile - grp * cotiles : 0;
+    const bool windowed = p.win_rows > 0;
+    const int coquads = (cochunks + kASlots - 1) / kASlots;
+    const int grp = taps_in_n ? tile / coquads : 0;
+    // this CTA's slots are a_first .. a_first+3 of a_count: (co chunk, tap) pairs co-major, or co chunks alone (taps in N)
+    const int a_first = (taps_in_n ? tile - grp * coquads : tile) * kASlots;
+    const int a_count = taps_in_n ? cochunks : p.taps * cochunks;
+    const int a_live = min(kASlots, a_count - a_first);
     const int nb = taps_in_n ? min(p.tpg, p.taps - grp * p.tpg) : 1;          // taps side by side in this CTA's B operand
     const bool with_bias = p.bias_scratch != nullptr && (!taps_in_n || grp == p.groups - 1);  // the last group has room for the ones
     const int b_chunks = nb * xchunks;
-    const int tx_bytes = (2 + b_chunks) * kChunkBytes;                     // what TMA brings per stage
-    // + a chunk of ones behind the X chunks: one more B column that is 1 for every pixel row
-    const int stage_bytes = (2 + (taps_in_n ? p.tpg * xchunks : xchunks + (p.bias_scratch ? 1 : 0))) * kChunkBytes;
+    // stage = G region (4 slots' worth) | X chunks | a chunk of ones: one more B column that is 1 for every pixel row
+    const int stage_bytes = kARegion + (taps_in_n ? p.tpg * xchunks : xchunks + (p.bias_scratch ? 1 : 0)) * kChunkBytes;
+    const int ones_off = kARegion + b_chunks * kChunkBytes;
     const int acc_cols = b_chunks * 64;
     const int umma_n = acc_cols + (with_bias ? 16 : 0);
     WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
+    WgradPlan* plan = reinterpret_cast<WgradPlan*>(bars + 1);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
     const int kb_total = (p.m_total + 63) / 64;
@@ -69,12 +98,44 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         tc::mbar_init(&bars->acc_full, 1);
         tc::fence_mbar_init();
         tc::tma_prefetch_desc(&tmap_g);
+        tc::tma_prefetch_desc(&tmap_gw);
         tc::tma_prefetch_desc(&tmap_x);
+        // ---- the plan
+        const int win_bytes = windowed ? ((p.win_rows * 128 + 1023) & ~1023) : kChunkBytes;
+        int cc[kASlots], shift[kASlots], win_of[kASlots];
+        int n_win = 0;
+        for (int i = 0; i < kASlots; i++) {
+            plan->slot_off[i] = -1; plan->slot_row[i] = 0; plan->slot_bias[i] = -1;
+            if (i >= a_live) continue;
+            const int c = a_first + i;
+            int tap = 0;
+            if (taps_in_n) { cc[i] = c; shift[i] = 0; }
+            else { cc[i] = c / p.taps; tap = c - cc[i] * p.taps; shift[i] = p.off[tap]; }
+            plan->slot_row[i] = tap * p.ldout + cc[i] * 64;
+            if (taps_in_n || tap == p.taps / 2) plan->slot_bias[i] = cc[i] * 64;  // unshifted G: its column sums are the bias gradient
+            if (windowed && i > 0 && cc[i] == cc[i - 1]) {
+                win_of[i] = win_of[i - 1];
+            } else {
+                win_of[i] = n_win;
+                plan->win_off[n_win] = n_win * win_bytes;
+                plan->win_col[n_win] = cc[i] * 64;
+                n_win++;
+            }
+            plan->win_shift[win_of[i]] = shift[i];  // shifts grow with the tap: the last member's is the window's first row
+        }
+        plan->n_win = n_win;
+        for (int i = 0; i < a_live; i++) plan->slot_off[i] = plan->win_off[win_of[i]] + (plan->win_shift[win_of[i]] - shift[i]) * 128;
+        for (int a = 0; a < 2; a++) {
+            const int s0 = 2 * a, s1 = 2 * a + 1;
+            if (s1 >= a_live) { plan->lo[a] = s0; plan->hi[a] = -1; }
+            else if (plan->slot_off[s0] < plan->slot_off[s1]) { plan->lo[a] = s0; plan->hi[a] = s1; }
+            else { plan->lo[a] = s1; plan->hi[a] = s0; }
+        }
     }
     if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
     if (with_bias) {  // the ones chunk of every stage (all elements equal, so the swizzle does not matter)
         for (int s = 0; s < kStages; s++) {
-            uint32_t* ones = reinterpret_cast<uint32_t*>(base + s * stage_bytes + tx_bytes);
+            uint32_t* ones = reinterpret_cast<uint32_t*>(base + s * stage_bytes + ones_off);
             for (int i = threadIdx.x; i < kChunkBytes / 4; i += kThreads) ones[i] = 0x3F803F80u;  // bf16 1.0 x2
         }
         tc::fence_proxy_async();  // generic-proxy writes, read by the tensor core
@@ -87,36 +148,23 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
 
     if (warp == 0) {
         // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
-        int shift[2], col[2];
-        bool live[2];
-        for (int h = 0; h < 2; h++) {  // the two halves of this CTA's 128 dW rows: (tap, co-chunk), or co-chunk alone
-            if (taps_in_n) {
-                int c = cpair * 2 + h;
-                live[h] = c < cochunks;
-                shift[h] = 0;
-                col[h] = live[h] ? c * 64 : 0;
-            } else {
-                int c = tile * 2 + h;
-                live[h] = c < nchunks;
-                int t = live[h] ? c / cochunks : 0;
-                shift[h] = p.off[t];
-                col[h] = live[h] ? (c - t * cochunks) * 64 : 0;
-            }
-        }
+        const int n_win = plan->n_win;
+        const CUtensorMap* gmap = windowed ? &tmap_gw : &tmap_g;
+        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : kChunkBytes) + b_chunks * kChunkBytes);
         int stage = 0;
         uint32_t phase = 0;
         for (int kb = kb0; kb < kb1; kb++) {
             tc::mbar_wait(&bars->empty[stage], phase ^ 1);
             if (tc::elect_one()) {
                 uint8_t* s = base + stage * stage_bytes;
-                tc::mbar_expect_tx(&bars->full[stage], (uint32_t)tx_bytes);
+                tc::mbar_expect_tx(&bars->full[stage], tx_bytes);
                 const int m0 = kb * 64;
-                for (int h = 0; h < 2; h++)  // a dead half reads far out of bounds -> zeros
-                    tc::tma_load_2d(s + h * kChunkBytes, &tmap_g, &bars->full[stage], col[h], live[h] ? m0 - shift[h] : 0x40000000);
+                for (int w = 0; w < n_win; w++)  // rows outside the tensor read as zeros
+                    tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
                 for (int j = 0; j < nb; j++) {
-                    const int xrow = taps_in_n ? m0 + p.off[grp * p.tpg + j] : m0;  // rows outside the tensor read as zeros
+                    const int xrow = taps_in_n ? m0 + p.off[grp * p.tpg + j] : m0;
                     for (int c = 0; c < xchunks; c++)
-                        tc::tma_load_2d(s + (2 + j * xchunks + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, xrow);
+                        tc::tma_load_2d(s + kARegion + (j * xchunks + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, xrow);
                 }
             }
             __syncwarp();
@@ -124,6 +172,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         }
     } else if (warp == 1) {
         const uint32_t idesc = tc::idesc_bf16(128, umma_n, 1, 1);
+        const bool second = a_live > 2;  // the second accumulator has at least one live half
+        // A operand of accumulator a: rows 0-63 from slot lo, rows 64-127 from slot hi (LBO = their distance)
+        uint32_t a_off[2], a_lbo[2];
+        for (int a = 0; a < 2; a++) {
+            const int lo = plan->lo[a], hi = plan->hi[a];
+            a_off[a] = (uint32_t)max(plan->slot_off[lo], 0);
+            a_lbo[a] = hi >= 0 ? (uint32_t)(plan->slot_off[hi] - plan->slot_off[lo]) : (uint32_t)kChunkBytes;
+        }
         int stage = 0;
         uint32_t phase = 0;
         bool ready = false;
@@ -132,11 +188,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             tc::fence_after_sync();
             if (tc::elect_one()) {
                 const uint32_t s = tc::smem_u32(base + stage * stage_bytes);
-                const uint64_t adesc = tc::desc_mnmajor_sw128(s, kChunkBytes);
-                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + 2 * kChunkBytes, kChunkBytes);
+                uint64_t adesc0 = tc::desc_mnmajor_sw128(s + a_off[0], a_lbo[0]);
+                uint64_t adesc1 = tc::desc_mnmajor_sw128(s + a_off[1], a_lbo[1]);
+                if (p.debug & 1) {  // experiment: descriptor base-offset field = position of the start inside the 1024-byte swizzle pattern
+                    adesc0 |= (uint64_t)(((s + a_off[0]) >> 7) & 7) << 49;
+                    adesc1 |= (uint64_t)(((s + a_off[1]) >> 7) & 7) << 49;
+                }
+                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + kARegion, kChunkBytes);
 #pragma unroll
-                for (int k = 0; k < 4; k++)  // 16 pixel rows per UMMA: +2048 B
-                    tc::umma_bf16(tmem_base, adesc + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                for (int k = 0; k < 4; k++) {  // 16 pixel rows per UMMA: +2048 B
+                    tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                    if (second)
+                        tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                }
                 tc::umma_commit(&bars->empty[stage]);
                 if (kb == kb1 - 1) tc::umma_commit(&bars->acc_full);
             }
@@ -146,44 +210,43 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         }
     } else {
         const int q = warp & 3;
-        const int r = q * 32 + lane;           // row of the 128-row tile
-        const int chunk = (taps_in_n ? cpair : tile) * 2 + (r >> 6);
-        const bool valid = chunk < (taps_in_n ? cochunks : nchunks);
-        // scratch row = tap*ldout + co  (shifted-G tiling: chunk*64 + r%64 by construction; taps in N: the tap comes from the column)
-        float* dst = p.scratch + ((size_t)split * p.taps * p.ldout + (size_t)chunk * 64 + (r & 63)) * p.kin;
+        const int r = q * 32 + lane;           // row of a 128-row accumulator
         if (kb1 > kb0) {
             tc::mbar_wait(&bars->acc_full, 0);
             tc::fence_after_sync();
         }
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        for (int c0 = 0; c0 < acc_cols; c0 += 32) {
-            uint32_t v[32];
-            if (kb1 > kb0) {
-                tc::tmem_ld32(taddr + c0, v);
-                tc::tmem_ld_wait();
-            } else {
+        for (int a = 0; a < 2; a++) {
+            if (a * 2 >= a_live) break;  // warp-uniform
+            const int slot = (r >> 6) ? plan->hi[a] : plan->lo[a];  // warp-uniform: a warp's 32 rows share a half
+            const bool valid = slot >= 0;
+            const int srow = valid ? plan->slot_row[slot] : 0;
+            float* dst = p.scratch + ((size_t)split * p.taps * p.ldout + (size_t)srow + (r & 63)) * p.kin;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * kAccStride;
+            for (int c0 = 0; c0 < acc_cols; c0 += 32) {
+                uint32_t v[32];
+                if (kb1 > kb0) {
+                    tc::tmem_ld32(taddr + c0, v);
+                    tc::tmem_ld_wait();
+                } else {
 #pragma unroll
-                for (int j = 0; j < 32; j++) v[j] = 0;
-            }
-            if (valid) {
-                float* d = dst + c0;
-                if (taps_in_n) {  // column c0 = (tap within the group) * kin + ci
-                    const int j = c0 / p.kin;
-                    d = dst + (size_t)(grp * p.tpg + j) * p.ldout * p.kin + (c0 - j * p.kin);
+                    for (int j = 0; j < 32; j++) v[j] = 0;
                 }
+                if (valid) {
+                    float* d = dst + c0;
+                    if (taps_in_n) {  // column c0 = (tap within the group) * kin + ci
+                        const int j = c0 / p.kin;
+                        d = dst + (size_t)(grp * p.tpg + j) * p.ldout * p.kin + (c0 - j * p.kin);
+                    }
 #pragma unroll
-                for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<uint4*>(d + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<uint4*>(d + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                }
             }
-        }
-        if (with_bias) {
-            // the column behind the last X chunk is sum_m G[m][co]: the bias gradient.  Shifted-G tiling: taken from the centre
-            // tap's rows (no shift); taps in N: G is never shifted.  (warp-uniform branch: a warp's 32 rows share a chunk)
-            const int t = taps_in_n ? 0 : (valid ? chunk / cochunks : -1);
-            if (valid && (taps_in_n || t == p.taps / 2)) {
+            if (with_bias && valid && plan->slot_bias[slot] >= 0) {
+                // the column behind the last X chunk is sum_m G[m][co] for an unshifted slot: the bias gradient
                 uint32_t v[32];
                 if (kb1 > kb0) { tc::tmem_ld32(taddr + acc_cols, v); tc::tmem_ld_wait(); } else v[0] = 0;
-                p.bias_scratch[(size_t)split * p.ldout + (chunk - t * cochunks) * 64 + (r & 63)] = __uint_as_float(v[0]);
+                p.bias_scratch[(size_t)split * p.ldout + plan->slot_bias[slot] + (r & 63)] = __uint_as_float(v[0]);
             }
         }
     }
@@ -195,11 +258,16 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     }
 }
 
-// dW[i] = sum_s scratch[s][i], fixed order
-__global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits,
-                                    const float* __restrict__ bias_scratch, float* __restrict__ db, int ldout) {
+// dW[i] = sum_s scratch[s][i] in a fixed association (deterministic): the block's 4 thread rows each sum every 4th
+// split (independent loads, all in flight together), then the four sums are added in order through shared memory.
+constexpr int kReduceCols = 64;   // float4 columns per block
+constexpr int kReduceWays = 4;
+__global__ void __launch_bounds__(kReduceCols * kReduceWays)
+wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits,
+                    const float* __restrict__ bias_scratch, float* __restrict__ db, int ldout) {
     pdl_trigger();
     pdl_wait();
+    __shared__ float4 part[kReduceWays][kReduceCols];
     if (db && blockIdx.x == 0) {
         for (int c = threadIdx.x; c < ldout; c += blockDim.x) {
             float t = 0.f;
@@ -209,13 +277,28 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ scratch, float* __
     }
     const float4* s4 = reinterpret_cast<const float4*>(scratch);
     float4* d4 = reinterpret_cast<float4*>(dw);
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count4; i += (size_t)gridDim.x * blockDim.x) {
-        float4 a = s4[i];
-        for (int s = 1; s < splits; s++) {
-            float4 b = s4[(size_t)s * count4 + i];
-            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    const int col = threadIdx.x % kReduceCols, way = threadIdx.x / kReduceCols;
+    for (size_t i0 = (size_t)blockIdx.x * kReduceCols; i0 < count4; i0 += (size_t)gridDim.x * kReduceCols) {
+        const size_t i = i0 + col;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < count4) {
+#pragma unroll 8
+            for (int s = way; s < splits; s += kReduceWays) {
+                const float4 b = __ldg(s4 + (size_t)s * count4 + i);
+                a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+            }
         }
-        d4[i] = a;
+        part[way][col] = a;
+        __syncthreads();
+        if (way == 0 && i < count4) {
+#pragma unroll
+            for (int w = 1; w < kReduceWays; w++) {
+                const float4 b = part[w][col];
+                a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+            }
+            d4[i] = a;
+        }
+        __syncthreads();
     }
 }
 
@@ -228,18 +311,54 @@ static int wgrad_tiling(int taps, int ldout, int kin, int* tpg, int* groups) {
     if (t >= 2 && taps >= 2 && taps % t != 0) {
         *tpg = t;
         *groups = (taps + t - 1) / t;
-        return ((ldout / 64 + 1) / 2) * *groups;
+        return ((ldout / 64 + kASlots - 1) / kASlots) * *groups;
     }
     *tpg = 1;
     *groups = taps;
-    return (taps * (ldout / 64) + 1) / 2;
+    return (taps * (ldout / 64) + kASlots - 1) / kASlots;
+}
+
+static int wgrad_stage_bytes(int taps, int kin, bool with_bias) {
+    int tpg, groups;
+    wgrad_tiling(taps, 64, kin, &tpg, &groups);
+    return kARegion + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0)) * kChunkBytes;
+}
+
+static int wgrad_stages(int taps, int kin, bool with_bias) {
+    int s = (227 * 1024 - 1024 - (int)sizeof(WgradBarriers) - (int)sizeof(WgradPlan) - 64) / wgrad_stage_bytes(taps, kin, with_bias);
+    return s > kMaxStages ? kMaxStages : s;
 }
 
 size_t wgrad_smem_bytes(int taps, int kin, bool with_bias) {
+    return 1024 + (size_t)wgrad_stages(taps, kin, with_bias) * wgrad_stage_bytes(taps, kin, with_bias) + sizeof(WgradBarriers) + sizeof(WgradPlan) + 64;
+}
+
+// Rows of the G box shared by the taps of one co chunk (0 = every slot fetches its own 64 rows): 64 + the largest
+// shift distance inside any four consecutive taps.  A CTA holds at most two such boxes (taps >= 3), which must fit
+// the G region of a stage.
+int wgrad_window_rows(int taps, const int* off, int kin) {
     int tpg, groups;
     wgrad_tiling(taps, 64, kin, &tpg, &groups);
-    int chunks = 2 + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0));
-    return 1024 + (size_t)kStages * chunks * kChunkBytes + sizeof(WgradBarriers) + 64;
+    static int enabled = -1;
+    if (enabled < 0) { const char* e = getenv("AG_WGRAD_WINDOW"); enabled = (e && e[0] == '0') ? 0 : 1; }
+    if (tpg > 1 || taps < 3 || !enabled) return 0;
+    int span = 0;
+    for (int t = 0; t < taps; t++) {
+        int u = t + kASlots - 1 < taps ? t + kASlots - 1 : taps - 1;
+        if (off[u] < off[t]) return 0;  // shifts must grow with the tap
+        if (off[u] - off[t] > span) span = off[u] - off[t];
+    }
+    int rows = (64 + span + 7) & ~7;
+    if (rows > 256 || 2 * ((rows * 128 + 1023) & ~1023) > kARegion) return 0;
+    return rows;
+}
+
+int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, int ldout, int kin, int taps, const int* off) {
+    int rc = make_tmap_2d(&m->g, g, rows, ldout, 64);
+    if (!rc) rc = make_tmap_2d(&m->x, x, rows, kin, 64);
+    m->win_rows = wgrad_window_rows(taps, off, kin);
+    if (!rc) rc = make_tmap_2d(&m->gw, g, rows, ldout, m->win_rows ? m->win_rows : 64);
+    return rc;
 }
 
 int wgrad_plan_splits(int taps, int ldout, int kin, int m_total) {
@@ -258,7 +377,7 @@ int wgrad_plan_splits(int taps, int ldout, int kin, int m_total) {
     return s;
 }
 
-int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, float* db, cudaStream_t stream) {
+int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cudaStream_t stream) {
     if (args.kin % 64 != 0 || args.kin < 64 || args.kin > 256 || args.ldout % 64 != 0) {
         set_error("wgrad: channel counts must be padded to 64 (kin=%d <= 256, ldout=%d)", args.kin, args.ldout);
         return AG_EINVAL;
@@ -274,12 +393,17 @@ int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, tmap_g, tmap_x, args);
+    { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AG_WGRAD_DEBUG"); dbg = e ? atoi(e) : 0; } args.debug = dbg; }
+    const int stages = wgrad_stages(args.taps, args.kin, args.bias_scratch != nullptr);
+    if (stages < 2) { set_error("wgrad: shared memory fits only %d stage(s)", stages); return AG_EINVAL; }
+    args.win_rows = maps.win_rows;
+    launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, maps.g, maps.gw, maps.x, args, stages);
     AG_LAUNCH_CHECK("wgrad_kernel");
     size_t count4 = (size_t)args.taps * args.ldout * args.kin / 4;
-    int grid = (int)((count4 + 255) / 256);
-    if (grid > sm_count() * 8) grid = sm_count() * 8;
-    launch_k(wgrad_reduce_kernel, dim3(grid), dim3(256), 0, stream, args.scratch, dw, count4, args.splits, args.bias_scratch, args.bias_scratch ? db : nullptr, args.ldout);
+    int grid = (int)((count4 + kReduceCols - 1) / kReduceCols);
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
+    launch_k(wgrad_reduce_kernel, dim3(grid), dim3(kReduceCols * kReduceWays), 0, stream, args.scratch, dw, count4, args.splits, args.bias_scratch,
+             args.bias_scratch ? db : nullptr, args.ldout);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
     return AG_OK;
 }
@@ -324,11 +448,10 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
     if ((size_t)a.splits * partial > scratch_bytes) a.splits = (int)(scratch_bytes / partial);
     if (a.splits < 1 || !d_scratch) { ag::set_error("ag_wgrad: scratch of %zu bytes is smaller than one partial (%zu bytes)", scratch_bytes, partial); return AG_EINVAL; }
     a.scratch = d_scratch;
-    CUtensorMap tg, tx;
-    rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
-    if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
+    ag::WgradMaps maps;
+    rc = ag::wgrad_make_maps(&maps, d_g, d_x, (uint64_t)rows, ldout, kin, a.taps, a.off);
     if (rc) return rc;
-    return ag::wgrad_launch(tg, tx, a, d_dw, nullptr, (cudaStream_t)stream);
+    return ag::wgrad_launch(maps, a, d_dw, nullptr, (cudaStream_t)stream);
 }
 
 }  // extern "C"
@@ -387,11 +510,10 @@ int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout,
     if ((size_t)a.splits * partial > AG_WGRAD_STATIC_SCRATCH_BYTES) a.splits = (int)(AG_WGRAD_STATIC_SCRATCH_BYTES / partial);
     rc = ag::wgrad_static_scratch_ptr(&a.scratch);
     if (rc) return rc;
-    CUtensorMap tg, tx;
-    rc = ag::make_tmap_2d(&tg, d_g, (uint64_t)rows, ldout, 64);
-    if (!rc) rc = ag::make_tmap_2d(&tx, d_x, (uint64_t)rows, kin, 64);
+    ag::WgradMaps maps;
+    rc = ag::wgrad_make_maps(&maps, d_g, d_x, (uint64_t)rows, ldout, kin, a.taps, a.off);
     if (rc) return rc;
-    return ag::wgrad_launch(tg, tx, a, d_dw, nullptr, (cudaStream_t)stream);
+    return ag::wgrad_launch(maps, a, d_dw, nullptr, (cudaStream_t)stream);
 }
 
 }  // extern "C"

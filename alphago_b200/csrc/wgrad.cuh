@@ -20,15 +20,23 @@ struct WgradArgs {
     int tiles;     // filled by wgrad_launch
     int tpg;       // filled by wgrad_launch: taps per B operand (1 = shifted-G tiling, >= 2 = taps-in-N tiling, see wgrad.cu)
     int groups;    // filled by wgrad_launch: tap groups (taps-in-N tiling)
+    int win_rows;  // filled by wgrad_launch from the maps
+    int debug;     // experiments only (AG_WGRAD_DEBUG)
     float* scratch;  // [splits][taps*ldout][kin] fp32
     float* bias_scratch;  // nullptr, or [splits][ldout] fp32: column sums of G (the bias gradient) ride along as one more B column
 };
 
 size_t wgrad_smem_bytes(int taps, int kin, bool with_bias);
 int wgrad_plan_splits(int taps, int ldout, int kin, int m_total);
-// tmap_g: G [m_total rows][ldout], tmap_x: X [m_total rows][kin], both with box [64][64] and EXACTLY
-// m_total rows (rows past the batch must read as zeros).  dw: [taps][ldout][kin] fp32.
+// Tensor maps of one weight-gradient problem: G [rows][ldout] and X [rows][kin] with box [64][64] and EXACTLY `rows`
+// rows (rows past the batch must read as zeros), plus G with a box of win_rows rows (the shared window, wgrad.cu).
+struct WgradMaps {
+    CUtensorMap g, gw, x;
+    int win_rows;
+};
+int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, int ldout, int kin, int taps, const int* off);
+// dw: [taps][ldout][kin] fp32.
 // db (optional, needs args.bias_scratch and kin <= 240): [ldout] fp32 bias gradient = sum over all rows of G
-int wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, WgradArgs args, float* dw, float* db, cudaStream_t stream);
+int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cudaStream_t stream);
 
 }  // namespace ag
