@@ -75,19 +75,29 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     __syncthreads();
     const int groups = ld / 8;  // 16-byte groups per row; lanes >= groups idle (ld <= 256)
     const float b0 = bias[0];
-    for (int p = warp; p < pts; p += nwarps) {
-        int x = p / S, y = p - x * S;
-        const bf16* row = X + ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld;
-        float acc = 0.f;
-        if (lane < groups) {
-            uint4 v = *reinterpret_cast<const uint4*>(row + lane * 8);
-            const bf16* vb = reinterpret_cast<const bf16*>(&v);
+    constexpr int U = 5;  // rows in flight per warp: the loop is bound by load latency, not bandwidth
+    for (int p0 = warp; p0 < pts; p0 += nwarps * U) {
+        uint4 v[U];
 #pragma unroll
-            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * s_w[lane * 8 + j];
+        for (int u = 0; u < U; u++) {
+            const int p = p0 + u * nwarps;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (p < pts && lane < groups) {
+                const int x = p / S, y = p - x * S;
+                v[u] = *reinterpret_cast<const uint4*>(X + ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld + lane * 8);
+            }
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) s_logit[p] = acc + b0 + (pos_bias ? pos_bias[p] : 0.f);
+        for (int u = 0; u < U; u++) {
+            const int p = p0 + u * nwarps;
+            const bf16* vb = reinterpret_cast<const bf16*>(&v[u]);
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * s_w[(lane * 8 + j) & 255];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0 && p < pts) s_logit[p] = acc + b0 + (pos_bias ? pos_bias[p] : 0.f);
+        }
     }
     __syncthreads();
     // softmax over pts (block reductions)
@@ -118,14 +128,22 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     if (!labels) return;
 
     const int label = labels[img];
-    if (threadIdx.x == 0) {
-        // accuracy: first maximum, as numpy/Theano argmax
-        int best = 0;
-        float bv = s_logit[0];
-        for (int p = 1; p < pts; p++) if (s_logit[p] > bv) { bv = s_logit[p]; best = p; }
-        float pl = fminf(fmaxf(s_logit[label], 1e-7f), 1.f - 1e-7f);
-        atomicAdd(&loss_acc[0], -logf(pl));
-        atomicAdd(&loss_acc[1], best == label ? 1.f : 0.f);
+    if (warp == 0) {
+        // accuracy: first maximum, as numpy/Theano argmax (ties go to the lowest index)
+        int best = 0x7fffffff;
+        float bv = -INFINITY;
+        for (int p = lane; p < pts; p += 32) if (s_logit[p] > bv) { bv = s_logit[p]; best = p; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+            if (ov > bv || (ov == bv && ob < best)) { bv = ov; best = ob; }
+        }
+        if (lane == 0) {
+            float pl = fminf(fmaxf(s_logit[label], 1e-7f), 1.f - 1e-7f);
+            atomicAdd(&loss_acc[0], -logf(pl));
+            atomicAdd(&loss_acc[1], best == label ? 1.f : 0.f);
+        }
     }
     __syncthreads();
     // dlogit in place
@@ -144,22 +162,36 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     __syncthreads();
     // G rows and dw partial
     float dw[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int p = warp; p < pts; p += nwarps) {
-        int x = p / S, y = p - x * S;
-        size_t roff = ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld;
-        float d = s_logit[p];
-        if (lane < groups) {
-            uint4 v = *reinterpret_cast<const uint4*>(X + roff + lane * 8);
-            const bf16* vb = reinterpret_cast<const bf16*>(&v);
-            uint4 o;
-            bf16* ob = reinterpret_cast<bf16*>(&o);
+    for (int p0 = warp; p0 < pts; p0 += nwarps * U) {
+        uint4 v[U];
+        size_t roff[U];
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                float xv = __bfloat162float(vb[j]);
-                dw[j] += d * xv;
-                ob[j] = __float2bfloat16(xv > 0.f ? d * s_w[lane * 8 + j] : 0.f);
+        for (int u = 0; u < U; u++) {
+            const int p = p0 + u * nwarps;
+            v[u] = make_uint4(0, 0, 0, 0);
+            roff[u] = 0;
+            if (p < pts && lane < groups) {
+                const int x = p / S, y = p - x * S;
+                roff[u] = ((size_t)img * L.img_stride + (size_t)x * L.row_stride + y) * ld + lane * 8;
+                v[u] = *reinterpret_cast<const uint4*>(X + roff[u]);
             }
-            *reinterpret_cast<uint4*>(G + roff + lane * 8) = o;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int p = p0 + u * nwarps;
+            if (p < pts && lane < groups) {
+                const float d = s_logit[p];
+                const bf16* vb = reinterpret_cast<const bf16*>(&v[u]);
+                uint4 o;
+                bf16* ob = reinterpret_cast<bf16*>(&o);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    float xv = __bfloat162float(vb[j]);
+                    dw[j] += d * xv;
+                    ob[j] = __float2bfloat16(xv > 0.f ? d * s_w[lane * 8 + j] : 0.f);
+                }
+                *reinterpret_cast<uint4*>(G + roff[u]) = o;
+            }
         }
     }
     if (lane < groups) {
@@ -182,15 +214,20 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     }
 }
 
-// sums the per-image head partials [n][625] -> grads: dw[ld], db[1], dpos[pts]
-__global__ void head_reduce_kernel(const float* __restrict__ partial, int n, int ld, int pts, float* __restrict__ dw,
-                                   float* __restrict__ db, float* __restrict__ dpos) {
+// sums the per-image head partials [n][625] -> grads: dw[ld], db[1], dpos[pts].  One warp per output: lanes take every
+// 32nd image, then a fixed-order shuffle tree (deterministic).
+__global__ void __launch_bounds__(256)
+head_reduce_kernel(const float* __restrict__ partial, int n, int ld, int pts, float* __restrict__ dw, float* __restrict__ db,
+                   float* __restrict__ dpos) {
     pdl_trigger();
     pdl_wait();
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= 256 + 1 + 368) return;
     float s = 0.f;
-    for (int k = 0; k < n; k++) s += partial[(size_t)k * 625 + i];
+    for (int k = lane; k < n; k += 32) s += partial[(size_t)k * 625 + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane != 0) return;
     if (i < 256) { if (i < ld) dw[i] = s; }
     else if (i == 256) db[0] = s;
     else if (i - 257 < pts && dpos) dpos[i - 257] = s;
@@ -296,65 +333,81 @@ __global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restr
     if (lane == 0) db[c] = t;
 }
 
-// SGD with momentum (Keras 1.0 SGD.get_updates: v = momentum*v - lr*g; w += v), one launch per layer.
+// SGD with momentum (Keras 1.0 SGD.get_updates: v = momentum*v - lr*g; w += v) over EVERY parameter in one launch.
 // Refreshes the bf16 operand copies: wf [tap][co][ci] (forward) and wb [tap][ci][co] (data gradient).
-// One CTA per 32x32 (co, ci) tile of one tap: coalesced fp32 update along ci, the bf16 tile goes through shared memory
-// so the transposed copy wb is written coalesced along co as well.  ldout and kin are multiples of 64.
+// One CTA per 32x32 (co, ci) tile of one tap of one layer: coalesced fp32 update along ci, the bf16 tile goes through
+// shared memory so the transposed copy wb is written coalesced along co as well.  ldout and kin are multiples of 64.
+// The CTA that owns a layer's first tile also updates its bias; the last few CTAs take the flat (head) parameters.
+struct SgdLayer {
+    float *w, *vel, *b, *bvel;
+    const float *g, *gb;
+    bf16 *wf, *wb;
+    int taps, ldout, kin;
+    int tile0;  // first global tile index of this layer
+};
+struct SgdFlat {
+    float *w, *vel;
+    const float* g;
+    int count;
+};
+constexpr int kSgdMaxFlat = 4;
+struct SgdFlats { SgdFlat f[kSgdMaxFlat]; int n; };
+
 __global__ void __launch_bounds__(256)
-sgd_conv_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, int taps, int ldout, int kin, float lr,
-                float momentum, float gscale, bf16* __restrict__ wf, bf16* __restrict__ wb, float* __restrict__ b,
-                float* __restrict__ bvel, const float* __restrict__ gb, int nbias) {
+sgd_all_kernel(const SgdLayer* __restrict__ layers, int n_layers, int total_tiles, const SgdFlats flats, float lr, float momentum, float gscale) {
     pdl_trigger();
     pdl_wait();
     __shared__ bf16 tile[32][33];
-    const int tiles_ci = kin / 32, tiles_co = ldout / 32;
-    const int n_tiles = taps * tiles_co * tiles_ci;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-    for (int tidx = blockIdx.x; tidx < n_tiles; tidx += gridDim.x) {
-        const int t = tidx / (tiles_co * tiles_ci);
-        const int rem = tidx - t * tiles_co * tiles_ci;
+    for (int tidx = blockIdx.x; tidx < total_tiles + flats.n; tidx += gridDim.x) {
+        if (tidx >= total_tiles) {  // a flat parameter vector
+            const SgdFlat& f = flats.f[tidx - total_tiles];
+            for (int i = threadIdx.x; i < f.count; i += blockDim.x) {
+                float v = -lr * f.g[i] * gscale;
+                if (momentum != 0.f) { v += momentum * f.vel[i]; f.vel[i] = v; }
+                f.w[i] += v;
+            }
+            continue;
+        }
+        int l = 0;
+        while (l + 1 < n_layers && layers[l + 1].tile0 <= tidx) l++;
+        const SgdLayer L = layers[l];
+        const int local = tidx - L.tile0;
+        const int tiles_ci = L.kin / 32, tiles_co = L.ldout / 32;
+        const int t = local / (tiles_co * tiles_ci);
+        const int rem = local - t * tiles_co * tiles_ci;
         const int co0 = (rem / tiles_ci) * 32, ci0 = (rem % tiles_ci) * 32;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int co = co0 + ty + 8 * k;
-            const size_t i = ((size_t)t * ldout + co) * kin + ci0 + tx;
-            float v = -lr * g[i] * gscale;
-            if (momentum != 0.f) { v += momentum * vel[i]; vel[i] = v; }  // plain SGD never touches the velocity
-            const float nw = w[i] + v;
-            w[i] = nw;
+            const size_t i = ((size_t)t * L.ldout + co) * L.kin + ci0 + tx;
+            float v = -lr * L.g[i] * gscale;
+            if (momentum != 0.f) { v += momentum * L.vel[i]; L.vel[i] = v; }  // plain SGD never touches the velocity
+            const float nw = L.w[i] + v;
+            L.w[i] = nw;
             const bf16 h = __float2bfloat16(nw);
-            wf[i] = h;
+            L.wf[i] = h;
             tile[ty + 8 * k][tx] = h;
         }
-        if (wb) {
-            __syncthreads();
+        __syncthreads();
+        if (L.wb) {
 #pragma unroll
             for (int k = 0; k < 4; k++) {
                 const int ci = ci0 + ty + 8 * k;
-                wb[((size_t)t * kin + ci) * ldout + co0 + tx] = tile[tx][ty + 8 * k];
+                L.wb[((size_t)t * L.kin + ci) * L.ldout + co0 + tx] = tile[tx][ty + 8 * k];
             }
-            __syncthreads();
         }
-    }
-    if (blockIdx.x == 0) {
-        for (int j = threadIdx.x; j < nbias; j += blockDim.x) {
-            float v = -lr * gb[j] * gscale;
-            if (momentum != 0.f) { v += momentum * bvel[j]; bvel[j] = v; }
-            b[j] += v;
+        __syncthreads();
+        if (local == 0) {
+            for (int j = threadIdx.x; j < L.ldout; j += blockDim.x) {
+                float v = -lr * L.gb[j] * gscale;
+                if (momentum != 0.f) { v += momentum * L.bvel[j]; L.bvel[j] = v; }
+                L.b[j] += v;
+            }
         }
     }
 }
-__global__ void sgd_flat_kernel(float* __restrict__ w, float* __restrict__ vel, const float* __restrict__ g, size_t count, float lr,
-                                float momentum, float gscale) {
-    pdl_trigger();
-    pdl_wait();
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
-        float v = momentum * vel[i] - lr * g[i] * gscale;
-        vel[i] = v;
-        w[i] += v;
-    }
-}
-// debug / test: padded-pixel rows -> fp32 [n][C][S][S]
+
 __global__ void unpack_rows_kernel(const bf16* __restrict__ rows, int n, int C, int S, PixelLayout L, int ld, float* __restrict__ out) {
     size_t total = (size_t)n * C * S * S;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -418,6 +471,8 @@ struct ag_net {
     int wgrad_n = -1;
     int colsum_blocks = 0;
     long long iterations = 0;
+    void* sgd_table = nullptr;      // device copy of the SGD kernel's per-layer table
+    int sgd_tiles = 0;
 };
 
 namespace ag {
@@ -548,6 +603,18 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
             if (!rc && c.pair_bwd) rc = make_tmap_2d(&c.tm_wb_half, c.wb, (uint64_t)c.taps * c.kin, c.ldout, c.nin / 2);
         }
     }
+    if (!rc) {  // the SGD kernel's layer table
+        std::vector<SgdLayer> tab(n_conv);
+        int tile0 = 0;
+        for (int l = 0; l < n_conv; l++) {
+            ConvLayer& c = net->L[l];
+            tab[l] = SgdLayer{c.w, c.vw, c.b, c.vb, c.gw, c.gb, c.wf, c.wb, c.taps, c.ldout, c.kin, tile0};
+            tile0 += c.taps * (c.ldout / 32) * (c.kin / 32);
+        }
+        net->sgd_tiles = tile0;
+        { unsigned char* t = nullptr; rc = dev_alloc(&t, sizeof(SgdLayer) * n_conv); net->sgd_table = t; }
+        if (!rc && cudaMemcpy(net->sgd_table, tab.data(), sizeof(SgdLayer) * n_conv, cudaMemcpyHostToDevice) != cudaSuccess) rc = AG_ECUDA;
+    }
     if (!rc) rc = dev_alloc(&net->hw, 256);
     if (!rc) rc = dev_alloc(&net->hb, 4);
     if (!rc) rc = dev_alloc(&net->hpos, 368);
@@ -580,7 +647,7 @@ void ag_net_destroy(ag_net* net) {
     float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
                   net->head_partial, net->colsum_part, net->wgrad_scratch, net->grads};
     for (float* p : f) cudaFree(p);
-    cudaFree(net->x0); cudaFree(net->x0_grad); cudaFree(net->gbuf[0]); cudaFree(net->gbuf[1]);
+    cudaFree(net->sgd_table); cudaFree(net->x0); cudaFree(net->x0_grad); cudaFree(net->gbuf[0]); cudaFree(net->gbuf[1]);
     delete net;
 }
 
@@ -750,7 +817,7 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
     launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
                                                   d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr);
     AG_LAUNCH_CHECK("policy_head_kernel");
-    launch_k(head_reduce_kernel, dim3((625 + 127) / 128), dim3(128), 0, st, net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
+    launch_k(head_reduce_kernel, dim3((625 + 7) / 8), dim3(256), 0, st, net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
                                                         net->use_pos_bias ? net->g_hpos : nullptr);
     AG_LAUNCH_CHECK("head_reduce_kernel");
     return AG_OK;
@@ -820,21 +887,16 @@ int ag_net_grads(ag_net* net, float** d_grads, long long* count, long long* h_of
 // first (1/world_size after a sum all-reduce).  Also refreshes the bf16 operand copies.
 int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    for (int l = 0; l < net->n_conv; l++) {
-        ConvLayer& c = net->L[l];
-        int tiles = c.taps * (c.ldout / 32) * (c.kin / 32);
-        launch_k(sgd_conv_kernel, dim3(tiles < sm_count() * 8 ? tiles : sm_count() * 8), dim3(256), 0, st, c.w, c.vw, c.gw, c.taps, c.ldout, c.kin, lr, momentum,
-                                                                                        grad_scale, c.wf, c.wb, c.b, c.vb, c.gb, c.ldout);
-        AG_LAUNCH_CHECK("sgd_conv_kernel");
-    }
-    launch_k(sgd_flat_kernel, dim3(1), dim3(256), 0, st, net->hw, net->vhw, net->g_hw, 256, lr, momentum, grad_scale);
-    AG_LAUNCH_CHECK("sgd_flat_kernel");
-    launch_k(sgd_flat_kernel, dim3(1), dim3(32), 0, st, net->hb, net->vhb, net->g_hb, 1, lr, momentum, grad_scale);
-    AG_LAUNCH_CHECK("sgd_flat_kernel");
-    if (net->use_pos_bias) {
-        launch_k(sgd_flat_kernel, dim3(1), dim3(256), 0, st, net->hpos, net->vhpos, net->g_hpos, (size_t)net->board * net->board, lr, momentum, grad_scale);
-        AG_LAUNCH_CHECK("sgd_flat_kernel");
-    }
+    SgdFlats flats;
+    memset(&flats, 0, sizeof(flats));
+    flats.f[0] = SgdFlat{net->hw, net->vhw, net->g_hw, 256};
+    flats.f[1] = SgdFlat{net->hb, net->vhb, net->g_hb, 1};
+    flats.n = 2;
+    if (net->use_pos_bias) flats.f[flats.n++] = SgdFlat{net->hpos, net->vhpos, net->g_hpos, net->board * net->board};
+    const int total = net->sgd_tiles + flats.n;
+    launch_k(sgd_all_kernel, dim3(total < sm_count() * 8 ? total : sm_count() * 8), dim3(256), 0, st, (const SgdLayer*)net->sgd_table, net->n_conv,
+             net->sgd_tiles, flats, lr, momentum, grad_scale);
+    AG_LAUNCH_CHECK("sgd_all_kernel");
     net->iterations++;
     return AG_OK;
 }

@@ -27,13 +27,11 @@ namespace ag {
 
 namespace {
 
-constexpr int kMaxStages = 6;
-constexpr int kChunkBytes = 64 * 128;  // [64 pixel rows][64 bf16]
+constexpr int kMaxStages = 8;
 constexpr int kThreads = 192;
 constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns between the CTA's two accumulators
 constexpr int kASlots = 4;       // 64-row slots of dW rows per CTA: two accumulators x two halves
-constexpr int kARegion = kASlots * kChunkBytes;  // bytes of a stage set aside for G
 
 struct __align__(8) WgradBarriers {
     uint64_t full[kMaxStages];
@@ -68,6 +66,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
     const int xchunks = p.kin / 64;
     const int cochunks = p.ldout / 64;
+    const int chunk_bytes = p.krows * 128;          // one TMA box: [krows pixel rows][64 bf16]
+    const int a_region = kASlots * chunk_bytes;     // bytes of a stage set aside for G
     const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const bool taps_in_n = p.tpg > 1;
     const bool windowed = p.win_rows > 0;
@@ -81,15 +81,15 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     const bool with_bias = p.bias_scratch != nullptr && (!taps_in_n || grp == p.groups - 1);  // the last group has room for the ones
     const int b_chunks = nb * xchunks;
     // stage = G region (4 slots' worth) | X chunks | a chunk of ones: one more B column that is 1 for every pixel row
-    const int stage_bytes = kARegion + (taps_in_n ? p.tpg * xchunks : xchunks + (p.bias_scratch ? 1 : 0)) * kChunkBytes;
-    const int ones_off = kARegion + b_chunks * kChunkBytes;
+    const int stage_bytes = a_region + (taps_in_n ? p.tpg * xchunks : xchunks + (p.bias_scratch ? 1 : 0)) * chunk_bytes;
+    const int ones_off = a_region + b_chunks * chunk_bytes;
     const int acc_cols = b_chunks * 64;
     const int umma_n = acc_cols + (with_bias ? 16 : 0);
     WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
     WgradPlan* plan = reinterpret_cast<WgradPlan*>(bars + 1);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
-    const int kb_total = (p.m_total + 63) / 64;
+    const int kb_total = (p.m_total + p.krows - 1) / p.krows;
     const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
 
     pdl_trigger();
@@ -101,7 +101,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         tc::tma_prefetch_desc(&tmap_gw);
         tc::tma_prefetch_desc(&tmap_x);
         // ---- the plan
-        const int win_bytes = windowed ? ((p.win_rows * 128 + 1023) & ~1023) : kChunkBytes;
+        const int win_bytes = windowed ? ((p.win_rows * 128 + 1023) & ~1023) : chunk_bytes;
         int cc[kASlots], shift[kASlots], win_of[kASlots];
         int n_win = 0;
         for (int i = 0; i < kASlots; i++) {
@@ -136,7 +136,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     if (with_bias) {  // the ones chunk of every stage (all elements equal, so the swizzle does not matter)
         for (int s = 0; s < kStages; s++) {
             uint32_t* ones = reinterpret_cast<uint32_t*>(base + s * stage_bytes + ones_off);
-            for (int i = threadIdx.x; i < kChunkBytes / 4; i += kThreads) ones[i] = 0x3F803F80u;  // bf16 1.0 x2
+            for (int i = threadIdx.x; i < chunk_bytes / 4; i += kThreads) ones[i] = 0x3F803F80u;  // bf16 1.0 x2
         }
         tc::fence_proxy_async();  // generic-proxy writes, read by the tensor core
     }
@@ -150,7 +150,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
         const int n_win = plan->n_win;
         const CUtensorMap* gmap = windowed ? &tmap_gw : &tmap_g;
-        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : kChunkBytes) + b_chunks * kChunkBytes);
+        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : chunk_bytes) + b_chunks * chunk_bytes);
         int stage = 0;
         uint32_t phase = 0;
         for (int kb = kb0; kb < kb1; kb++) {
@@ -158,13 +158,13 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (tc::elect_one()) {
                 uint8_t* s = base + stage * stage_bytes;
                 tc::mbar_expect_tx(&bars->full[stage], tx_bytes);
-                const int m0 = kb * 64;
+                const int m0 = kb * p.krows;
                 for (int w = 0; w < n_win; w++)  // rows outside the tensor read as zeros
                     tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
                 for (int j = 0; j < nb; j++) {
                     const int xrow = taps_in_n ? m0 + p.off[grp * p.tpg + j] : m0;
                     for (int c = 0; c < xchunks; c++)
-                        tc::tma_load_2d(s + kARegion + (j * xchunks + c) * kChunkBytes, &tmap_x, &bars->full[stage], c * 64, xrow);
+                        tc::tma_load_2d(s + a_region + (j * xchunks + c) * chunk_bytes, &tmap_x, &bars->full[stage], c * 64, xrow);
                 }
             }
             __syncwarp();
@@ -178,8 +178,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         for (int a = 0; a < 2; a++) {
             const int lo = plan->lo[a], hi = plan->hi[a];
             a_off[a] = (uint32_t)max(plan->slot_off[lo], 0);
-            a_lbo[a] = hi >= 0 ? (uint32_t)(plan->slot_off[hi] - plan->slot_off[lo]) : (uint32_t)kChunkBytes;
+            a_lbo[a] = hi >= 0 ? (uint32_t)(plan->slot_off[hi] - plan->slot_off[lo]) : (uint32_t)chunk_bytes;
         }
+        const int ksteps = p.krows / 16;
         int stage = 0;
         uint32_t phase = 0;
         bool ready = false;
@@ -194,9 +195,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     adesc0 |= (uint64_t)(((s + a_off[0]) >> 7) & 7) << 49;
                     adesc1 |= (uint64_t)(((s + a_off[1]) >> 7) & 7) << 49;
                 }
-                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + kARegion, kChunkBytes);
-#pragma unroll
-                for (int k = 0; k < 4; k++) {  // 16 pixel rows per UMMA: +2048 B
+                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
+#pragma unroll 4
+                for (int k = 0; k < ksteps; k++) {  // 16 pixel rows per UMMA: +2048 B
                     tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
                     if (second)
                         tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
@@ -318,25 +319,34 @@ static int wgrad_tiling(int taps, int ldout, int kin, int* tpg, int* groups) {
     return (taps * (ldout / 64) + kASlots - 1) / kASlots;
 }
 
-static int wgrad_stage_bytes(int taps, int kin, bool with_bias) {
-    int tpg, groups;
-    wgrad_tiling(taps, 64, kin, &tpg, &groups);
-    return kARegion + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0)) * kChunkBytes;
+// pixel rows per pipeline stage (one TMA box per operand chunk).  Measured (3x3, 192 channels, batch 256): 64 rows x 3
+// stages 65.9 us, 32 rows x 6 stages 83 us: the smaller boxes cost more than the deeper pipeline gains.
+static int wgrad_krows() {
+    static int v = 0;
+    if (!v) { const char* e = getenv("AG_WGRAD_KROWS"); v = (e && atoi(e) == 32) ? 32 : 64; }
+    return v;
 }
 
-static int wgrad_stages(int taps, int kin, bool with_bias) {
-    int s = (227 * 1024 - 1024 - (int)sizeof(WgradBarriers) - (int)sizeof(WgradPlan) - 64) / wgrad_stage_bytes(taps, kin, with_bias);
+static int wgrad_stage_bytes(int taps, int kin, bool with_bias, int krows) {
+    int tpg, groups;
+    wgrad_tiling(taps, 64, kin, &tpg, &groups);
+    return (kASlots + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0))) * krows * 128;
+}
+
+static int wgrad_stages(int taps, int kin, bool with_bias, int krows) {
+    int s = (227 * 1024 - 1024 - (int)sizeof(WgradBarriers) - (int)sizeof(WgradPlan) - 64) / wgrad_stage_bytes(taps, kin, with_bias, krows);
     return s > kMaxStages ? kMaxStages : s;
 }
 
-size_t wgrad_smem_bytes(int taps, int kin, bool with_bias) {
-    return 1024 + (size_t)wgrad_stages(taps, kin, with_bias) * wgrad_stage_bytes(taps, kin, with_bias) + sizeof(WgradBarriers) + sizeof(WgradPlan) + 64;
+static size_t wgrad_smem_bytes(int taps, int kin, bool with_bias, int krows) {
+    return 1024 + (size_t)wgrad_stages(taps, kin, with_bias, krows) * wgrad_stage_bytes(taps, kin, with_bias, krows) + sizeof(WgradBarriers) +
+           sizeof(WgradPlan) + 64;
 }
 
-// Rows of the G box shared by the taps of one co chunk (0 = every slot fetches its own 64 rows): 64 + the largest
+// Rows of the G box shared by the taps of one co chunk (0 = every slot fetches its own krows rows): krows + the largest
 // shift distance inside any four consecutive taps.  A CTA holds at most two such boxes (taps >= 3), which must fit
 // the G region of a stage.
-int wgrad_window_rows(int taps, const int* off, int kin) {
+static int wgrad_window_rows(int taps, const int* off, int kin, int krows) {
     int tpg, groups;
     wgrad_tiling(taps, 64, kin, &tpg, &groups);
     static int enabled = -1;
@@ -348,16 +358,17 @@ int wgrad_window_rows(int taps, const int* off, int kin) {
         if (off[u] < off[t]) return 0;  // shifts must grow with the tap
         if (off[u] - off[t] > span) span = off[u] - off[t];
     }
-    int rows = (64 + span + 7) & ~7;
-    if (rows > 256 || 2 * ((rows * 128 + 1023) & ~1023) > kARegion) return 0;
+    int rows = (krows + span + 7) & ~7;
+    if (rows > 256 || 2 * ((rows * 128 + 1023) & ~1023) > kASlots * krows * 128) return 0;
     return rows;
 }
 
 int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, int ldout, int kin, int taps, const int* off) {
-    int rc = make_tmap_2d(&m->g, g, rows, ldout, 64);
-    if (!rc) rc = make_tmap_2d(&m->x, x, rows, kin, 64);
-    m->win_rows = wgrad_window_rows(taps, off, kin);
-    if (!rc) rc = make_tmap_2d(&m->gw, g, rows, ldout, m->win_rows ? m->win_rows : 64);
+    m->krows = wgrad_krows();
+    int rc = make_tmap_2d(&m->g, g, rows, ldout, m->krows);
+    if (!rc) rc = make_tmap_2d(&m->x, x, rows, kin, m->krows);
+    m->win_rows = wgrad_window_rows(taps, off, kin, m->krows);
+    if (!rc) rc = make_tmap_2d(&m->gw, g, rows, ldout, m->win_rows ? m->win_rows : m->krows);
     return rc;
 }
 
@@ -387,14 +398,15 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     static size_t configured = 0;
     if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
     if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
-    size_t smem = wgrad_smem_bytes(args.taps, args.kin, args.bias_scratch != nullptr);
+    args.krows = maps.krows;
+    size_t smem = wgrad_smem_bytes(args.taps, args.kin, args.bias_scratch != nullptr, args.krows);
     if (smem > 227 * 1024) { set_error("wgrad: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AG_WGRAD_DEBUG"); dbg = e ? atoi(e) : 0; } args.debug = dbg; }
-    const int stages = wgrad_stages(args.taps, args.kin, args.bias_scratch != nullptr);
+    const int stages = wgrad_stages(args.taps, args.kin, args.bias_scratch != nullptr, args.krows);
     if (stages < 2) { set_error("wgrad: shared memory fits only %d stage(s)", stages); return AG_EINVAL; }
     args.win_rows = maps.win_rows;
     launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, maps.g, maps.gw, maps.x, args, stages);

@@ -21,18 +21,18 @@ struct WgradArgs {
     int tpg;       // filled by wgrad_launch: taps per B operand (1 = shifted-G tiling, >= 2 = taps-in-N tiling, see wgrad.cu)
     int groups;    // filled by wgrad_launch: tap groups (taps-in-N tiling)
     int win_rows;  // filled by wgrad_launch from the maps
+    int krows;     // filled by wgrad_launch from the maps: pixel rows per pipeline stage (32 or 64)
     int debug;     // experiments only (AG_WGRAD_DEBUG)
     float* scratch;  // [splits][taps*ldout][kin] fp32
     float* bias_scratch;  // nullptr, or [splits][ldout] fp32: column sums of G (the bias gradient) ride along as one more B column
 };
 
-size_t wgrad_smem_bytes(int taps, int kin, bool with_bias);
 int wgrad_plan_splits(int taps, int ldout, int kin, int m_total);
-// Tensor maps of one weight-gradient problem: G [rows][ldout] and X [rows][kin] with box [64][64] and EXACTLY `rows`
+// Tensor maps of one weight-gradient problem: G [rows][ldout] and X [rows][kin] with box [krows][64] and EXACTLY `rows`
 // rows (rows past the batch must read as zeros), plus G with a box of win_rows rows (the shared window, wgrad.cu).
 struct WgradMaps {
     CUtensorMap g, gw, x;
-    int win_rows;
+    int win_rows, krows;
 };
 int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, int ldout, int kin, int taps, const int* off);
 // dw: [taps][ldout][kin] fp32.
