@@ -118,3 +118,67 @@ class SLTrainer(object):
         t = t.cpu().numpy()
         c = float(cnt.cpu()[0])
         return float(t[0]) / max(c, 1.0), float(t[1]) / max(c, 1.0)
+
+
+class HostFeeder(object):
+    """Feeds an SLTrainer from a dataset that lives in HOST memory (numpy arrays, or HDF5 datasets read into them):
+    the trainer-side half of the reference's `shuffled_hdf5_batch_generator` + `fit_generator` loop (spt.py:18-40,
+    207-213) when the data does not fit, or is not wanted, on the device.
+
+    Per step: gather the minibatch into one of two pinned staging buffers, copy it to the device on a copy stream,
+    augment + train on the compute stream, and copy the running (loss sum, correct count) back.  Nothing waits for the
+    step just queued: the copy of batch k overlaps the kernels of step k-1, and `step()` returns the metrics of the
+    PREVIOUS step (None on the first call); `flush()` returns the last ones.
+    """
+
+    def __init__(self, trainer, h_states, h_actions, batch):
+        import torch
+        self.torch, self.trainer = torch, trainer
+        self.h_states, self.h_actions, self.batch = h_states, h_actions, int(batch)
+        shape = (self.batch,) + tuple(h_states.shape[1:])
+        self.pin_x = [torch.empty(shape, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.pin_a = [torch.empty((self.batch, 2), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.pin_m = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.dx = [torch.empty(shape, dtype=torch.uint8, device="cuda") for _ in range(2)]
+        self.da = [torch.empty((self.batch, 2), dtype=torch.uint8, device="cuda") for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream()
+        self.ev_copied = [torch.cuda.Event() for _ in range(2)]
+        self.ev_consumed = [torch.cuda.Event() for _ in range(2)]
+        self.ev_metrics = [torch.cuda.Event() for _ in range(2)]
+        self.ident = np.arange(self.batch)
+        self.k = 0
+        self.h2d_bytes = self.pin_x[0].numel() + self.pin_a[0].numel()
+        self.d2h_bytes = 8
+
+    def _metrics(self, slot):
+        self.ev_metrics[slot].synchronize()
+        return float(self.pin_m[slot][0]), float(self.pin_m[slot][1])
+
+    def step(self, index, transform):
+        torch = self.torch
+        slot = self.k & 1
+        if len(index) != self.batch:
+            raise ValueError("HostFeeder was built for minibatches of %d, got %d" % (self.batch, len(index)))
+        if self.k >= 2:
+            self.ev_copied[slot].synchronize()      # the staging buffer's previous copy has left the host
+        np.take(self.h_states, index, axis=0, out=self.pin_x[slot].numpy())
+        np.take(self.h_actions, index, axis=0, out=self.pin_a[slot].numpy())
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self.copy_stream):
+            if self.k >= 2:
+                self.copy_stream.wait_event(self.ev_consumed[slot])  # the step that read dx[slot] two steps ago
+            self.dx[slot].copy_(self.pin_x[slot], non_blocking=True)
+            self.da[slot].copy_(self.pin_a[slot], non_blocking=True)
+            self.ev_copied[slot].record(self.copy_stream)
+        main.wait_event(self.ev_copied[slot])
+        x, y = self.trainer.assemble(self.dx[slot], self.da[slot], self.ident, transform)
+        self.ev_consumed[slot].record(main)
+        self.trainer.step(x, y)
+        self.pin_m[slot].copy_(self.trainer.loss_acc, non_blocking=True)
+        self.ev_metrics[slot].record(main)
+        self.k += 1
+        return self._metrics(slot ^ 1) if self.k >= 2 else None
+
+    def flush(self):
+        """metrics after the last queued step (synchronises with it)"""
+        return self._metrics((self.k - 1) & 1) if self.k else None
