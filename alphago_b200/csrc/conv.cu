@@ -327,6 +327,147 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     }
 }
 
+// ---- CTA-pair variant with a shared activation window.  The pair kernel above is bound by shared-memory bandwidth, not by
+// the tensor cores: per 64-channel slice a CTA's smem takes 28 KB of TMA writes and 28 KB of UMMA reads for 4 UMMAs whose
+// tensor-core floor is 4 x 96 cycles (N = 192) -- 146 B/cycle against the SM's 128.  But the nine (or 25) taps of one
+// channel slice read the SAME activation rows shifted by a few pixel rows, and the 128-byte swizzle is a function of the
+// shared-memory address, so a K-major UMMA descriptor may start at any 128-byte row of a larger box.  Hence: per channel
+// slice ONE box of 128 + 2*halo rows (the "window", halo = largest |tap shift|) is fetched, and every tap's UMMAs start at
+// row halo + shift(tap) of it.  Activation traffic (L2 -> smem) drops by the number of taps; weights stream through their
+// own ring.  Loop order: channel slice outer, tap inner.
+constexpr int kWinSlots = 2;
+constexpr int kMaxBStages = 12;
+
+struct __align__(8) WinBarriers {
+    uint64_t a_full[kWinSlots];
+    uint64_t a_empty[kWinSlots];
+    uint64_t b_full[kMaxBStages];
+    uint64_t b_empty[kMaxBStages];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint32_t tmem_base;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_gemm_win_kernel(const __grid_constant__ CUtensorMap tmap_aw, const __grid_constant__ CUtensorMap tmap_bh, const ConvArgs p,
+                     const int kBStages) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    const int half_n = p.n / 2;
+    const int b_bytes = half_n * 128;
+    const int win_box = p.win_rows * 128;                 // bytes one window box brings
+    const int win_bytes = (win_box + 1023) & ~1023;       // its slot
+    uint8_t* b_base = base + kWinSlots * win_bytes;
+    WinBarriers* bars = reinterpret_cast<WinBarriers*>(b_base + kBStages * b_bytes);
+    float* s_bias = reinterpret_cast<float*>(bars + 1);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int n_pairs = (p.m_total + 2 * kTileM - 1) / (2 * kTileM);
+    const int n_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
+
+    pdl_trigger();
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kWinSlots; s++) { tc::mbar_init(&bars->a_full[s], 1); tc::mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < kBStages; s++) { tc::mbar_init(&bars->b_full[s], 1); tc::mbar_init(&bars->b_empty[s], 1); }
+        for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 256); }
+        tc::fence_mbar_init();
+        tc::tma_prefetch_desc(&tmap_aw);
+        tc::tma_prefetch_desc(&tmap_bh);
+    }
+    if (warp == 1) tc::tmem_alloc_pair(&bars->tmem_base, kTmemCols);
+    pdl_wait();
+    for (int i = threadIdx.x; i < p.n; i += kThreads) s_bias[i] = p.bias ? p.bias[i] : 0.f;
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // both CTAs' barriers exist before anyone signals across the pair
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ===== TMA producer (each CTA: its own 128 rows' window, its half of the weight rows; the leader's barriers count both)
+        int ai = 0, bi = 0;
+        uint32_t aph = 0, bph = 0;
+        for (int pair = cluster_id; pair < n_pairs; pair += n_clusters) {
+            const int m0 = pair * 2 * kTileM + (int)rank * kTileM;
+            for (int kc = 0; kc < p.kchunks; kc++) {
+                tc::mbar_wait(&bars->a_empty[ai], aph ^ 1);
+                if (tc::elect_one()) {
+                    if (leader) tc::mbar_expect_tx(&bars->a_full[ai], 2 * (uint32_t)win_box);
+                    tc::tma_load_2d_pair(base + ai * win_bytes, &tmap_aw, &bars->a_full[ai], kc * 64, m0 - p.halo);
+                }
+                __syncwarp();
+                if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
+                for (int t = 0; t < p.taps; t++) {
+                    tc::mbar_wait(&bars->b_empty[bi], bph ^ 1);
+                    if (tc::elect_one()) {
+                        if (leader) tc::mbar_expect_tx(&bars->b_full[bi], 2 * (uint32_t)b_bytes);
+                        tc::tma_load_2d_pair(b_base + bi * b_bytes, &tmap_bh, &bars->b_full[bi], kc * 64, t * p.b_tap_rows + (int)rank * half_n);
+                    }
+                    __syncwarp();
+                    if (++bi == kBStages) { bi = 0; bph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            const uint32_t idesc = tc::idesc_bf16(2 * kTileM, p.n, 0, 0);
+            int ai = 0, bi = 0, it = 0;
+            uint32_t aph = 0, bph = 0;
+            bool ready = false;
+            for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
+                const int buf = it & 1;
+                tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t d_tmem = tmem_base + buf * kAccStride;
+                for (int kc = 0; kc < p.kchunks; kc++) {
+                    tc::mbar_wait(&bars->a_full[ai], aph);
+                    const uint32_t a_addr = tc::smem_u32(base + ai * win_bytes);
+                    for (int t = 0; t < p.taps; t++) {
+                        if (!ready) tc::mbar_wait(&bars->b_full[bi], bph);
+                        tc::fence_after_sync();
+                        if (tc::elect_one()) {
+                            const uint64_t adesc = tc::desc_kmajor_sw128(a_addr + (uint32_t)(p.halo + p.off[t]) * 128u);
+                            const uint64_t bdesc = tc::desc_kmajor_sw128(tc::smem_u32(b_base + bi * b_bytes));
+#pragma unroll
+                            for (int k = 0; k < 4; k++)  // 4 x K=16 inside the 64-channel slice: +32 B each
+                                tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t | k) != 0);
+                            tc::umma_commit_pair(&bars->b_empty[bi]);
+                            if (t == p.taps - 1) {
+                                tc::umma_commit_pair(&bars->a_empty[ai]);
+                                if (kc == p.kchunks - 1) tc::umma_commit_pair(&bars->acc_full[buf]);
+                            }
+                        }
+                        __syncwarp();
+                        if (++bi == kBStages) { bi = 0; bph ^= 1; }
+                        ready = tc::mbar_try_wait(&bars->b_full[bi], bph);  // peek at the next weight slice while these UMMAs run
+                    }
+                    if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const uint32_t empty_remote0 = tc::map_to_cta(&bars->acc_empty[0], 0), empty_remote1 = tc::map_to_cta(&bars->acc_empty[1], 0);
+        int it = 0;
+        for (int pair = cluster_id; pair < n_pairs; pair += n_clusters, it++) {
+            const int buf = it & 1;
+            epilogue_tile(p, s_bias, pair * 2 * kTileM + (int)rank * kTileM + q * 32 + lane,
+                          tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride, &bars->acc_full[buf], (it >> 1) & 1);
+            tc::fence_before_sync();
+            tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // the peer's smem and barriers stay alive until the leader's last UMMA / arrival is done
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -380,8 +521,25 @@ static bool conv_pair_enabled() {
     return on != 0;
 }
 
-int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const ConvArgs& args,
-                     cudaStream_t stream) {
+static bool conv_window_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("AG_CONV_WINDOW"); on = e ? atoi(e) : 1; }
+    return on != 0;
+}
+
+int conv_window_rows(const int* off, int taps) {
+    int halo = 0;
+    for (int t = 0; t < taps; t++) { int a = off[t] < 0 ? -off[t] : off[t]; if (a > halo) halo = a; }
+    int rows = kTileM + 2 * halo;
+    return rows <= 256 ? rows : 0;
+}
+
+static size_t conv_win_smem_bytes(int n, int win_rows, int bstages) {
+    return 1024 + (size_t)kWinSlots * ((win_rows * 128 + 1023) & ~1023) + (size_t)bstages * (n / 2) * 128 + sizeof(WinBarriers) + 256 * sizeof(float);
+}
+
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const CUtensorMap* tmap_a_win,
+                     const ConvArgs& args, cudaStream_t stream) {
     if (args.n < 16 || args.n > 256 || args.n % 16 != 0) { set_error("conv: N=%d must be a multiple of 16 in [16,256]", args.n); return AG_EINVAL; }
     if (args.taps < 1 || args.taps > kConvMaxTaps || args.kchunks < 1) { set_error("conv: bad taps/kchunks"); return AG_EINVAL; }
     static int debug = -1;
@@ -392,6 +550,28 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
     if (tiles < 1) return AG_OK;
     // CTA pairs: N/2 rows of weights per CTA must be whole 8-row swizzle groups, and there must be work for a pair
     if (tmap_b_half && conv_pair_enabled() && args.n % 32 == 0 && tiles >= 2) {
+        const int win_rows = tmap_a_win && conv_window_enabled() ? conv_window_rows(args.off, args.taps) : 0;
+        if (win_rows) {
+            // one activation window per channel slice, taps as row-shifted descriptor starts
+            static size_t configured3 = 0;
+            int bstages = kMaxBStages;
+            while (bstages > 2 && conv_win_smem_bytes(args.n, win_rows, bstages) > 227 * 1024) bstages--;
+            size_t smem = conv_win_smem_bytes(args.n, win_rows, bstages);
+            if (smem <= 227 * 1024) {
+                if (smem > configured3) {
+                    AG_CUDA(cudaFuncSetAttribute(conv_gemm_win_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                    configured3 = smem;
+                }
+                dargs.win_rows = win_rows;
+                dargs.halo = (win_rows - kTileM) / 2;
+                int pairs = (tiles + 1) / 2;
+                int clusters = sm_count() / 2;
+                if (clusters > pairs) clusters = pairs;
+                launch_k(conv_gemm_win_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, *tmap_a_win, *tmap_b_half, dargs, bstages);
+                AG_LAUNCH_CHECK("conv_gemm_win_kernel");
+                return AG_OK;
+            }
+        }
         static size_t configured2 = 0;
         int stages = kMaxStages;
         while (stages > 2 && conv_pair_smem_bytes(args.n, stages) > 227 * 1024) stages--;

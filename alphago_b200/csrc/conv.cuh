@@ -39,6 +39,7 @@ struct ConvArgs {
     __nv_bfloat16* out;   // rows in dst layout, out_ld wide
     int out_ld;
     int relu;
+    int halo, win_rows;   // filled by conv_gemm_launch (window kernel): largest |off|, rows of the activation window box
     int debug;            // measurement only (AG_CONV_DEBUG): 1 = skip A loads, 2 = skip B loads, 4 = skip epilogue memory traffic
 };
 
@@ -46,9 +47,14 @@ struct ConvArgs {
 // 2D bf16 matrix [rows][cols], box [box_rows][64 columns], 128-byte swizzle, zero OOB fill.
 int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows);
 
+// rows of the activation window box (128 + 2 * largest |off|) the window kernel wants tmap_a_win built with; 0 = too tall
+int conv_window_rows(const int* off, int taps);
+
 // D[m, :] = sum_t sum_k A[m + off[t], k] * B[t][:, k]   (+bias, ReLU / gate), bf16 in, fp32 accumulate
-// tmap_b_half (optional): the same B tensor with a box of N/2 rows; when given (and N % 32 == 0) the CTA-pair kernel runs
-int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const ConvArgs& args,
-                     cudaStream_t stream);
+// tmap_b_half (optional): the same B tensor with a box of N/2 rows; when given (and N % 32 == 0) a CTA-pair kernel runs
+// tmap_a_win (optional): the A tensor with a box of conv_window_rows() rows: the pair kernel then fetches each activation
+// row once per channel slice instead of once per tap
+int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const CUtensorMap* tmap_a_win,
+                     const ConvArgs& args, cudaStream_t stream);
 
 }  // namespace ag

@@ -438,6 +438,8 @@ struct ConvLayer {
     int off_fwd[kConvMaxTaps], off_bwd[kConvMaxTaps];
     CUtensorMap tm_in, tm_wf, tm_g, tm_wb;      // forward A / B, dgrad A / B (full-size tensors)
     CUtensorMap tm_wf_half, tm_wb_half;         // B with a box of N/2 rows, for the CTA-pair kernel
+    CUtensorMap tm_in_win, tm_g_win;            // A with a box of win_rows rows (activation window kernel)
+    bool win_fwd, win_bwd;
     bool pair_fwd, pair_bwd;
     WgradMaps tm_wg;                            // wgrad operands, exact batch rows (rebuilt when n changes)
     int wgrad_splits;
@@ -596,6 +598,11 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         c.pair_fwd = c.nout % 32 == 0;
         c.pair_bwd = l > 0 && c.nin % 32 == 0;
         if (!rc && c.pair_fwd) rc = make_tmap_2d(&c.tm_wf_half, c.wf, (uint64_t)c.taps * c.ldout, c.kin, c.nout / 2);
+        const int win_rows = conv_window_rows(c.off_fwd, c.taps);
+        c.win_fwd = c.pair_fwd && win_rows > 0;
+        c.win_bwd = c.pair_bwd && win_rows > 0;
+        if (!rc && c.win_fwd) rc = make_tmap_2d(&c.tm_in_win, xin, (uint64_t)max_batch * c.lin.img_stride, c.kin, win_rows);
+        if (!rc && c.win_bwd) rc = make_tmap_2d(&c.tm_g_win, net->gbuf[l & 1], (uint64_t)max_batch * c.lout.img_stride, c.ldout, win_rows);
         if (!rc && l > 0) {
             // data gradient: A = G of this layer (lay_mid rows, ldout wide), B = wb [tap][ci][co]
             rc = make_tmap_2d(&c.tm_g, net->gbuf[l & 1], (uint64_t)max_batch * c.lout.img_stride, c.ldout, 128);
@@ -770,7 +777,7 @@ static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStrea
         memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
         a.in = c.lin; a.dst = c.lout;
         a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
-        int rc = conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, a, st);
+        int rc = conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, c.win_fwd ? &c.tm_in_win : nullptr, a, st);
         if (rc) return rc;
     }
     return AG_OK;
@@ -869,7 +876,7 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     } else {
         a.dst = c.lout; a.out = net->gbuf[(layer - 1) & 1];
     }
-    return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, a, st);
+    return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
 }
 
 // Flat fp32 gradient buffer (device): conv layers in order (weights [tap][ldout][kin] then bias [ldout]),
@@ -924,7 +931,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
         a.in = c.lin; a.dst = c.lout;
         a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
-        return conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, a, st);
+        return conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, c.win_fwd ? &c.tm_in_win : nullptr, a, st);
     }
     if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
     if (mode == 2) {
@@ -945,7 +952,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         a.in = c.lout; a.dst = c.lout;
         a.gate_mask = below.mask; a.gate_layout = below.lout;
         a.out = net->gbuf[(layer - 1) & 1]; a.out_ld = below.ldout; a.b_tap_rows = c.kin;
-        return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, a, st);
+        return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
     }
     set_error("ag_net_run_layer: mode %d not available for layer %d", mode, layer);
     return AG_EINVAL;
