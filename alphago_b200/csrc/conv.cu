@@ -337,6 +337,7 @@ conv_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
 // own ring.  Loop order: channel slice outer, tap inner.
 constexpr int kWinSlots = 2;
 constexpr int kMaxBStages = 12;
+constexpr int kTapsPerStage = 3;   // weight slices (taps) per ring stage = UMMAs / 4 per barrier round trip
 
 struct __align__(8) WinBarriers {
     uint64_t a_full[kWinSlots];
@@ -358,7 +359,7 @@ conv_gemm_win_kernel(const __grid_constant__ CUtensorMap tmap_aw, const __grid_c
     const int win_box = p.win_rows * 128;                 // bytes one window box brings
     const int win_bytes = (win_box + 1023) & ~1023;       // its slot
     uint8_t* b_base = base + kWinSlots * win_bytes;
-    WinBarriers* bars = reinterpret_cast<WinBarriers*>(b_base + kBStages * b_bytes);
+    WinBarriers* bars = reinterpret_cast<WinBarriers*>(b_base + kBStages * kTapsPerStage * b_bytes);
     float* s_bias = reinterpret_cast<float*>(bars + 1);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
@@ -394,16 +395,25 @@ conv_gemm_win_kernel(const __grid_constant__ CUtensorMap tmap_aw, const __grid_c
             for (int kc = 0; kc < p.kchunks; kc++) {
                 tc::mbar_wait(&bars->a_empty[ai], aph ^ 1);
                 if (tc::elect_one()) {
-                    if (leader) tc::mbar_expect_tx(&bars->a_full[ai], 2 * (uint32_t)win_box);
-                    tc::tma_load_2d_pair(base + ai * win_bytes, &tmap_aw, &bars->a_full[ai], kc * 64, m0 - p.halo);
+                    if (p.debug & 1) { if (leader) tc::mbar_arrive(&bars->a_full[ai]); }
+                    else {
+                        if (leader) tc::mbar_expect_tx(&bars->a_full[ai], 2 * (uint32_t)win_box);
+                        tc::tma_load_2d_pair(base + ai * win_bytes, &tmap_aw, &bars->a_full[ai], kc * 64, m0 - p.halo);
+                    }
                 }
                 __syncwarp();
                 if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
-                for (int t = 0; t < p.taps; t++) {
+                for (int t0 = 0; t0 < p.taps; t0 += kTapsPerStage) {
+                    const int nt = min(kTapsPerStage, p.taps - t0);
                     tc::mbar_wait(&bars->b_empty[bi], bph ^ 1);
                     if (tc::elect_one()) {
-                        if (leader) tc::mbar_expect_tx(&bars->b_full[bi], 2 * (uint32_t)b_bytes);
-                        tc::tma_load_2d_pair(b_base + bi * b_bytes, &tmap_bh, &bars->b_full[bi], kc * 64, t * p.b_tap_rows + (int)rank * half_n);
+                        if (p.debug & 2) { if (leader) tc::mbar_arrive(&bars->b_full[bi]); }
+                        else {
+                            if (leader) tc::mbar_expect_tx(&bars->b_full[bi], 2 * (uint32_t)(nt * b_bytes));
+                            for (int j = 0; j < nt; j++)
+                                tc::tma_load_2d_pair(b_base + (bi * kTapsPerStage + j) * b_bytes, &tmap_bh, &bars->b_full[bi], kc * 64,
+                                                     (t0 + j) * p.b_tap_rows + (int)rank * half_n);
+                        }
                     }
                     __syncwarp();
                     if (++bi == kBStages) { bi = 0; bph ^= 1; }
@@ -423,25 +433,33 @@ conv_gemm_win_kernel(const __grid_constant__ CUtensorMap tmap_aw, const __grid_c
                 const uint32_t d_tmem = tmem_base + buf * kAccStride;
                 for (int kc = 0; kc < p.kchunks; kc++) {
                     tc::mbar_wait(&bars->a_full[ai], aph);
-                    const uint32_t a_addr = tc::smem_u32(base + ai * win_bytes);
-                    for (int t = 0; t < p.taps; t++) {
+                    const uint64_t a_desc0 = tc::desc_kmajor_sw128(tc::smem_u32(base + ai * win_bytes)) + (uint64_t)(p.halo * 8);  // window row `halo`
+                    for (int t0 = 0; t0 < p.taps; t0 += kTapsPerStage) {
+                        const int nt = min(kTapsPerStage, p.taps - t0);
                         if (!ready) tc::mbar_wait(&bars->b_full[bi], bph);
                         tc::fence_after_sync();
                         if (tc::elect_one()) {
-                            const uint64_t adesc = tc::desc_kmajor_sw128(a_addr + (uint32_t)(p.halo + p.off[t]) * 128u);
-                            const uint64_t bdesc = tc::desc_kmajor_sw128(tc::smem_u32(b_base + bi * b_bytes));
+                            // one barrier round trip per kTapsPerStage taps: the issuing thread, not the tensor core, was the bottleneck
+                            const uint64_t b_desc0 = tc::desc_kmajor_sw128(tc::smem_u32(b_base + bi * kTapsPerStage * b_bytes));
 #pragma unroll
-                            for (int k = 0; k < 4; k++)  // 4 x K=16 inside the 64-channel slice: +32 B each
-                                tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t | k) != 0);
+                            for (int j = 0; j < kTapsPerStage; j++) {
+                                if (j < nt && !(p.debug & 16)) {
+                                    const uint64_t adesc = a_desc0 + (int64_t)(p.off[t0 + j] * 8);   // a pixel row = 128 B = 8 descriptor units
+                                    const uint64_t bdesc = b_desc0 + (uint64_t)(j * (b_bytes >> 4));
+#pragma unroll
+                                    for (int k = 0; k < 4; k++)  // 4 x K=16 inside the 64-channel slice: +32 B each
+                                        tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t0 | j | k) != 0);
+                                }
+                            }
                             tc::umma_commit_pair(&bars->b_empty[bi]);
-                            if (t == p.taps - 1) {
+                            if (t0 + nt == p.taps) {
                                 tc::umma_commit_pair(&bars->a_empty[ai]);
                                 if (kc == p.kchunks - 1) tc::umma_commit_pair(&bars->acc_full[buf]);
                             }
                         }
                         __syncwarp();
                         if (++bi == kBStages) { bi = 0; bph ^= 1; }
-                        ready = tc::mbar_try_wait(&bars->b_full[bi], bph);  // peek at the next weight slice while these UMMAs run
+                        ready = tc::mbar_try_wait(&bars->b_full[bi], bph);  // peek at the next weight slices while these UMMAs run
                     }
                     if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
                 }
@@ -457,6 +475,197 @@ conv_gemm_win_kernel(const __grid_constant__ CUtensorMap tmap_aw, const __grid_c
                           tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride, &bars->acc_full[buf], (it >> 1) & 1);
             tc::fence_before_sync();
             tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // the peer's smem and barriers stay alive until the leader's last UMMA / arrival is done
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
+// ---- A whole chain of layers in ONE persistent launch (the forward conv stack, or the data-gradient chain of backward).
+// One kernel per layer leaves ~10 % of the machine idle: 400 tiles of 256 rows over 74 CTA pairs is 5.4 rounds, run as 6,
+// and every launch pays its own prologue and drain.  Here the tiles of all layers form one sequence g = 0, 1, 2 ...
+// (layer-major), pair c takes g = c, c + pairs, c + 2*pairs ..., and a tile starts as soon as the 128-row tiles of the layer
+// before it that cover its rows (+ halo) are finished: every CTA publishes a tile with a release store of the launch's
+// epoch to flags[layer][tile128], and the TMA producer acquires the flags it needs before fetching the window.  All CTAs are
+// resident (grid <= SM count, 1 CTA/SM) and each walks its tiles in increasing g, while a tile only waits for tiles with
+// smaller g: no cycle, so no deadlock.  The kernel body is the window kernel's; the layer table travels as a kernel
+// parameter (constant bank: the tensor maps and per-layer arguments are read like any other kernel argument).
+__device__ __forceinline__ void chain_wait_flag(const unsigned int* flag, unsigned int epoch) {
+    unsigned int v;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v == epoch) return;
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 4000000000LL) {
+            printf("alphago_b200: conv chain dependency wait timed out (block %d flag %p has %u, want %u)\n", blockIdx.x, (const void*)flag, v, epoch);
+            __trap();
+        }
+        __nanosleep(64);
+    }
+}
+
+// layer of global tile g (layers are few: a linear scan over the parameter table)
+__device__ __forceinline__ int chain_layer_of(const ChainParams& P, int g, int l) {
+    while (l + 1 < P.n_layers && P.layers[l + 1].tile0 <= g) l++;
+    return l;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restrict__ flags, const unsigned int epoch, const int win_bytes,
+                  const int b_bytes_max, const int kBStages) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    uint8_t* b_base = base + kWinSlots * win_bytes;
+    const int stage_bytes = kTapsPerStage * b_bytes_max;
+    WinBarriers* bars = reinterpret_cast<WinBarriers*>(b_base + kBStages * stage_bytes);
+    float* s_bias = reinterpret_cast<float*>(bars + 1);  // [256]
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int n_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
+    const int total_tiles = P.total_tiles;
+
+    pdl_trigger();
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kWinSlots; s++) { tc::mbar_init(&bars->a_full[s], 1); tc::mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < kBStages; s++) { tc::mbar_init(&bars->b_full[s], 1); tc::mbar_init(&bars->b_empty[s], 1); }
+        for (int b = 0; b < 2; b++) { tc::mbar_init(&bars->acc_full[b], 1); tc::mbar_init(&bars->acc_empty[b], 256); }
+        tc::fence_mbar_init();
+    }
+    if (warp == 1) tc::tmem_alloc_pair(&bars->tmem_base, kTmemCols);
+    pdl_wait();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync_all();  // both CTAs' barriers exist before anyone signals across the pair
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ===== TMA producer
+        int ai = 0, bi = 0, l = 0;
+        uint32_t aph = 0, bph = 0;
+        for (int g = cluster_id; g < total_tiles; g += n_clusters) {
+            l = chain_layer_of(P, g, l);
+            const ChainLayer& L = P.layers[l];
+            const ConvArgs& p = L.a;
+            const int half_n = p.n / 2, b_bytes = half_n * 128, win_box = p.win_rows * 128;
+            const int m0 = (g - L.tile0) * 2 * kTileM + (int)rank * kTileM;
+            if (L.dep) {
+                // rows [m0 - halo, m0 + 128 + halo) of the input must be final: the 128-row tiles of the layer before that wrote them
+                int lo = m0 - p.halo, hi = m0 + kTileM - 1 + p.halo;
+                if (L.dep == 2) {  // rows -> images -> GEMM rows of the previous layer
+                    lo = (lo < 0 ? 0 : lo / p.in.img_stride) * L.prev_in_img_stride;
+                    hi = (hi / p.in.img_stride + 1) * L.prev_in_img_stride - 1;
+                }
+                if (lo < 0) lo = 0;
+                if (hi > L.prev_rows - 1) hi = L.prev_rows - 1;
+                const unsigned int* f = flags + P.layers[l - 1].flag0;
+                for (int j = lo / kTileM + lane; j <= hi / kTileM; j += 32) chain_wait_flag(f + j, epoch);
+                __syncwarp();
+                asm volatile("fence.proxy.async.global;" ::: "memory");  // the generic-proxy stores just acquired, before TMA reads them
+            }
+            for (int kc = 0; kc < p.kchunks; kc++) {
+                tc::mbar_wait(&bars->a_empty[ai], aph ^ 1);
+                if (tc::elect_one()) {
+                    if (leader) tc::mbar_expect_tx(&bars->a_full[ai], 2 * (uint32_t)win_box);
+                    tc::tma_load_2d_pair(base + ai * win_bytes, &L.tmap_aw, &bars->a_full[ai], kc * 64, m0 - p.halo);
+                }
+                __syncwarp();
+                if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
+                for (int t0 = 0; t0 < p.taps; t0 += kTapsPerStage) {
+                    const int nt = min(kTapsPerStage, p.taps - t0);
+                    tc::mbar_wait(&bars->b_empty[bi], bph ^ 1);
+                    if (tc::elect_one()) {
+                        if (leader) tc::mbar_expect_tx(&bars->b_full[bi], 2 * (uint32_t)(nt * b_bytes));
+                        for (int j = 0; j < nt; j++)
+                            tc::tma_load_2d_pair(b_base + bi * stage_bytes + j * b_bytes, &L.tmap_bh, &bars->b_full[bi], kc * 64,
+                                                 (t0 + j) * p.b_tap_rows + (int)rank * half_n);
+                    }
+                    __syncwarp();
+                    if (++bi == kBStages) { bi = 0; bph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            int ai = 0, bi = 0, it = 0, l = 0;
+            uint32_t aph = 0, bph = 0;
+            bool ready = false;
+            for (int g = cluster_id; g < total_tiles; g += n_clusters, it++) {
+                l = chain_layer_of(P, g, l);
+                const ConvArgs& p = P.layers[l].a;
+                const uint32_t idesc = tc::idesc_bf16(2 * kTileM, p.n, 0, 0);
+                const int b_bytes = (p.n / 2) * 128;
+                const int buf = it & 1;
+                tc::mbar_wait(&bars->acc_empty[buf], ((it >> 1) & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t d_tmem = tmem_base + buf * kAccStride;
+                for (int kc = 0; kc < p.kchunks; kc++) {
+                    tc::mbar_wait(&bars->a_full[ai], aph);
+                    const uint64_t a_desc0 = tc::desc_kmajor_sw128(tc::smem_u32(base + ai * win_bytes)) + (uint64_t)(p.halo * 8);  // window row `halo`
+                    for (int t0 = 0; t0 < p.taps; t0 += kTapsPerStage) {
+                        const int nt = min(kTapsPerStage, p.taps - t0);
+                        if (!ready) tc::mbar_wait(&bars->b_full[bi], bph);
+                        tc::fence_after_sync();
+                        if (tc::elect_one()) {
+                            const uint64_t b_desc0 = tc::desc_kmajor_sw128(tc::smem_u32(b_base + bi * stage_bytes));
+#pragma unroll
+                            for (int j = 0; j < kTapsPerStage; j++) {
+                                if (j < nt) {
+                                    const uint64_t adesc = a_desc0 + (int64_t)(p.off[t0 + j] * 8);   // a pixel row = 128 B = 8 descriptor units
+                                    const uint64_t bdesc = b_desc0 + (uint64_t)(j * (b_bytes >> 4));
+#pragma unroll
+                                    for (int k = 0; k < 4; k++)
+                                        tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t0 | j | k) != 0);
+                                }
+                            }
+                            tc::umma_commit_pair(&bars->b_empty[bi]);
+                            if (t0 + nt == p.taps) {
+                                tc::umma_commit_pair(&bars->a_empty[ai]);
+                                if (kc == p.kchunks - 1) tc::umma_commit_pair(&bars->acc_full[buf]);
+                            }
+                        }
+                        __syncwarp();
+                        if (++bi == kBStages) { bi = 0; bph ^= 1; }
+                        ready = tc::mbar_try_wait(&bars->b_full[bi], bph);
+                    }
+                    if (++ai == kWinSlots) { ai = 0; aph ^= 1; }
+                }
+            }
+        }
+    } else {
+        // ===== epilogue warps (128 threads, named barrier 1)
+        const int q = warp & 3, et = threadIdx.x - 64;
+        const uint32_t empty_remote0 = tc::map_to_cta(&bars->acc_empty[0], 0), empty_remote1 = tc::map_to_cta(&bars->acc_empty[1], 0);
+        int it = 0, l = 0, bias_l = -1;
+        for (int g = cluster_id; g < total_tiles; g += n_clusters, it++) {
+            l = chain_layer_of(P, g, l);
+            const ChainLayer& L = P.layers[l];
+            if (l != bias_l) {
+                bias_l = l;
+                asm volatile("bar.sync 1, 128;" ::: "memory");  // everyone is done with the previous layer's bias
+                const float* bias = L.a.bias;
+                for (int i = et; i < 256; i += 128) s_bias[i] = (bias && i < L.a.n) ? __ldg(bias + i) : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            const int buf = it & 1;
+            const int tile128 = (g - L.tile0) * 2 + (int)rank;
+            epilogue_tile(L.a, s_bias, tile128 * kTileM + q * 32 + lane, tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride,
+                          &bars->acc_full[buf], (it >> 1) & 1);
+            tc::fence_before_sync();
+            tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
+            // publish the tile: every thread's stores, made visible device-wide, then one release store of the epoch
+            asm volatile("fence.proxy.async.global;" ::: "memory");  // the consumer reads these rows through TMA (async proxy)
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (et == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + L.flag0 + tile128), "r"(epoch) : "memory");
         }
     }
     tc::fence_before_sync();
@@ -535,7 +744,8 @@ int conv_window_rows(const int* off, int taps) {
 }
 
 static size_t conv_win_smem_bytes(int n, int win_rows, int bstages) {
-    return 1024 + (size_t)kWinSlots * ((win_rows * 128 + 1023) & ~1023) + (size_t)bstages * (n / 2) * 128 + sizeof(WinBarriers) + 256 * sizeof(float);
+    return 1024 + (size_t)kWinSlots * ((win_rows * 128 + 1023) & ~1023) + (size_t)bstages * kTapsPerStage * (n / 2) * 128 + sizeof(WinBarriers) +
+           256 * sizeof(float);
 }
 
 int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const CUtensorMap* tmap_a_win,
@@ -598,6 +808,48 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
     int grid = tiles < sm_count() ? tiles : sm_count();
     launch_k(conv_gemm_kernel, dim3(grid), dim3(kThreads), smem, stream, tmap_a, tmap_b, dargs, stages);
     AG_LAUNCH_CHECK("conv_gemm_kernel");
+    return AG_OK;
+}
+
+bool conv_chain_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("AG_CONV_CHAIN"); on = e ? atoi(e) : 1; }
+    return on != 0 && conv_pair_enabled() && conv_window_enabled();
+}
+
+static size_t conv_chain_smem_bytes(int win_bytes, int b_bytes, int bstages) {
+    return 1024 + (size_t)kWinSlots * win_bytes + (size_t)bstages * kTapsPerStage * b_bytes + sizeof(WinBarriers) + 256 * sizeof(float) + 64;
+}
+
+int conv_chain_launch(const ChainParams& P, unsigned int* d_flags, unsigned int epoch, int win_rows_max, int n_max, cudaStream_t stream) {
+    if (P.n_layers < 1 || P.total_tiles < 1) return AG_OK;
+    if (P.n_layers > kChainMaxLayers) { set_error("conv chain: %d layers in one launch (max %d)", P.n_layers, kChainMaxLayers); return AG_EINVAL; }
+    const int win_bytes = (win_rows_max * 128 + 1023) & ~1023, b_bytes = (n_max / 2) * 128;
+    int bstages = kMaxBStages;
+    while (bstages > 2 && conv_chain_smem_bytes(win_bytes, b_bytes, bstages) > 227 * 1024) bstages--;
+    size_t smem = conv_chain_smem_bytes(win_bytes, b_bytes, bstages);
+    // one CTA per SM, always: two CTAs of this kernel on one SM would deadlock (the second blocks in the TMEM allocation while
+    // the first waits for tiles of the second's pair), so ask for more than half of the SM's shared memory
+    if (smem < 120 * 1024) smem = 120 * 1024;
+    if (smem > 227 * 1024) { set_error("conv chain: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
+    static size_t configured = 0;
+    static int max_clusters = 0;
+    if (smem > configured) {
+        AG_CUDA(cudaFuncSetAttribute(conv_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+        // every CTA pair must be resident at once (tiles wait for each other): ask how many the device can hold
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(sm_count() & ~1); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem;
+        int n = 0;
+        AG_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_chain_kernel, &cfg));
+        max_clusters = n;
+    }
+    int clusters = sm_count() / 2;
+    if (clusters > max_clusters) clusters = max_clusters;
+    if (clusters > P.total_tiles) clusters = P.total_tiles;
+    if (clusters < 1) { set_error("conv chain: no CTA pair fits on this device"); return AG_ECUDA; }
+    launch_k(conv_chain_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, P, d_flags, epoch, win_bytes, b_bytes, bstages);
+    AG_LAUNCH_CHECK("conv_chain_kernel");
     return AG_OK;
 }
 

@@ -57,4 +57,31 @@ int conv_window_rows(const int* off, int taps);
 int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap* tmap_b_half, const CUtensorMap* tmap_a_win,
                      const ConvArgs& args, cudaStream_t stream);
 
+// One entry of a layer chain run by a single persistent launch (conv.cu, conv_chain_kernel)
+struct __align__(64) ChainLayer {
+    CUtensorMap tmap_aw;   // A: the layer's input with a box of win_rows rows
+    CUtensorMap tmap_bh;   // B: its weights with a box of N/2 rows
+    ConvArgs a;
+    int n_pairs;           // 256-row tiles of this layer
+    int tile0;             // g of its first tile
+    int flag0;             // index of its first flag
+    int dep;               // 0: input comes from outside the chain; 1: from the layer before, same row space; 2: from the layer
+                           // before, whose GEMM rows live in another layout than its output (first layer 5x5): wait by image
+    int prev_in_img_stride;  // dep 2: img_stride of the previous layer's GEMM rows
+    int prev_rows;           // GEMM rows of the previous layer (bounds its flags)
+};
+
+
+constexpr int kChainMaxLayers = 16;   // per launch (the table is a kernel parameter: 16 x ~0.6 KB of the 32 KB limit)
+struct ChainParams {
+    ChainLayer layers[kChainMaxLayers];
+    int n_layers;
+    int total_tiles;
+};
+
+bool conv_chain_enabled();
+// runs P.layers[0..n_layers) in one launch; flags: one unsigned per 128-row tile of every layer (layer l's start at flag0),
+// epoch: a value no earlier launch on these flags used; win_rows_max / n_max: largest window box and N over the layers
+int conv_chain_launch(const ChainParams& P, unsigned int* d_flags, unsigned int epoch, int win_rows_max, int n_max, cudaStream_t stream);
+
 }  // namespace ag

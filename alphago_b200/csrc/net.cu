@@ -8,6 +8,7 @@
 #include <math.h>
 #include <string.h>
 
+#include <stdlib.h>
 #include <vector>
 
 #include "common.cuh"
@@ -455,7 +456,16 @@ struct ag_net {
     PixelLayout lay_in, lay_mid;
     bf16* x0 = nullptr;        // packed input rows [max_batch*lay_in.img_stride][kin0]
     bf16* x0_grad = nullptr;   // G of layer 0 in the input layout (only when layer 0's layout differs)
-    bf16* gbuf[2] = {nullptr, nullptr};  // ping-pong pre-activation gradients in lay_mid
+    std::vector<bf16*> gbuf;   // per-layer pre-activation gradients in lay_mid ([0] unused when x0_grad holds layer 0's)
+    // layer chains (conv.cu, conv_chain_kernel): the whole forward stack / data-gradient chain in one launch each
+    bool chain_ok = false;      // the layers can run as chains
+    bool chain_fwd = false, chain_bwd = false;  // ... and the forward stack / the data gradients do (AG_CONV_CHAIN: 1 both, 2 forward only, 3 backward only)
+    int chain_n = -1;          // batch the device tables were built for
+    std::vector<ChainParams> chain_fwd_p, chain_bwd_p;   // launches of <= kChainMaxLayers layers each
+    unsigned int *chain_flags_fwd = nullptr, *chain_flags_bwd = nullptr;
+    unsigned int chain_epoch_fwd = 0, chain_epoch_bwd = 0;
+    int chain_win_rows = 0, chain_nmax_fwd = 0, chain_nmax_bwd = 0;
+    bool dgrad_chain_done = false;  // the data-gradient chain of the current forward_loss has been queued
     // head
     float *hw = nullptr, *hb = nullptr, *hpos = nullptr;       // 1x1 conv w[ld], b[1], position bias[pts] (optional)
     float *vhw = nullptr, *vhb = nullptr, *vhpos = nullptr;    // velocities
@@ -502,12 +512,96 @@ static int grid_for(size_t work, int threads) {
     return (int)(g < cap ? (g ? g : 1) : cap);
 }
 
+static void fwd_conv_args(ag_net* net, int l, int n, ConvArgs* a) {
+    ConvLayer& c = net->L[l];
+    memset(a, 0, sizeof(*a));
+    a->m_total = n * c.lin.img_stride;
+    a->n = c.nout; a->taps = c.taps; a->kchunks = c.kin / 64;
+    memcpy(a->off, c.off_fwd, sizeof(int) * c.taps);
+    a->in = c.lin; a->dst = c.lout;
+    a->bias = c.b; a->mask_out = c.mask; a->out = c.act; a->out_ld = c.ldout; a->b_tap_rows = c.ldout; a->relu = 1;
+}
+
+// data gradient of layer `l` (> 0) into the layer below, gated by that layer's ReLU mask
+static void bwd_conv_args(ag_net* net, int l, int n, ConvArgs* a) {
+    ConvLayer& c = net->L[l];
+    ConvLayer& below = net->L[l - 1];
+    memset(a, 0, sizeof(*a));
+    a->m_total = n * c.lout.img_stride;
+    a->n = c.nin; a->taps = c.taps; a->kchunks = c.ldout / 64;
+    memcpy(a->off, c.off_bwd, sizeof(int) * c.taps);
+    a->in = c.lout;
+    a->gate_mask = below.mask; a->gate_layout = below.lout;
+    a->out_ld = below.ldout; a->b_tap_rows = c.kin;
+    if (l - 1 == 0 && net->x0_grad) {
+        // the first layer's G lives in the INPUT layout so its weight gradient can pair it with x0; the gate
+        // (layer-0 ReLU mask) is still read in the mid layout
+        a->dst = net->lay_in; a->out = net->x0_grad;
+    } else {
+        a->dst = c.lout; a->out = net->gbuf[l - 1];
+    }
+}
+
+// kernel-parameter tables of the two layer chains for batch n, split into launches of <= kChainMaxLayers layers
+static void chain_append(std::vector<ChainParams>& out, const ChainLayer& e_in, int* flag0) {
+    if (out.empty() || out.back().n_layers == kChainMaxLayers) {
+        out.emplace_back();
+        memset(&out.back(), 0, sizeof(ChainParams));
+    }
+    ChainParams& P = out.back();
+    ChainLayer e = e_in;
+    e.tile0 = P.total_tiles;
+    e.flag0 = *flag0;
+    if (P.n_layers == 0) e.dep = 0;  // the launch before this one has finished
+    P.layers[P.n_layers++] = e;
+    P.total_tiles += e.n_pairs;
+    *flag0 += 2 * e.n_pairs;
+}
+
+static int net_build_chains(ag_net* net, int n) {
+    if (!net->chain_ok || net->chain_n == n) return AG_OK;
+    const int nc = net->n_conv;
+    net->chain_fwd_p.clear();
+    net->chain_bwd_p.clear();
+    int flag0 = 0;
+    for (int l = 0; l < nc; l++) {
+        ChainLayer e;
+        memset(&e, 0, sizeof(e));
+        ConvLayer& c = net->L[l];
+        e.tmap_aw = c.tm_in_win; e.tmap_bh = c.tm_wf_half;
+        fwd_conv_args(net, l, n, &e.a);
+        e.a.win_rows = conv_window_rows(e.a.off, e.a.taps); e.a.halo = (e.a.win_rows - 128) / 2;
+        e.n_pairs = (e.a.m_total + 255) / 256;
+        if (l > 0) {
+            ConvLayer& pv = net->L[l - 1];
+            e.dep = (pv.lin.img_stride == pv.lout.img_stride && pv.lin.row_stride == pv.lout.row_stride) ? 1 : 2;
+            e.prev_in_img_stride = pv.lin.img_stride; e.prev_rows = n * pv.lin.img_stride;
+        }
+        chain_append(net->chain_fwd_p, e, &flag0);
+    }
+    flag0 = 0;
+    for (int k = 0; k + 1 < nc; k++) {
+        const int l = nc - 1 - k;
+        ChainLayer e;
+        memset(&e, 0, sizeof(e));
+        ConvLayer& c = net->L[l];
+        e.tmap_aw = c.tm_g_win; e.tmap_bh = c.tm_wb_half;
+        bwd_conv_args(net, l, n, &e.a);
+        e.a.win_rows = conv_window_rows(e.a.off, e.a.taps); e.a.halo = (e.a.win_rows - 128) / 2;
+        e.n_pairs = (e.a.m_total + 255) / 256;
+        if (k > 0) { e.dep = 1; e.prev_in_img_stride = c.lout.img_stride; e.prev_rows = n * c.lout.img_stride; }  // G rows all live in lay_mid
+        chain_append(net->chain_bwd_p, e, &flag0);
+    }
+    net->chain_n = n;
+    return AG_OK;
+}
+
 static int net_build_wgrad_maps(ag_net* net, int n) {
     if (net->wgrad_n == n) return AG_OK;
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
         const bf16* xin = l == 0 ? net->x0 : net->L[l - 1].act;
-        const bf16* g = (l == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[l & 1];
+        const bf16* g = (l == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[l];
         uint64_t rows = (uint64_t)n * c.lin.img_stride;
         int rc = wgrad_make_maps(&c.tm_wg, g, xin, rows, c.ldout, c.kin, c.taps, c.off_fwd);
         if (rc) return rc;
@@ -575,9 +669,9 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
     if (!rc) rc = dev_alloc(&net->wgrad_scratch, scratch + (size_t)kWgradMaxSplits * 256, false);  // + bias-column partials
     if (!rc) rc = dev_alloc(&net->x0, (size_t)max_batch * net->lay_in.img_stride * net->L[0].kin);
     if (!rc && !same_layout) rc = dev_alloc(&net->x0_grad, (size_t)max_batch * net->lay_in.img_stride * net->L[0].ldout);
-    size_t gmax = 0;
-    for (int l = 0; l < n_conv; l++) { size_t s = (size_t)max_batch * net->lay_mid.img_stride * net->L[l].ldout; if (s > gmax) gmax = s; }
-    for (int i = 0; i < 2 && !rc; i++) rc = dev_alloc(&net->gbuf[i], gmax);
+    net->gbuf.assign(n_conv, nullptr);
+    for (int l = 0; l < n_conv && !rc; l++)
+        if (!(l == 0 && net->x0_grad)) rc = dev_alloc(&net->gbuf[l], (size_t)max_batch * net->lay_mid.img_stride * net->L[l].ldout);
     for (int l = 0; l < n_conv && !rc; l++) {
         ConvLayer& c = net->L[l];
         rc = dev_alloc(&c.w, c.wcount);
@@ -602,12 +696,34 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         c.win_fwd = c.pair_fwd && win_rows > 0;
         c.win_bwd = c.pair_bwd && win_rows > 0;
         if (!rc && c.win_fwd) rc = make_tmap_2d(&c.tm_in_win, xin, (uint64_t)max_batch * c.lin.img_stride, c.kin, win_rows);
-        if (!rc && c.win_bwd) rc = make_tmap_2d(&c.tm_g_win, net->gbuf[l & 1], (uint64_t)max_batch * c.lout.img_stride, c.ldout, win_rows);
+        if (!rc && c.win_bwd) rc = make_tmap_2d(&c.tm_g_win, net->gbuf[l], (uint64_t)max_batch * c.lout.img_stride, c.ldout, win_rows);
         if (!rc && l > 0) {
             // data gradient: A = G of this layer (lay_mid rows, ldout wide), B = wb [tap][ci][co]
-            rc = make_tmap_2d(&c.tm_g, net->gbuf[l & 1], (uint64_t)max_batch * c.lout.img_stride, c.ldout, 128);
+            rc = make_tmap_2d(&c.tm_g, net->gbuf[l], (uint64_t)max_batch * c.lout.img_stride, c.ldout, 128);
             if (!rc) rc = make_tmap_2d(&c.tm_wb, c.wb, (uint64_t)c.taps * c.kin, c.ldout, c.nin);
             if (!rc && c.pair_bwd) rc = make_tmap_2d(&c.tm_wb_half, c.wb, (uint64_t)c.taps * c.kin, c.ldout, c.nin / 2);
+        }
+    }
+    if (!rc) {  // layer chains: every layer must be able to run the pair + window kernel
+        bool ok = conv_chain_enabled();
+        int wmax = 0, nf = 0, nb = 0;
+        size_t flags = 0;
+        for (int l = 0; l < n_conv; l++) {
+            ConvLayer& c = net->L[l];
+            ok = ok && c.win_fwd && (l == 0 || c.win_bwd);
+            int w = conv_window_rows(c.off_fwd, c.taps);
+            if (w > wmax) wmax = w;
+            if (c.nout > nf) nf = c.nout;
+            if (l > 0 && c.nin > nb) nb = c.nin;
+            size_t rows = (size_t)max_batch * (c.lin.img_stride > c.lout.img_stride ? c.lin.img_stride : c.lout.img_stride);
+            flags += 2 * ((rows + 255) / 256);
+        }
+        net->chain_ok = ok;
+        { const char* e = getenv("AG_CONV_CHAIN"); int m = e ? atoi(e) : 1; net->chain_fwd = ok && (m == 1 || m == 2); net->chain_bwd = ok && (m == 1 || m == 3); }
+        net->chain_win_rows = wmax; net->chain_nmax_fwd = nf; net->chain_nmax_bwd = nb;
+        if (ok) {
+            rc = dev_alloc(&net->chain_flags_fwd, flags);
+            if (!rc) rc = dev_alloc(&net->chain_flags_bwd, flags);
         }
     }
     if (!rc) {  // the SGD kernel's layer table
@@ -654,7 +770,9 @@ void ag_net_destroy(ag_net* net) {
     float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
                   net->head_partial, net->colsum_part, net->wgrad_scratch, net->grads};
     for (float* p : f) cudaFree(p);
-    cudaFree(net->sgd_table); cudaFree(net->x0); cudaFree(net->x0_grad); cudaFree(net->gbuf[0]); cudaFree(net->gbuf[1]);
+    cudaFree(net->sgd_table); cudaFree(net->x0); cudaFree(net->x0_grad);
+    for (bf16* g : net->gbuf) cudaFree(g);
+    cudaFree(net->chain_flags_fwd); cudaFree(net->chain_flags_bwd);
     delete net;
 }
 
@@ -768,15 +886,20 @@ static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStrea
     size_t work = (size_t)n * S * S * (c0.kin / 8);
     launch_k(pack_input_kernel, dim3(grid_for(work, 256)), dim3(256), 0, st, d_planes, n, net->in_planes, S, net->lay_in, c0.kin, net->x0);
     AG_LAUNCH_CHECK("pack_input_kernel");
+    if (net->chain_fwd) {
+        int rc = net_build_chains(net, n);
+        if (rc) return rc;
+        ++net->chain_epoch_fwd;
+        for (const ChainParams& P : net->chain_fwd_p) {
+            rc = conv_chain_launch(P, net->chain_flags_fwd, net->chain_epoch_fwd, net->chain_win_rows, net->chain_nmax_fwd, st);
+            if (rc) return rc;
+        }
+        return AG_OK;
+    }
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
         ConvArgs a;
-        memset(&a, 0, sizeof(a));
-        a.m_total = n * c.lin.img_stride;
-        a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
-        memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
-        a.in = c.lin; a.dst = c.lout;
-        a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        fwd_conv_args(net, l, n, &a);
         int rc = conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, c.win_fwd ? &c.tm_in_win : nullptr, a, st);
         if (rc) return rc;
     }
@@ -817,9 +940,10 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
     if (rc) return rc;
     rc = net_build_wgrad_maps(net, n);
     if (rc) return rc;
+    net->dgrad_chain_done = false;
     const int last = net->n_conv - 1;
     ConvLayer& cl = net->L[last];
-    bf16* G = (last == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[last & 1];
+    bf16* G = (last == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[last];
     if (last == 0 && net->x0_grad) { set_error("single-layer nets with a wide first filter are not trainable"); return AG_ESTATE; }
     launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
                                                   d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr);
@@ -840,7 +964,20 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     }
     cudaStream_t st = (cudaStream_t)stream;
     ConvLayer& c = net->L[layer];
-    const bf16* G = (layer == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[layer & 1];
+    int rc;
+    if (net->chain_bwd && !net->dgrad_chain_done) {
+        // every data gradient of this backward pass in one launch (G of every layer has its own buffer); the weight
+        // gradients follow layer by layer as the caller asks for them
+        rc = net_build_chains(net, n);
+        if (rc) return rc;
+        ++net->chain_epoch_bwd;
+        for (const ChainParams& P : net->chain_bwd_p) {
+            rc = conv_chain_launch(P, net->chain_flags_bwd, net->chain_epoch_bwd, net->chain_win_rows, net->chain_nmax_bwd, st);
+            if (rc) return rc;
+        }
+        net->dgrad_chain_done = true;
+    }
+    const bf16* G = (layer == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[layer];
     const size_t rows = (size_t)n * c.lin.img_stride;
     // weight gradient
     WgradArgs w;
@@ -849,7 +986,14 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
     const bool fused_bias = c.kin + 16 <= 256;  // the bias gradient rides in the weight-gradient GEMM as an extra column of ones
     w.bias_scratch = fused_bias ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
-    int rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
+    if (!net->chain_bwd && layer > 0) {
+        // data gradient into the layer below first (it only needs G of this layer; the weight gradient can then overlap nothing it depends on)
+        ConvArgs a;
+        bwd_conv_args(net, layer, n, &a);
+        rc = conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
+        if (rc) return rc;
+    }
+    rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
     if (rc) return rc;
     if (!fused_bias) {
         launch_k(colsum_stage1_kernel, dim3(net->colsum_blocks), dim3(256), 0, st, G, rows, c.ldout, net->colsum_part);
@@ -857,26 +1001,7 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
         launch_k(colsum_stage2_kernel, dim3((c.ldout + 7) / 8), dim3(256), 0, st, net->colsum_part, net->colsum_blocks, c.ldout, c.ldout, c.gb);
         AG_LAUNCH_CHECK("colsum_stage2_kernel");
     }
-    if (layer == 0) return AG_OK;
-    // data gradient into the layer below
-    ConvLayer& below = net->L[layer - 1];
-    ConvArgs a;
-    memset(&a, 0, sizeof(a));
-    a.m_total = n * c.lout.img_stride;
-    a.n = c.nin; a.taps = c.taps; a.kchunks = c.ldout / 64;
-    memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
-    a.in = c.lout;
-    a.bias = nullptr; a.relu = 0;
-    a.gate_mask = below.mask; a.gate_layout = below.lout;
-    a.out_ld = below.ldout; a.b_tap_rows = c.kin;
-    if (layer - 1 == 0 && net->x0_grad) {
-        // the first layer's G lives in the INPUT layout so its weight gradient can pair it with x0; the gate
-        // (layer-0 ReLU mask) is still read in the mid layout
-        a.dst = net->lay_in; a.out = net->x0_grad;
-    } else {
-        a.dst = c.lout; a.out = net->gbuf[(layer - 1) & 1];
-    }
-    return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
+    return AG_OK;
 }
 
 // Flat fp32 gradient buffer (device): conv layers in order (weights [tap][ldout][kin] then bias [ldout]),
@@ -925,12 +1050,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
     ConvLayer& c = net->L[layer];
     if (mode == 0) {
         ConvArgs a;
-        memset(&a, 0, sizeof(a));
-        a.m_total = n * c.lin.img_stride;
-        a.n = c.nout; a.taps = c.taps; a.kchunks = c.kin / 64;
-        memcpy(a.off, c.off_fwd, sizeof(int) * c.taps);
-        a.in = c.lin; a.dst = c.lout;
-        a.bias = c.b; a.mask_out = c.mask; a.out = c.act; a.out_ld = c.ldout; a.b_tap_rows = c.ldout; a.relu = 1;
+        fwd_conv_args(net, layer, n, &a);
         return conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, c.win_fwd ? &c.tm_in_win : nullptr, a, st);
     }
     if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
@@ -942,16 +1062,9 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         w.bias_scratch = c.kin + 16 <= 256 ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
         return wgrad_launch(c.tm_wg, w, c.gw, w.bias_scratch ? c.gb : nullptr, st);
     }
-    if (mode == 1 && layer > 0 && !(layer == 1 && net->x0_grad)) {
-        ConvLayer& below = net->L[layer - 1];
+    if (mode == 1 && layer > 0) {
         ConvArgs a;
-        memset(&a, 0, sizeof(a));
-        a.m_total = n * c.lout.img_stride;
-        a.n = c.nin; a.taps = c.taps; a.kchunks = c.ldout / 64;
-        memcpy(a.off, c.off_bwd, sizeof(int) * c.taps);
-        a.in = c.lout; a.dst = c.lout;
-        a.gate_mask = below.mask; a.gate_layout = below.lout;
-        a.out = net->gbuf[(layer - 1) & 1]; a.out_ld = below.ldout; a.b_tap_rows = c.kin;
+        bwd_conv_args(net, layer, n, &a);
         return conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
     }
     set_error("ag_net_run_layer: mode %d not available for layer %d", mode, layer);
@@ -966,7 +1079,7 @@ int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out) {
     const bf16* src; PixelLayout lay;
     if (kind == 0) { src = c.act; lay = c.lout; }
     else if (layer == 0 && net->x0_grad) { src = net->x0_grad; lay = net->lay_in; }
-    else { src = net->gbuf[layer & 1]; lay = c.lout; }
+    else { src = net->gbuf[layer]; lay = c.lout; }
     size_t count = (size_t)n * c.cout * net->board * net->board;
     float* d = nullptr;
     AG_CUDA(cudaMalloc(&d, count * 4));
