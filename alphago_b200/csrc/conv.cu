@@ -662,10 +662,13 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
             tc::fence_before_sync();
             tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier
             // publish the tile: every thread's stores, made visible device-wide, then one release store of the epoch
-            asm volatile("fence.proxy.async.global;" ::: "memory");  // the consumer reads these rows through TMA (async proxy)
-            __threadfence();
+            // (the barrier orders the other 127 threads' stores before thread 0's release, which is cumulative; the consumer
+            // adds the generic -> async proxy fence on its side before TMA reads the rows)
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (et == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + L.flag0 + tile128), "r"(epoch) : "memory");
+            if (et == 0) {
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + L.flag0 + tile128), "r"(epoch) : "memory");
+            }
         }
     }
     tc::fence_before_sync();

@@ -265,3 +265,29 @@ def test_augment_matches_reference_transforms():
         assert np.array_equal(x.cpu().numpy(), want_x)
         assert np.array_equal(y.cpu().numpy(), want_y)
         net.close()
+
+
+def test_forward_and_backward_are_bitwise_repeatable():
+    """The chained launches hand tiles from layer to layer through flags: a missed dependency would show up as run-to-run
+    differences, so the same step twenty times over must give identical bits (activations, gradients)."""
+    import torch
+    board, planes, filters, widths, batch = 19, 48, [192] * 6, [5] + [3] * 5, 64
+    params = no.make_params(planes, filters, widths, seed=21, bias_scale=0.05)
+    net = make_net(board, planes, filters, widths, params, max_batch=batch)
+    rng = np.random.RandomState(3)
+    x = torch.from_numpy((rng.rand(batch, planes, board, board) < 0.3).astype(np.uint8)).cuda()
+    y = torch.from_numpy(rng.randint(0, board * board, batch).astype(np.int32)).cuda()
+    acc = torch.zeros(2, device="cuda")
+    first = None
+    for it in range(20):
+        probs = net.forward(x).cpu().numpy()
+        net.forward_loss(x, y, acc)
+        for l in range(len(filters) - 1, -1, -1):
+            net.backward_layer(l, batch)
+        grads = net.grad_tensor().cpu().numpy().copy()
+        if first is None:
+            first = (probs, grads)
+        else:
+            assert np.array_equal(first[0], probs), "forward differs at repetition %d" % it
+            assert np.array_equal(first[1], grads), "gradients differ at repetition %d" % it
+    net.close()
