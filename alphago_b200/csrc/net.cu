@@ -1043,7 +1043,8 @@ int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_lab
 }
 
 // Measurement hook: re-runs ONE kernel of the step on the buffers the last forward_loss/backward left in
-// place: mode 0 = forward conv of `layer`, 1 = its data gradient, 2 = its weight gradient (+ reduce).
+// place: mode 0 = forward conv of `layer`, 1 = its data gradient, 2 = its weight gradient (+ reduce), 3 = the chained
+// forward stack (all layers, one launch), 4 = the chained data gradients.
 int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
     if (layer < 0 || layer >= net->n_conv || n < 1 || n > net->max_batch) { set_error("ag_net_run_layer: bad argument"); return AG_EINVAL; }
     cudaStream_t st = (cudaStream_t)stream;
@@ -1052,6 +1053,16 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         ConvArgs a;
         fwd_conv_args(net, layer, n, &a);
         return conv_gemm_launch(c.tm_in, c.tm_wf, c.pair_fwd ? &c.tm_wf_half : nullptr, c.win_fwd ? &c.tm_in_win : nullptr, a, st);
+    }
+    if (mode == 3 || mode == 4) {  // the whole forward stack / data-gradient chain as the step launches it (`layer` ignored)
+        if (!(mode == 3 ? net->chain_fwd : net->chain_bwd) || net->chain_n != n) { set_error("ag_net_run_layer: no layer chain built for this batch"); return AG_ESTATE; }
+        unsigned int epoch = mode == 3 ? ++net->chain_epoch_fwd : ++net->chain_epoch_bwd;
+        for (const ChainParams& P : (mode == 3 ? net->chain_fwd_p : net->chain_bwd_p)) {
+            int rc = conv_chain_launch(P, mode == 3 ? net->chain_flags_fwd : net->chain_flags_bwd, epoch, net->chain_win_rows,
+                                       mode == 3 ? net->chain_nmax_fwd : net->chain_nmax_bwd, st);
+            if (rc) return rc;
+        }
+        return AG_OK;
     }
     if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
     if (mode == 2) {

@@ -1,0 +1,31 @@
+"""Condense an .ncu-rep (ncu --set full) into the few numbers DESIGN.md / bench.py quote: per captured launch the kernel
+name, duration, DRAM bytes, tensor-pipe activity, occupancy-side facts.  Usage: python scripts/ncu_summary.py rep.ncu-rep out.json"""
+import csv
+import io
+import json
+import subprocess
+import sys
+
+KEEP = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor.sum", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+        "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "smsp__cycles_active.avg", "sm__cycles_elapsed.max", "smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio"]
+
+
+def main(rep, out):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    head, units, data = rows[0], rows[1], rows[2:]
+    res = {}
+    for k in KEEP:
+        if k in head:
+            i = head.index(k)
+            res[k] = [units[i]] + [r[i][:60] for r in data]
+    json.dump(res, open(out, "w"), indent=1)
+    print(json.dumps(res, indent=1))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2])
