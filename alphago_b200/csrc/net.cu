@@ -444,11 +444,15 @@ struct ConvLayer {
     bool pair_fwd, pair_bwd;
     WgradMaps tm_wg;                            // wgrad operands, exact batch rows (rebuilt when n changes)
     int wgrad_splits;
+    bool wgrad_chain;                           // can take part in a chained weight-gradient launch
+    unsigned int wgrad_chain_count;             // chained launches since its counters were zeroed
 };
 
 }  // namespace ag
 
 using namespace ag;
+
+constexpr int kWgradCounterStride = 64;   // >= tiles of any chained layer
 
 struct ag_net {
     int board, in_planes, n_conv, head_kind, max_batch;
@@ -476,6 +480,8 @@ struct ag_net {
     float* head_partial = nullptr;  // [max_batch][625]
     float* colsum_part = nullptr;   // [colsum_blocks][256]
     float* wgrad_scratch = nullptr;
+    float* wgrad_scratch2 = nullptr;          // second partial buffer: chained weight gradients alternate between the two
+    unsigned int* wgrad_counters = nullptr;   // [n_conv][kWgradCounterStride] split-arrival counters of the chained launches
     size_t wgrad_scratch_floats = 0;
     float* grads = nullptr;  // flat: per conv layer gw then gb; then head w, b, pos
     size_t grad_count = 0;
@@ -608,7 +614,15 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows);
         size_t need = (size_t)c.wgrad_splits * c.wcount;
         if (need > net->wgrad_scratch_floats) { set_error("wgrad scratch too small"); return AG_ESTATE; }
+        WgradArgs w;
+        memset(&w, 0, sizeof(w));
+        w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
+        c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && (c.taps * (c.ldout / 64) + 3) / 4 <= kWgradCounterStride;
     }
+    // the arrival counters count in units of this batch's split factors: start over
+    AG_CUDA(cudaMemsetAsync(net->wgrad_counters, 0, sizeof(unsigned int) * net->n_conv * kWgradCounterStride, 0));
+    AG_CUDA(cudaStreamSynchronize(0));
+    for (auto& c : net->L) c.wgrad_chain_count = 0;
     net->wgrad_n = n;
     return AG_OK;
 }
@@ -667,6 +681,8 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
     rc = dev_alloc(&net->grads, gcount);
     net->wgrad_scratch_floats = scratch;
     if (!rc) rc = dev_alloc(&net->wgrad_scratch, scratch + (size_t)kWgradMaxSplits * 256, false);  // + bias-column partials
+    if (!rc) rc = dev_alloc(&net->wgrad_scratch2, scratch + (size_t)kWgradMaxSplits * 256, false);
+    if (!rc) rc = dev_alloc(&net->wgrad_counters, (size_t)n_conv * kWgradCounterStride);
     if (!rc) rc = dev_alloc(&net->x0, (size_t)max_batch * net->lay_in.img_stride * net->L[0].kin);
     if (!rc && !same_layout) rc = dev_alloc(&net->x0_grad, (size_t)max_batch * net->lay_in.img_stride * net->L[0].ldout);
     net->gbuf.assign(n_conv, nullptr);
@@ -768,7 +784,8 @@ void ag_net_destroy(ag_net* net) {
     if (!net) return;
     for (auto& c : net->L) { cudaFree(c.w); cudaFree(c.b); cudaFree(c.vw); cudaFree(c.vb); cudaFree(c.wf); cudaFree(c.wb); cudaFree(c.act); cudaFree(c.mask); }
     float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
-                  net->head_partial, net->colsum_part, net->wgrad_scratch, net->grads};
+                  net->head_partial, net->colsum_part, net->wgrad_scratch, net->wgrad_scratch2, net->grads};
+    cudaFree(net->wgrad_counters);
     for (float* p : f) cudaFree(p);
     cudaFree(net->sgd_table); cudaFree(net->x0); cudaFree(net->x0_grad);
     for (bf16* g : net->gbuf) cudaFree(g);
@@ -954,46 +971,18 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
     return AG_OK;
 }
 
-// Backward of conv layer `layer` (call for layer = n_conv-1 down to 0 after ag_net_forward_loss):
-// weight + bias gradients into the flat gradient buffer, then (layer > 0) the data gradient,
-// gated by the ReLU of the layer below, as the next layer's pre-activation gradient.
-int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
-    if (layer < 0 || layer >= net->n_conv || n < 1 || n > net->max_batch || net->wgrad_n != n) {
-        set_error("ag_net_backward_layer: bad layer/batch or no forward_loss before it");
-        return AG_EINVAL;
-    }
-    cudaStream_t st = (cudaStream_t)stream;
+// weight (+ bias) gradient of one layer: its own kernel + the split reduction kernel
+static int net_wgrad_one(ag_net* net, int layer, int n, cudaStream_t st) {
     ConvLayer& c = net->L[layer];
-    int rc;
-    if (net->chain_bwd && !net->dgrad_chain_done) {
-        // every data gradient of this backward pass in one launch (G of every layer has its own buffer); the weight
-        // gradients follow layer by layer as the caller asks for them
-        rc = net_build_chains(net, n);
-        if (rc) return rc;
-        ++net->chain_epoch_bwd;
-        for (const ChainParams& P : net->chain_bwd_p) {
-            rc = conv_chain_launch(P, net->chain_flags_bwd, net->chain_epoch_bwd, net->chain_win_rows, net->chain_nmax_bwd, st);
-            if (rc) return rc;
-        }
-        net->dgrad_chain_done = true;
-    }
     const bf16* G = (layer == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[layer];
     const size_t rows = (size_t)n * c.lin.img_stride;
-    // weight gradient
     WgradArgs w;
     memset(&w, 0, sizeof(w));
     w.m_total = (int)rows; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
     w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
     const bool fused_bias = c.kin + 16 <= 256;  // the bias gradient rides in the weight-gradient GEMM as an extra column of ones
     w.bias_scratch = fused_bias ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
-    if (!net->chain_bwd && layer > 0) {
-        // data gradient into the layer below first (it only needs G of this layer; the weight gradient can then overlap nothing it depends on)
-        ConvArgs a;
-        bwd_conv_args(net, layer, n, &a);
-        rc = conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
-        if (rc) return rc;
-    }
-    rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
+    int rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
     if (rc) return rc;
     if (!fused_bias) {
         launch_k(colsum_stage1_kernel, dim3(net->colsum_blocks), dim3(256), 0, st, G, rows, c.ldout, net->colsum_part);
@@ -1003,6 +992,84 @@ int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) {
     }
     return AG_OK;
 }
+
+static bool same_wgrad_geometry(const ConvLayer& a, const ConvLayer& b) {
+    return a.taps == b.taps && a.ldout == b.ldout && a.kin == b.kin && a.wgrad_splits == b.wgrad_splits && a.lin.img_stride == b.lin.img_stride &&
+           a.tm_wg.win_rows == b.tm_wg.win_rows && a.tm_wg.krows == b.tm_wg.krows && memcmp(a.off_fwd, b.off_fwd, sizeof(int) * a.taps) == 0;
+}
+
+// weight gradients of layers hi .. lo: runs of layers with one geometry go out as chained launches (wgrad.cu)
+static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) {
+    int l = hi;
+    while (l >= lo) {
+        ConvLayer& first = net->L[l];
+        if (!first.wgrad_chain) {
+            int rc = net_wgrad_one(net, l, n, st);
+            if (rc) return rc;
+            l--;
+            continue;
+        }
+        WgradChainEntry e[kWgradChainMaxLayers];
+        int cnt = 0;
+        while (l >= lo && cnt < kWgradChainMaxLayers && net->L[l].wgrad_chain && same_wgrad_geometry(net->L[l], first)) {
+            ConvLayer& c = net->L[l];
+            float* scratch = (cnt & 1) ? net->wgrad_scratch2 : net->wgrad_scratch;
+            e[cnt].maps = &c.tm_wg;
+            e[cnt].scratch = scratch;
+            e[cnt].bias_scratch = scratch + net->wgrad_scratch_floats;
+            e[cnt].dw = c.gw; e[cnt].db = c.gb;
+            e[cnt].counters = net->wgrad_counters + (size_t)l * kWgradCounterStride;
+            e[cnt].target = ++c.wgrad_chain_count * (unsigned int)c.wgrad_splits;
+            cnt++;
+            l--;
+        }
+        WgradArgs w;
+        memset(&w, 0, sizeof(w));
+        w.m_total = n * first.lin.img_stride; w.taps = first.taps; memcpy(w.off, first.off_fwd, sizeof(int) * first.taps);
+        w.ldout = first.ldout; w.kin = first.kin; w.splits = first.wgrad_splits;
+        int rc = wgrad_chain_launch(w, e, cnt, st);
+        if (rc) return rc;
+    }
+    return AG_OK;
+}
+
+// Backward of conv layers hi .. lo (hi >= lo; call with descending, non-overlapping ranges after ag_net_forward_loss,
+// starting at n_conv-1): weight + bias gradients into the flat gradient buffer and the data gradients into the layers
+// below, each gated by the ReLU of the layer it lands in.
+int ag_net_backward_range(ag_net* net, int hi, int lo, int n, void* stream) {
+    if (lo < 0 || hi >= net->n_conv || lo > hi || n < 1 || n > net->max_batch || net->wgrad_n != n) {
+        set_error("ag_net_backward_range: bad layers/batch or no forward_loss before it");
+        return AG_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc;
+    if (net->chain_bwd) {
+        if (!net->dgrad_chain_done) {
+            // every data gradient of this backward pass in one launch (G of every layer has its own buffer); the weight
+            // gradients follow range by range as the caller asks for them
+            rc = net_build_chains(net, n);
+            if (rc) return rc;
+            ++net->chain_epoch_bwd;
+            for (const ChainParams& P : net->chain_bwd_p) {
+                rc = conv_chain_launch(P, net->chain_flags_bwd, net->chain_epoch_bwd, net->chain_win_rows, net->chain_nmax_bwd, st);
+                if (rc) return rc;
+            }
+            net->dgrad_chain_done = true;
+        }
+    } else {
+        for (int l = hi; l >= lo && l > 0; l--) {  // data gradient of layer l into the layer below (needs only G of layer l)
+            ConvLayer& c = net->L[l];
+            ConvArgs a;
+            bwd_conv_args(net, l, n, &a);
+            rc = conv_gemm_launch(c.tm_g, c.tm_wb, c.pair_bwd ? &c.tm_wb_half : nullptr, c.win_bwd ? &c.tm_g_win : nullptr, a, st);
+            if (rc) return rc;
+        }
+    }
+    return net_wgrad_range(net, hi, lo, n, st);
+}
+
+// Backward of one conv layer (call for layer = n_conv-1 down to 0 after ag_net_forward_loss).
+int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream) { return ag_net_backward_range(net, layer, layer, n, stream); }
 
 // Flat fp32 gradient buffer (device): conv layers in order (weights [tap][ldout][kin] then bias [ldout]),
 // then the head (w[256], b[1], pos[368]).  h_offsets receives n_conv+2 element offsets (layer starts,
@@ -1037,7 +1104,7 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
 int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_labels, int n, float lr, float momentum,
                       float* d_loss_acc, void* stream) {
     int rc = ag_net_forward_loss(net, d_planes, d_labels, n, nullptr, d_loss_acc, stream);
-    for (int l = net->n_conv - 1; l >= 0 && !rc; l--) rc = ag_net_backward_layer(net, l, n, stream);
+    if (!rc) rc = ag_net_backward_range(net, net->n_conv - 1, 0, n, stream);
     if (!rc) rc = ag_net_sgd(net, lr, momentum, 1.f, stream);
     return rc;
 }

@@ -52,6 +52,41 @@ struct WgradPlan {
     int lo[2], hi[2];        // slots behind rows 0-63 / 64-127 of each accumulator (hi = -1: dead half); lo has the lower address
 };
 
+// Per-CTA constants (see WgradPlan), worked out once by one thread.
+__device__ __forceinline__ void wgrad_make_plan(const WgradArgs& p, WgradPlan* plan, const bool taps_in_n, const bool windowed,
+                                                const int chunk_bytes, const int a_first, const int a_live) {
+    const int win_bytes = windowed ? ((p.win_rows * 128 + 1023) & ~1023) : chunk_bytes;
+    int cc[kASlots], shift[kASlots], win_of[kASlots];
+    int n_win = 0;
+    for (int i = 0; i < kASlots; i++) {
+        plan->slot_off[i] = -1; plan->slot_row[i] = 0; plan->slot_bias[i] = -1;
+        if (i >= a_live) continue;
+        const int c = a_first + i;
+        int tap = 0;
+        if (taps_in_n) { cc[i] = c; shift[i] = 0; }
+        else { cc[i] = c / p.taps; tap = c - cc[i] * p.taps; shift[i] = p.off[tap]; }
+        plan->slot_row[i] = tap * p.ldout + cc[i] * 64;
+        if (taps_in_n || tap == p.taps / 2) plan->slot_bias[i] = cc[i] * 64;  // unshifted G: its column sums are the bias gradient
+        if (windowed && i > 0 && cc[i] == cc[i - 1]) {
+            win_of[i] = win_of[i - 1];
+        } else {
+            win_of[i] = n_win;
+            plan->win_off[n_win] = n_win * win_bytes;
+            plan->win_col[n_win] = cc[i] * 64;
+            n_win++;
+        }
+        plan->win_shift[win_of[i]] = shift[i];  // shifts grow with the tap: the last member's is the window's first row
+    }
+    plan->n_win = n_win;
+    for (int i = 0; i < a_live; i++) plan->slot_off[i] = plan->win_off[win_of[i]] + (plan->win_shift[win_of[i]] - shift[i]) * 128;
+    for (int a = 0; a < 2; a++) {
+        const int s0 = 2 * a, s1 = 2 * a + 1;
+        if (s1 >= a_live) { plan->lo[a] = s0; plan->hi[a] = -1; }
+        else if (plan->slot_off[s0] < plan->slot_off[s1]) { plan->lo[a] = s0; plan->hi[a] = s1; }
+        else { plan->lo[a] = s1; plan->hi[a] = s0; }
+    }
+}
+
 // The kernel is bound by L2 -> shared-memory bandwidth, not by the tensor cores (a 128-row tile alone would need 16 KB
 // of G and 24 KB of X per 4 UMMAs; the chip's L2 delivers ~43 B per SM per cycle), so
 //   * a CTA owns TWO 128-row tiles that share the X operand: two accumulators in TMEM, 8 UMMAs per stage;
@@ -100,37 +135,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         tc::tma_prefetch_desc(&tmap_g);
         tc::tma_prefetch_desc(&tmap_gw);
         tc::tma_prefetch_desc(&tmap_x);
-        // ---- the plan
-        const int win_bytes = windowed ? ((p.win_rows * 128 + 1023) & ~1023) : chunk_bytes;
-        int cc[kASlots], shift[kASlots], win_of[kASlots];
-        int n_win = 0;
-        for (int i = 0; i < kASlots; i++) {
-            plan->slot_off[i] = -1; plan->slot_row[i] = 0; plan->slot_bias[i] = -1;
-            if (i >= a_live) continue;
-            const int c = a_first + i;
-            int tap = 0;
-            if (taps_in_n) { cc[i] = c; shift[i] = 0; }
-            else { cc[i] = c / p.taps; tap = c - cc[i] * p.taps; shift[i] = p.off[tap]; }
-            plan->slot_row[i] = tap * p.ldout + cc[i] * 64;
-            if (taps_in_n || tap == p.taps / 2) plan->slot_bias[i] = cc[i] * 64;  // unshifted G: its column sums are the bias gradient
-            if (windowed && i > 0 && cc[i] == cc[i - 1]) {
-                win_of[i] = win_of[i - 1];
-            } else {
-                win_of[i] = n_win;
-                plan->win_off[n_win] = n_win * win_bytes;
-                plan->win_col[n_win] = cc[i] * 64;
-                n_win++;
-            }
-            plan->win_shift[win_of[i]] = shift[i];  // shifts grow with the tap: the last member's is the window's first row
-        }
-        plan->n_win = n_win;
-        for (int i = 0; i < a_live; i++) plan->slot_off[i] = plan->win_off[win_of[i]] + (plan->win_shift[win_of[i]] - shift[i]) * 128;
-        for (int a = 0; a < 2; a++) {
-            const int s0 = 2 * a, s1 = 2 * a + 1;
-            if (s1 >= a_live) { plan->lo[a] = s0; plan->hi[a] = -1; }
-            else if (plan->slot_off[s0] < plan->slot_off[s1]) { plan->lo[a] = s0; plan->hi[a] = s1; }
-            else { plan->lo[a] = s1; plan->hi[a] = s0; }
-        }
+        wgrad_make_plan(p, plan, taps_in_n, windowed, chunk_bytes, a_first, a_live);
     }
     if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
     if (with_bias) {  // the ones chunk of every stage (all elements equal, so the swizzle does not matter)
@@ -303,6 +308,248 @@ wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, s
     }
 }
 
+// ---- Weight gradients of a run of layers with identical geometry in ONE launch, split reduction included.
+// Per layer a CTA does the same (tile, split) work item as wgrad_kernel; what changes is what happens around it:
+//   * no launch / prologue / pipeline fill per layer: the TMA ring simply continues with the next layer's operands while the
+//     epilogue warps are still busy with this one's accumulators;
+//   * the split-K reduction is done by the same CTAs: after writing its partial a CTA bumps the tile's counter, waits until all
+//     `splits` partials of the tile are there, and sums its 1/splits share of the tile's rows (same association as
+//     wgrad_reduce_kernel: bit-identical results) -- all on the epilogue warps, which would otherwise idle during the next
+//     layer's main loop.  Needs every CTA of the grid resident at once (checked on the host).
+// Partials alternate between two scratch buffers by layer parity (a CTA cannot reach layer l+2 before every CTA of its tile
+// has finished reducing layer l, see the counter wait), so they stay in L2.
+constexpr int kWgradChainMax = 16;
+struct WgradChainLayer {
+    CUtensorMap g, gw, x;
+    float* scratch;        // this layer's partial buffer [splits][taps*ldout][kin]
+    float* bias_scratch;   // [splits][ldout]
+    float* dw;             // [taps][ldout][kin]
+    float* db;             // [ldout]
+    unsigned int* counters;  // [tiles], running totals over launches
+    unsigned int target;     // counter value that means "all splits of this launch have arrived"
+};
+struct WgradChainParams {
+    WgradArgs a;           // shared geometry (scratch pointers unused)
+    WgradChainLayer layers[kWgradChainMax];
+    int n_layers;
+};
+
+__device__ __forceinline__ float4 ldcg4(const float4* p) {  // L2 only: other CTAs wrote these lines during this launch
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
+    const WgradArgs& p = P.a;
+    const int xchunks = p.kin / 64;
+    const int cochunks = p.ldout / 64;
+    const int chunk_bytes = p.krows * 128;
+    const int a_region = kASlots * chunk_bytes;
+    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
+    const bool windowed = p.win_rows > 0;
+    const int a_first = tile * kASlots;
+    const int a_count = p.taps * cochunks;
+    const int a_live = min(kASlots, a_count - a_first);
+    const bool with_bias = P.layers[0].bias_scratch != nullptr;
+    const int stage_bytes = a_region + (xchunks + (with_bias ? 1 : 0)) * chunk_bytes;
+    const int ones_off = a_region + xchunks * chunk_bytes;
+    const int acc_cols = xchunks * 64;
+    const int umma_n = acc_cols + (with_bias ? 16 : 0);
+    WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(base + kStages * stage_bytes);
+    WgradPlan* plan = reinterpret_cast<WgradPlan*>(bars + 1);
+    uint64_t* acc_empty = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(plan + 1) + 7) & ~uintptr_t(7));
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+
+    const int kb_total = (p.m_total + p.krows - 1) / p.krows;
+    const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
+
+    pdl_trigger();
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
+        tc::mbar_init(&bars->acc_full, 1);
+        tc::mbar_init(acc_empty, 128);
+        tc::fence_mbar_init();
+        wgrad_make_plan(p, plan, false, windowed, chunk_bytes, a_first, a_live);
+    }
+    if (warp == 1) tc::tmem_alloc(&bars->tmem_base, kTmemCols);
+    if (with_bias) {  // the ones chunk of every stage (all elements equal, so the swizzle does not matter)
+        for (int s = 0; s < kStages; s++) {
+            uint32_t* ones = reinterpret_cast<uint32_t*>(base + s * stage_bytes + ones_off);
+            for (int i = threadIdx.x; i < chunk_bytes / 4; i += kThreads) ones[i] = 0x3F803F80u;  // bf16 1.0 x2
+        }
+        tc::fence_proxy_async();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_base;
+    pdl_wait();
+
+    if (warp == 0) {
+        // producer: one ring over all layers
+        const int n_win = plan->n_win;
+        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : chunk_bytes) + xchunks * chunk_bytes);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int li = 0; li < P.n_layers; li++) {
+            const WgradChainLayer& L = P.layers[li];
+            const CUtensorMap* gmap = windowed ? &L.gw : &L.g;
+            for (int kb = kb0; kb < kb1; kb++) {
+                tc::mbar_wait(&bars->empty[stage], phase ^ 1);
+                if (tc::elect_one()) {
+                    uint8_t* s = base + stage * stage_bytes;
+                    tc::mbar_expect_tx(&bars->full[stage], tx_bytes);
+                    const int m0 = kb * p.krows;
+                    for (int w = 0; w < n_win; w++)  // rows outside the tensor read as zeros
+                        tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
+                    for (int c = 0; c < xchunks; c++)
+                        tc::tma_load_2d(s + a_region + c * chunk_bytes, &L.x, &bars->full[stage], c * 64, m0);
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        const uint32_t idesc = tc::idesc_bf16(128, umma_n, 1, 1);
+        const bool second = a_live > 2;
+        uint32_t a_off[2], a_lbo[2];
+        for (int a = 0; a < 2; a++) {
+            const int lo = plan->lo[a], hi = plan->hi[a];
+            a_off[a] = (uint32_t)max(plan->slot_off[lo], 0);
+            a_lbo[a] = hi >= 0 ? (uint32_t)(plan->slot_off[hi] - plan->slot_off[lo]) : (uint32_t)chunk_bytes;
+        }
+        const int ksteps = p.krows / 16;
+        int stage = 0;
+        uint32_t phase = 0;
+        bool ready = false;
+        for (int li = 0; li < P.n_layers; li++) {
+            tc::mbar_wait(acc_empty, (li & 1) ^ 1);  // the epilogue warps have read the previous layer's accumulators out of TMEM
+            tc::fence_after_sync();
+            for (int kb = kb0; kb < kb1; kb++) {
+                if (!ready) tc::mbar_wait(&bars->full[stage], phase);
+                tc::fence_after_sync();
+                if (tc::elect_one()) {
+                    const uint32_t s = tc::smem_u32(base + stage * stage_bytes);
+                    const uint64_t adesc0 = tc::desc_mnmajor_sw128(s + a_off[0], a_lbo[0]);
+                    const uint64_t adesc1 = tc::desc_mnmajor_sw128(s + a_off[1], a_lbo[1]);
+                    const uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
+#pragma unroll 4
+                    for (int k = 0; k < ksteps; k++) {  // 16 pixel rows per UMMA: +2048 B
+                        tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                        if (second)
+                            tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                    }
+                    tc::umma_commit(&bars->empty[stage]);
+                    if (kb == kb1 - 1) tc::umma_commit(&bars->acc_full);
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                ready = tc::mbar_try_wait(&bars->full[stage], phase);
+            }
+        }
+    } else {
+        // epilogue warps: partial out of TMEM, then this CTA's share of the tile's split reduction
+        const int q = warp & 3, et = threadIdx.x - 64;
+        const int r = q * 32 + lane;
+        const size_t count4 = (size_t)p.taps * p.ldout * p.kin / 4;
+        const int kin4 = p.kin / 4;
+        const int units = a_live * 64 * kin4;  // float4 elements of this tile's dW rows
+        const int u0 = (int)((long long)units * split / p.splits), u1 = (int)((long long)units * (split + 1) / p.splits);
+        for (int li = 0; li < P.n_layers; li++) {
+            const WgradChainLayer& L = P.layers[li];
+            tc::mbar_wait(&bars->acc_full, li & 1);
+            tc::fence_after_sync();
+            for (int a = 0; a < 2; a++) {
+                if (a * 2 >= a_live) break;  // warp-uniform
+                const int slot = (r >> 6) ? plan->hi[a] : plan->lo[a];
+                const bool valid = slot >= 0;
+                const int srow = valid ? plan->slot_row[slot] : 0;
+                float* dst = L.scratch + ((size_t)split * p.taps * p.ldout + (size_t)srow + (r & 63)) * p.kin;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * kAccStride;
+                for (int c0 = 0; c0 < acc_cols; c0 += 32) {
+                    uint32_t v[32];
+                    tc::tmem_ld32(taddr + c0, v);
+                    tc::tmem_ld_wait();
+                    if (valid) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    }
+                }
+                if (with_bias && valid && plan->slot_bias[slot] >= 0) {
+                    uint32_t v[32];
+                    tc::tmem_ld32(taddr + acc_cols, v);
+                    tc::tmem_ld_wait();
+                    L.bias_scratch[(size_t)split * p.ldout + plan->slot_bias[slot] + (r & 63)] = __uint_as_float(v[0]);
+                }
+            }
+            tc::fence_before_sync();
+            tc::mbar_arrive(acc_empty);  // TMEM is free for the next layer's UMMAs
+            // ---- publish the partial, wait for the tile's other splits
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (et == 0) {
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(L.counters + tile) : "memory");
+                unsigned int v;
+                long long t0 = 0;
+                for (;;) {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(L.counters + tile) : "memory");
+                    if (v >= L.target) break;
+                    if (t0 == 0) t0 = clock64();
+                    else if (clock64() - t0 > 4000000000LL) {
+                        printf("alphago_b200: wgrad chain split wait timed out (block %d layer %d counter %u, want %u)\n", blockIdx.x, li, v, L.target);
+                        __trap();
+                    }
+                    __nanosleep(64);
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
+            // ---- this CTA's share of the tile: units [u0, u1), four interleaved partial sums added in order
+            const float4* s4 = reinterpret_cast<const float4*>(L.scratch);
+            float4* d4 = reinterpret_cast<float4*>(L.dw);
+            for (int u = u0 + et; u < u1; u += 128) {
+                const int sl = u / (64 * kin4);
+                const int rem = u - sl * 64 * kin4;
+                const size_t i = (size_t)(plan->slot_row[sl] + rem / kin4) * kin4 + (rem % kin4);
+                float4 acc[kReduceWays];
+#pragma unroll
+                for (int w = 0; w < kReduceWays; w++) {
+                    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int s = w; s < p.splits; s += kReduceWays) {
+                        const float4 b = ldcg4(s4 + (size_t)s * count4 + i);
+                        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                    }
+                    acc[w] = a;
+                }
+                float4 a = acc[0];
+#pragma unroll
+                for (int w = 1; w < kReduceWays; w++) { a.x += acc[w].x; a.y += acc[w].y; a.z += acc[w].z; a.w += acc[w].w; }
+                d4[i] = a;
+            }
+            if (with_bias && split == 0 && et < 64) {
+                for (int sl = 0; sl < a_live; sl++) {
+                    if (plan->slot_bias[sl] < 0) continue;
+                    const int c = plan->slot_bias[sl] + et;
+                    float t = 0.f;
+                    for (int s = 0; s < p.splits; s++) t += __ldcg(L.bias_scratch + (size_t)s * p.ldout + c);
+                    L.db[c] = t;
+                }
+            }
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
 }  // namespace
 
 // Tiling choice: taps per B operand (1 = shifted-G tiling) and the CTA tiles of one split.  Taps in N needs a spare
@@ -417,6 +664,55 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     launch_k(wgrad_reduce_kernel, dim3(grid), dim3(kReduceCols * kReduceWays), 0, stream, args.scratch, dw, count4, args.splits, args.bias_scratch,
              args.bias_scratch ? db : nullptr, args.ldout);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
+    return AG_OK;
+}
+
+// ---- chained launch (wgrad_chain_kernel): layers share args' geometry; each entry brings its maps, buffers and counters
+bool wgrad_chain_ok(const WgradArgs& a_in, const WgradMaps& maps, bool with_bias) {
+    static int enabled = -1;
+    if (enabled < 0) { const char* e = getenv("AG_WGRAD_CHAIN"); enabled = (e && e[0] == '0') ? 0 : 1; }
+    if (!enabled) return false;
+    WgradArgs a = a_in;
+    a.tiles = wgrad_tiling(a.taps, a.ldout, a.kin, &a.tpg, &a.groups);
+    if (a.tpg != 1 || a.kin % 64 || a.ldout % 64 || a.kin > 256) return false;
+    if (with_bias && a.kin + 16 > 256) return false;
+    const int kb_total = (a.m_total + maps.krows - 1) / maps.krows;
+    if (a.splits < 1 || kb_total < a.splits) return false;
+    // every CTA must be resident at once (they wait for each other's partials): one CTA per SM with this much shared memory
+    return a.tiles * a.splits <= sm_count() && wgrad_stages(a.taps, a.kin, with_bias, maps.krows) >= 2;
+}
+
+int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_layers, cudaStream_t stream) {
+    if (n_layers < 1) return AG_OK;
+    if (n_layers > kWgradChainMax) { set_error("wgrad chain: %d layers in one launch (max %d)", n_layers, kWgradChainMax); return AG_EINVAL; }
+    WgradChainParams P;
+    memset(&P, 0, sizeof(P));
+    args.tiles = wgrad_tiling(args.taps, args.ldout, args.kin, &args.tpg, &args.groups);
+    args.win_rows = entries[0].maps->win_rows;
+    args.krows = entries[0].maps->krows;
+    args.debug = 0;
+    const bool with_bias = entries[0].bias_scratch != nullptr;
+    for (int i = 0; i < n_layers; i++) {
+        WgradChainLayer& L = P.layers[i];
+        L.g = entries[i].maps->g; L.gw = entries[i].maps->gw; L.x = entries[i].maps->x;
+        L.scratch = entries[i].scratch; L.bias_scratch = entries[i].bias_scratch;
+        L.dw = entries[i].dw; L.db = entries[i].db; L.counters = entries[i].counters; L.target = entries[i].target;
+        if ((entries[i].bias_scratch != nullptr) != with_bias || entries[i].maps->win_rows != args.win_rows) {
+            set_error("wgrad chain: layers of one launch must share their geometry");
+            return AG_EINVAL;
+        }
+    }
+    P.a = args; P.n_layers = n_layers;
+    const int stages = wgrad_stages(args.taps, args.kin, with_bias, args.krows);
+    size_t smem = wgrad_smem_bytes(args.taps, args.kin, with_bias, args.krows);
+    if (smem < 120 * 1024) smem = 120 * 1024;  // one CTA per SM (see wgrad_chain_ok)
+    static size_t configured = 0;
+    if (smem > configured) {
+        AG_CUDA(cudaFuncSetAttribute(wgrad_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    launch_k(wgrad_chain_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, P, stages);
+    AG_LAUNCH_CHECK("wgrad_chain_kernel");
     return AG_OK;
 }
 

@@ -39,4 +39,20 @@ int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, i
 // db (optional, needs args.bias_scratch and kin <= 240): [ldout] fp32 bias gradient = sum over all rows of G
 int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cudaStream_t stream);
 
+// One layer of a chained weight-gradient launch (wgrad.cu, wgrad_chain_kernel): same geometry for all, own buffers each.
+struct WgradChainEntry {
+    const WgradMaps* maps;
+    float* scratch;            // [splits][taps*ldout][kin]; consecutive entries must alternate between two buffers
+    float* bias_scratch;       // [splits][ldout] or nullptr (then db is not produced)
+    float* dw;
+    float* db;
+    unsigned int* counters;    // [tiles] arrival counters (running totals over launches)
+    unsigned int target;       // their value once this launch's partials are all in: (launches so far, this one included) * splits
+};
+// can this problem run chained (taps not folded into N, all CTAs resident at once, ...)?
+bool wgrad_chain_ok(const WgradArgs& args, const WgradMaps& maps, bool with_bias);
+// weight (+bias) gradients of n_layers layers in one launch, split reduction included; args: m_total, taps, off, ldout, kin, splits
+int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_layers, cudaStream_t stream);
+constexpr int kWgradChainMaxLayers = 16;
+
 }  // namespace ag

@@ -119,6 +119,10 @@ class ConvNet(object):
                                                 lr, momentum, C.c_void_p(loss_acc.data_ptr()), _lib.current_stream()),
                    "ag_net_train_step")
 
+    def backward_range(self, hi, lo, n):
+        """backward of layers hi .. lo in one call (descending ranges after forward_loss): equal layers share chained launches"""
+        _lib.check(_lib.lib().ag_net_backward_range(self._h, hi, lo, n, _lib.current_stream()), "ag_net_backward_range")
+
     def run_layer(self, layer, mode, n):
         _lib.check(_lib.lib().ag_net_run_layer(self._h, layer, mode, n, _lib.current_stream()), "ag_net_run_layer")
 

@@ -93,8 +93,7 @@ class SLTrainer(object):
             net.forward_loss(planes, labels, self.loss_acc)
 
             def backward_bucket(i, lo, hi):
-                for l in range(hi - 1, lo - 1, -1):
-                    net.backward_layer(l, n)
+                net.backward_range(hi - 1, lo, n)
             # each bucket is reduced as soon as its layers' gradients are enqueued: NCCL's stream picks up after the
             # kernels issued so far, so the exchange overlaps the backward of the layers below
             works = allreduce_in_buckets(self.dist, net.grad_tensor(), self.plan, self.group, backward_bucket)

@@ -124,6 +124,10 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
 /* backward of conv layer `layer`; call for n_conv-1 ... 0 after ag_net_forward_loss (fit_generator's backprop,
  * supervised_policy_trainer.py:207-213).  The layer's slice of the gradient buffer is final when it returns. */
 int ag_net_backward_layer(ag_net* net, int layer, int n, void* stream);
+/* the same for layers hi .. lo in one call (descending, non-overlapping ranges starting at n_conv-1): lets runs of equal
+ * layers share one chained launch; what data-parallel training calls per gradient bucket.  Replaces the same Keras
+ * backward pass as ag_net_backward_layer (supervised_policy_trainer.py:207-213). */
+int ag_net_backward_range(ag_net* net, int hi, int lo, int n, void* stream);
 /* the flat fp32 gradient buffer (device) data-parallel training all-reduces; h_offsets gets n_conv+2 offsets */
 int ag_net_grads(ag_net* net, float** d_grads, long long* count, long long* h_offsets);
 /* fused SGD(+momentum) over all parameters; gradients are multiplied by grad_scale first
