@@ -487,6 +487,7 @@ struct ag_net {
     size_t grad_count = 0;
     std::vector<long long> grad_offsets;  // start of each conv layer's slice, then head, then end
     int wgrad_n = -1;
+    int sm_budget = 0;   // SMs the weight-gradient launches may fill (0 = all)
     int colsum_blocks = 0;
     long long iterations = 0;
     void* sgd_table = nullptr;      // device copy of the SGD kernel's per-layer table
@@ -611,7 +612,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         uint64_t rows = (uint64_t)n * c.lin.img_stride;
         int rc = wgrad_make_maps(&c.tm_wg, g, xin, rows, c.ldout, c.kin, c.taps, c.off_fwd);
         if (rc) return rc;
-        c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows);
+        c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows, net->sm_budget);
         size_t need = (size_t)c.wgrad_splits * c.wcount;
         if (need > net->wgrad_scratch_floats) { set_error("wgrad scratch too small"); return AG_ESTATE; }
         WgradArgs w;
@@ -669,7 +670,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         net->grad_offsets.push_back((long long)gcount);
         gcount += c.wcount + c.ldout;
         size_t rows_in = (size_t)max_batch * c.lin.img_stride;
-        int splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows_in);
+        int splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows_in, 0);
         if ((size_t)kWgradMaxSplits * c.wcount > scratch) scratch = (size_t)kWgradMaxSplits * c.wcount;
         (void)splits;
     }
@@ -1097,6 +1098,16 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
              net->sgd_tiles, flats, lr, momentum, grad_scale);
     AG_LAUNCH_CHECK("sgd_all_kernel");
     net->iterations++;
+    return AG_OK;
+}
+
+// SMs the weight-gradient launches may fill (0 = all, the default).  Data-parallel training sets this a little below the SM
+// count: the chained weight gradients need all their CTAs resident at once, and the all-reduce of the previous gradient
+// bucket is running on a few SMs at the same time.
+int ag_net_set_sm_budget(ag_net* net, int sms) {
+    if (sms < 0) { set_error("ag_net_set_sm_budget: negative"); return AG_EINVAL; }
+    net->sm_budget = sms;
+    net->wgrad_n = -1;  // re-plan the split factors at the next forward_loss
     return AG_OK;
 }
 

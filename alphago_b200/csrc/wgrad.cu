@@ -619,13 +619,13 @@ int wgrad_make_maps(WgradMaps* m, const void* g, const void* x, uint64_t rows, i
     return rc;
 }
 
-int wgrad_plan_splits(int taps, int ldout, int kin, int m_total) {
+int wgrad_plan_splits(int taps, int ldout, int kin, int m_total, int sm_budget) {
     // CTAs = tiles * splits should fill whole waves of the SMs: one wave if that keeps >= 85 % of them busy,
     // else two.  Fewer, longer K slices also mean fewer fp32 partials to write and reduce.
     int tpg, groups;
     int tiles = wgrad_tiling(taps, ldout, kin, &tpg, &groups);
     int kb = (m_total + 63) / 64;
-    int sms = sm_count();
+    int sms = sm_budget > 0 && sm_budget < sm_count() ? sm_budget : sm_count();  // SMs the grid may occupy
     int s1 = sms / tiles, s2 = 2 * sms / tiles;
     int s = s1;
     if (s1 < 1 || ((double)tiles * s1 / sms < 0.85 && (double)tiles * s2 / (2.0 * sms) > (double)tiles * s1 / sms + 0.05)) s = s2;
@@ -739,7 +739,7 @@ extern "C" {
 // bytes of scratch ag_wgrad wants for this problem (the split-K partials)
 size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows) {
     if (ag::wgrad_check(rows, ldout, kin, 1) || width < 1 || width > 5) return 0;
-    return (size_t)ag::wgrad_plan_splits(width * width, ldout, kin, (int)rows) * width * width * ldout * kin * sizeof(float);
+    return (size_t)ag::wgrad_plan_splits(width * width, ldout, kin, (int)rows, 0) * width * width * ldout * kin * sizeof(float);
 }
 
 int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride, float* d_scratch,
@@ -752,7 +752,7 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
     if (rc) return rc;
     a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
     const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
-    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows);
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows, 0);
     if ((size_t)a.splits * partial > scratch_bytes) a.splits = (int)(scratch_bytes / partial);
     if (a.splits < 1 || !d_scratch) { ag::set_error("ag_wgrad: scratch of %zu bytes is smaller than one partial (%zu bytes)", scratch_bytes, partial); return AG_EINVAL; }
     a.scratch = d_scratch;
@@ -814,7 +814,7 @@ int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout,
                       "use ag_wgrad with your own scratch", width, width, ldout, kin, partial, AG_WGRAD_STATIC_SCRATCH_BYTES);
         return AG_EINVAL;
     }
-    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows);
+    a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows, 0);
     if ((size_t)a.splits * partial > AG_WGRAD_STATIC_SCRATCH_BYTES) a.splits = (int)(AG_WGRAD_STATIC_SCRATCH_BYTES / partial);
     rc = ag::wgrad_static_scratch_ptr(&a.scratch);
     if (rc) return rc;

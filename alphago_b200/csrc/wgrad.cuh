@@ -27,7 +27,8 @@ struct WgradArgs {
     float* bias_scratch;  // nullptr, or [splits][ldout] fp32: column sums of G (the bias gradient) ride along as one more B column
 };
 
-int wgrad_plan_splits(int taps, int ldout, int kin, int m_total);
+// sm_budget: SMs the launch may fill (0 = all): data-parallel training leaves a few to the collective running beside it
+int wgrad_plan_splits(int taps, int ldout, int kin, int m_total, int sm_budget);
 // Tensor maps of one weight-gradient problem: G [rows][ldout] and X [rows][kin] with box [krows][64] and EXACTLY `rows`
 // rows (rows past the batch must read as zeros), plus G with a box of win_rows rows (the shared window, wgrad.cu).
 struct WgradMaps {

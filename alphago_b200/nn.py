@@ -119,6 +119,10 @@ class ConvNet(object):
                                                 lr, momentum, C.c_void_p(loss_acc.data_ptr()), _lib.current_stream()),
                    "ag_net_train_step")
 
+    def set_sm_budget(self, sms):
+        """SMs the weight-gradient launches may fill (0 = all); see ag_net_set_sm_budget"""
+        _lib.check(_lib.lib().ag_net_set_sm_budget(self._h, int(sms)), "ag_net_set_sm_budget")
+
     def backward_range(self, hi, lo, n):
         """backward of layers hi .. lo in one call (descending ranges after forward_loss): equal layers share chained launches"""
         _lib.check(_lib.lib().ag_net_backward_range(self._h, hi, lo, n, _lib.current_stream()), "ag_net_backward_range")

@@ -18,14 +18,20 @@ from . import _lib, nn
 def plan_buckets(n_conv, offsets, buckets=4):
     """Gradient exchange plan: [(layer_lo, layer_hi, start, end)] over the flat gradient buffer, in the order the
     slices become final during backward (last layers first).  `offsets` = n_conv+2 element offsets (layer starts,
-    head start, end); the first bucket also carries the head's slice (ready right after the loss)."""
-    per = max(1, (n_conv + buckets - 1) // buckets)
+    head start, end); the first bucket also carries the head's slice (ready right after the loss).  The LAST bucket is
+    the first layer alone: nothing is left to overlap its all-reduce with, so it should be the smallest."""
+    buckets = max(1, min(buckets, n_conv))
+    tail = 1 if (buckets >= 2 and n_conv >= 3) else 0
+    body = buckets - tail
+    per = max(1, (n_conv - tail + body - 1) // body)
     plan, hi = [], n_conv
-    while hi > 0:
-        lo = max(0, hi - per)
+    while hi > tail:
+        lo = max(tail, hi - per)
         end = offsets[-1] if not plan else offsets[hi]
         plan.append((lo, hi, offsets[lo], end))
         hi = lo
+    if tail:
+        plan.append((0, tail, offsets[0], offsets[tail] if plan else offsets[-1]))
     return plan
 
 
@@ -41,7 +47,7 @@ def allreduce_in_buckets(dist, flat, plan, group=None, after_bucket=None):
 
 
 class SLTrainer(object):
-    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=4, process_group=None):
+    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=2, process_group=None):
         import torch
         self.torch = torch
         self.net, self.lr0, self.decay, self.momentum = net, float(lr), float(decay), float(momentum)
@@ -55,8 +61,15 @@ class SLTrainer(object):
                 self.dist, self.world, self.group = dist, dist.get_world_size(process_group), process_group
         except ImportError:
             pass
+        if self.dist is not None:
+            # the all-reduce of bucket k runs on a few SMs while bucket k+1's weight gradients are computed: leave it room
+            import os
+            import torch as _t
+            sms = _t.cuda.get_device_properties(_t.cuda.current_device()).multi_processor_count
+            net.set_sm_budget(max(1, sms - int(os.environ.get("AG_DP_RESERVE_SMS", "8"))))
         # gradient buckets: contiguous runs of layers, last layers first (they finish first in backward)
-        self.plan = plan_buckets(net.n_conv, net.grad_offsets, buckets)
+        import os as _os
+        self.plan = plan_buckets(net.n_conv, net.grad_offsets, int(_os.environ.get("AG_DP_BUCKETS", buckets)))
         self._out = None
         self._labels = None
 
