@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "encode.cuh"
 #include "ladder.cuh"
+#include "ladder_warp.cuh"
 
 namespace ag {
 namespace enc {
@@ -339,56 +340,46 @@ __global__ void __launch_bounds__(WARPS * 32) encode_kernel(
 #undef CODE
 
 // Ladder planes, second half.  Input: the planes encode_kernel wrote, whose ladder planes hold 1 on every candidate
-// move.  Each warp claims chunks of positions from a global counter, lists the candidates of its chunk in shared
-// memory, and its lanes pull queries from that list one at a time (so a deep read-out on one move does not hold up
-// the other 31 lanes); each query's 0/1 answer overwrites the candidate mark in place.
-constexpr int kResolveWarps = 4;
-constexpr int kResolveChunk = 1;      // positions claimed at a time (measured: 1-2 best; the tail is a few deep read-outs)
-constexpr int kResolveList = 2 * MAXN * kResolveChunk;
+// move.  Each warp claims positions one at a time from a global counter, lists the position's candidates (ascending, by
+// ballot) in shared memory and reads them out one after the other with the whole warp (ladder_warp.cuh: the board's bit
+// sets are spread over the lanes, so the search has one control path); each 0/1 answer overwrites the candidate mark.
+constexpr int kResolveWarps = 8;
 
 __global__ void __launch_bounds__(kResolveWarps * 32)
 ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko,
                       int npos, int size, int n_planes, int cap_plane, int esc_plane, uint8_t* __restrict__ g_out,
                       unsigned int* __restrict__ counter) {
-    __shared__ uint32_t s_list[kResolveWarps][kResolveList];  // local position << 10 | kind << 9 | point
-    __shared__ uint32_t s_count[kResolveWarps], s_next[kResolveWarps];
-    __shared__ BoardMasks s_masks;
+    __shared__ LadderFrame s_frames[kResolveWarps][kLadderDepth + 2];
+    __shared__ uint16_t s_list[kResolveWarps][2 * MAXN];  // kind << 9 | point
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = size * size;
-    if (threadIdx.x == 0) board_masks_fill(s_masks, size);
-    __syncthreads();
-    LadderBoard B;
-    LadderFrame fr[kLadderDepth + 2];
-    int loaded = -1;  // position whose board is in B
+    WBoard B;
     while (true) {
-        unsigned int base = 0;
-        if (lane == 0) { base = atomicAdd(counter, (unsigned)kResolveChunk); s_count[warp] = 0; s_next[warp] = 0; }
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= (unsigned)npos) break;
-        __syncwarp();
-        const int cnt_pos = min(kResolveChunk, npos - (int)base);
-        for (int lp = 0; lp < cnt_pos; lp++) {
-            const uint8_t* planes = g_out + (size_t)(base + lp) * n_planes * n;
-            for (int kind = 0; kind < 2; kind++) {
-                const int pl = kind ? esc_plane : cap_plane;
-                if (pl < 0) continue;
-                for (int p = lane; p < n; p += 32)
-                    if (planes[(size_t)pl * n + p]) s_list[warp][atomicAdd(&s_count[warp], 1u)] = (uint32_t)(lp << 10 | kind << 9 | p);
+        unsigned int pos = 0;
+        if (lane == 0) pos = atomicAdd(counter, 1u);
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+        if (pos >= (unsigned)npos) break;
+        uint8_t* planes = g_out + (size_t)pos * n_planes * n;
+        int count = 0;
+        for (int kind = 0; kind < 2; kind++) {
+            const int pl = kind ? esc_plane : cap_plane;
+            if (pl < 0) continue;
+            for (int p0 = 0; p0 < n; p0 += 32) {
+                const int p = p0 + lane;
+                const bool mark = p < n && planes[(size_t)pl * n + p] != 0;
+                const unsigned bal = __ballot_sync(0xffffffffu, mark);
+                if (mark) s_list[warp][count + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)(kind << 9 | p);
+                count += __popc(bal);
             }
         }
         __syncwarp();
-        const unsigned total = s_count[warp];
-        while (true) {
-            unsigned i = atomicAdd(&s_next[warp], 1u);
-            if (i >= total) break;
-            const uint32_t c = s_list[warp][i];
-            const int pos = (int)base + (int)(c >> 10), kind = (c >> 9) & 1, a = c & 0x1FF;
-            if (loaded != pos) {
-                lb_load(B, g_board + (size_t)pos * n, size, g_player[pos], g_ko[pos], &s_masks);
-                loaded = pos;
-            }
-            const bool yes = ladder_query(B, fr, kind, a);
-            g_out[((size_t)pos * n_planes + (kind ? esc_plane : cap_plane)) * n + a] = yes ? 1 : 0;
+        if (count == 0) continue;
+        wl_load(B, g_board + (size_t)pos * n, size, g_player[pos], g_ko[pos], lane);
+        for (int i = 0; i < count; i++) {
+            const int c = s_list[warp][i];
+            const int kind = c >> 9, a = c & 0x1FF;
+            const bool yes = wl_query(B, s_frames[warp], kind, a);
+            if (lane == 0) planes[(size_t)(kind ? esc_plane : cap_plane) * n + a] = yes ? 1 : 0;
         }
         __syncwarp();
     }
@@ -436,8 +427,7 @@ int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player,
     unsigned int* ctr = counters + (next_counter++ & 15);
     AG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned int), stream));
     int rgrid = sm_count() * 8;
-    int need = (npos + enc::kResolveChunk - 1) / enc::kResolveChunk;
-    need = (need + enc::kResolveWarps - 1) / enc::kResolveWarps;
+    int need = (npos + enc::kResolveWarps - 1) / enc::kResolveWarps;
     if (rgrid > need) rgrid = need;
     enc::ladder_resolve_kernel<<<rgrid, enc::kResolveWarps * 32, 0, stream>>>(board, player, ko, npos, size, tab.n_planes, cap_plane, esc_plane, out, ctr);
     AG_LAUNCH_CHECK("ladder_resolve_kernel");
