@@ -65,6 +65,7 @@ struct WBoard {
     int size, player, ko, lane;
     uint32_t undo_cap[kLadderDepth + 2];   // per move on the path: this lane's word of the captured stones
     int16_t undo_pt[kLadderDepth + 2], undo_ko[kLadderDepth + 2];
+    uint32_t replies[kLadderDepth + 2];    // per frame: this lane's word of the current prey's reply set
     int undo_top;
 };
 
@@ -89,6 +90,22 @@ __device__ __forceinline__ uint32_t wl_group(const WBoard& B, int p, int colour)
     }
 }
 __device__ __forceinline__ uint32_t wl_liberties(const WBoard& B, uint32_t group) { return wl_dilate(B, group) & ~B.blk & ~B.wht; }
+// Grows the group of `colour` at p and counts its liberties, giving up as soon as more than `limit` of them are certain
+// (most groups a ladder search looks at are large and far from capture: one or two dilations settle the question).
+// Returns the liberty count when it is <= limit -- *group and *libs are then complete -- else limit + 1.
+__device__ __forceinline__ int wl_group_libs(const WBoard& B, int p, int colour, int limit, uint32_t* group, uint32_t* libs) {
+    const uint32_t own = colour > 0 ? B.blk : B.wht, stones = B.blk | B.wht;
+    uint32_t g = wb_point(p, B.lane);
+    while (true) {
+        const uint32_t d = wl_dilate(B, g);
+        const uint32_t l = d & ~stones;
+        const int c = wb_count(l);
+        const uint32_t n = g | (d & own);
+        if (c > limit) { *group = n; *libs = l; return limit + 1; }
+        if (!__any_sync(kFullWarp, n != g)) { *group = g; *libs = l; return c; }
+        g = n;
+    }
+}
 
 __device__ __forceinline__ bool wl_legal(const WBoard& B, int a) {  // go.py:181-216 for the side to move
     if (wl_colour(B, a) != 0 || a == B.ko) return false;
@@ -96,7 +113,8 @@ __device__ __forceinline__ bool wl_legal(const WBoard& B, int a) {  // go.py:181
     if (wb_any(nb & ~B.blk & ~B.wht)) return true;  // an empty neighbour
     for (int q = wb_next(nb, -1, B.lane); q >= 0; q = wb_next(nb, q, B.lane)) {  // every neighbour holds a stone
         const int c = wl_colour(B, q);
-        const bool other = wb_count(wl_liberties(B, wl_group(B, q, c))) > 1;  // a itself is one of its liberties
+        uint32_t g, l;
+        const bool other = wl_group_libs(B, q, c, 1, &g, &l) > 1;  // a itself is one of its liberties
         if (c == B.player && other) return true;
         if (c == -B.player && !other) return true;
     }
@@ -116,13 +134,13 @@ __device__ __forceinline__ void wl_play(WBoard& B, int a) {
     for (int j = 0; j < 4; j++) {
         const int q = cand[j];
         if (q < 0 || wl_colour(B, q) != -color) continue;
-        const uint32_t g = wl_group(B, q, -color);
-        if (wb_any(wl_liberties(B, g))) continue;
+        uint32_t g, l;
+        if (wl_group_libs(B, q, -color, 0, &g, &l) > 0) continue;
         if (color > 0) B.wht &= ~g; else B.blk &= ~g;
         captured |= g;
         if (wb_count(g) == 1) {  // go.py:323-331, evaluated inside the loop
-            const uint32_t me = wl_group(B, a, color);
-            if (wb_count(me) == 1 && wb_count(wl_liberties(B, me)) == 1) B.ko = q;
+            uint32_t me, ml;
+            if (wl_group_libs(B, a, color, 1, &me, &ml) == 1 && wb_count(me) == 1) B.ko = q;
         }
     }
     B.undo_cap[B.undo_top] = captured;
@@ -171,9 +189,10 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
                     for (int j = 0; j < 4; j++) {  // each adjacent group once, named by the first neighbour that touches it
                         const int q = cand[j];
                         if (q < 0 || wl_colour(B, q) != want_col || wb_get(seen, q)) continue;
-                        const uint32_t g = wl_group(B, q, want_col);
-                        seen |= g;
-                        if (wb_count(wl_liberties(B, g)) == want_libs) f.preys[nprey++] = (uint16_t)q;
+                        uint32_t g, l;
+                        const int libs = wl_group_libs(B, q, want_col, want_libs, &g, &l);
+                        if (libs <= want_libs) seen |= g;  // complete group (a group given up on early is no prey from any side)
+                        if (libs == want_libs) f.preys[nprey++] = (uint16_t)q;
                     }
                 }
                 f.nprey = (uint8_t)nprey; f.iprey = 0;
@@ -187,7 +206,8 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
                 bool go_on = true;
                 if (fkind == 1) {
                     const int pr = f.preys[f.iprey];
-                    const int libs = wb_count(wl_liberties(B, wl_group(B, pr, wl_colour(B, pr))));
+                    uint32_t g, l;
+                    const int libs = wl_group_libs(B, pr, wl_colour(B, pr), 2, &g, &l);
                     if (libs >= 3) { wl_undo(B); done = true; value = true; go_on = false; }
                     else if (libs <= 1) { wl_undo(B); f.iprey++; go_on = false; }
                 }
@@ -196,18 +216,24 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
         } else if (phase == LP_NEXT_CHILD) {
             const int pr = f.preys[f.iprey];
             const int after = f.last == kNoPoint ? -1 : (int)f.last;
-            const int prey_col = wl_colour(B, pr);
-            const uint32_t prey = wl_group(B, pr, prey_col);
-            uint32_t replies = wl_liberties(B, prey);
-            if (fkind == 0) {
-                // + the single liberty of every hunter group that touches the prey and is in atari
-                uint32_t touching = wl_dilate(B, prey) & (prey_col > 0 ? B.wht : B.blk);
-                for (int s = wb_next(touching, -1, B.lane); s >= 0; s = wb_next(touching, -1, B.lane)) {
-                    const uint32_t h = wl_group(B, s, -prey_col);
-                    touching &= ~h;
-                    const uint32_t hl = wl_liberties(B, h);
-                    if (wb_count(hl) == 1) replies |= hl;
+            uint32_t replies;
+            if (f.last == kNoPoint) {  // first child of this prey: work the reply set out once, keep it for the siblings
+                const int prey_col = wl_colour(B, pr);
+                uint32_t prey;
+                wl_group_libs(B, pr, prey_col, 0x7fff, &prey, &replies);
+                if (fkind == 0) {
+                    // + the single liberty of every hunter group that touches the prey and is in atari
+                    uint32_t touching = wl_dilate(B, prey) & (prey_col > 0 ? B.wht : B.blk);
+                    for (int s = wb_next(touching, -1, B.lane); s >= 0; s = wb_next(touching, -1, B.lane)) {
+                        uint32_t h, hl;
+                        const int nl = wl_group_libs(B, s, -prey_col, 1, &h, &hl);  // h is partial when given up early: it still holds s
+                        touching &= ~h;
+                        if (nl == 1) replies |= hl;
+                    }
                 }
+                B.replies[sp - 1] = replies;
+            } else {
+                replies = B.replies[sp - 1];
             }
             const int e = wb_next(replies, after, B.lane);
             if (e < 0) {  // no reply left: the capture holds / nothing catches the escaper
