@@ -102,10 +102,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     const int xchunks = p.kin / 64;
     const int cochunks = p.ldout / 64;
     const int chunk_bytes = p.krows * 128;          // one TMA box: [krows pixel rows][64 bf16]
-    const int a_region = kASlots * chunk_bytes;     // bytes of a stage set aside for G
+    const bool windowed = p.win_rows > 0;
+    // bytes of a stage set aside for G: four slots' boxes, or the (at most two) shared windows
+    const int a_region = windowed ? 2 * ((p.win_rows * 128 + 1023) & ~1023) : kASlots * chunk_bytes;
     const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const bool taps_in_n = p.tpg > 1;
-    const bool windowed = p.win_rows > 0;
     const int coquads = (cochunks + kASlots - 1) / kASlots;
     const int grp = taps_in_n ? tile / coquads : 0;
     // this CTA's slots are a_first .. a_first+3 of a_count: (co chunk, tap) pairs co-major, or co chunks alone (taps in N)
@@ -348,9 +349,9 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
     const int xchunks = p.kin / 64;
     const int cochunks = p.ldout / 64;
     const int chunk_bytes = p.krows * 128;
-    const int a_region = kASlots * chunk_bytes;
-    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const bool windowed = p.win_rows > 0;
+    const int a_region = windowed ? 2 * ((p.win_rows * 128 + 1023) & ~1023) : kASlots * chunk_bytes;
+    const int tile = blockIdx.x % p.tiles, split = blockIdx.x / p.tiles;
     const int a_first = tile * kASlots;
     const int a_count = p.taps * cochunks;
     const int a_live = min(kASlots, a_count - a_first);
@@ -574,20 +575,21 @@ static int wgrad_krows() {
     return v;
 }
 
-static int wgrad_stage_bytes(int taps, int kin, bool with_bias, int krows) {
+static int wgrad_stage_bytes(int taps, int kin, bool with_bias, int krows, int win_rows) {
     int tpg, groups;
     wgrad_tiling(taps, 64, kin, &tpg, &groups);
-    return (kASlots + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0))) * krows * 128;
+    const int a_region = win_rows > 0 ? 2 * ((win_rows * 128 + 1023) & ~1023) : kASlots * krows * 128;  // as in the kernels
+    return a_region + (tpg > 1 ? tpg * (kin / 64) : kin / 64 + (with_bias ? 1 : 0)) * krows * 128;
 }
 
-static int wgrad_stages(int taps, int kin, bool with_bias, int krows) {
-    int s = (227 * 1024 - 1024 - (int)sizeof(WgradBarriers) - (int)sizeof(WgradPlan) - 64) / wgrad_stage_bytes(taps, kin, with_bias, krows);
+static int wgrad_stages(int taps, int kin, bool with_bias, int krows, int win_rows) {
+    int s = (227 * 1024 - 1024 - (int)sizeof(WgradBarriers) - (int)sizeof(WgradPlan) - 64) / wgrad_stage_bytes(taps, kin, with_bias, krows, win_rows);
     return s > kMaxStages ? kMaxStages : s;
 }
 
-static size_t wgrad_smem_bytes(int taps, int kin, bool with_bias, int krows) {
-    return 1024 + (size_t)wgrad_stages(taps, kin, with_bias, krows) * wgrad_stage_bytes(taps, kin, with_bias, krows) + sizeof(WgradBarriers) +
-           sizeof(WgradPlan) + 64;
+static size_t wgrad_smem_bytes(int taps, int kin, bool with_bias, int krows, int win_rows) {
+    return 1024 + (size_t)wgrad_stages(taps, kin, with_bias, krows, win_rows) * wgrad_stage_bytes(taps, kin, with_bias, krows, win_rows) +
+           sizeof(WgradBarriers) + sizeof(WgradPlan) + 64;
 }
 
 // Rows of the G box shared by the taps of one co chunk (0 = every slot fetches its own krows rows): krows + the largest
@@ -646,14 +648,14 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
     if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
     args.krows = maps.krows;
-    size_t smem = wgrad_smem_bytes(args.taps, args.kin, args.bias_scratch != nullptr, args.krows);
+    size_t smem = wgrad_smem_bytes(args.taps, args.kin, args.bias_scratch != nullptr, args.krows, maps.win_rows);
     if (smem > 227 * 1024) { set_error("wgrad: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AG_WGRAD_DEBUG"); dbg = e ? atoi(e) : 0; } args.debug = dbg; }
-    const int stages = wgrad_stages(args.taps, args.kin, args.bias_scratch != nullptr, args.krows);
+    const int stages = wgrad_stages(args.taps, args.kin, args.bias_scratch != nullptr, args.krows, maps.win_rows);
     if (stages < 2) { set_error("wgrad: shared memory fits only %d stage(s)", stages); return AG_EINVAL; }
     args.win_rows = maps.win_rows;
     launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, maps.g, maps.gw, maps.x, args, stages);
@@ -679,7 +681,7 @@ bool wgrad_chain_ok(const WgradArgs& a_in, const WgradMaps& maps, bool with_bias
     const int kb_total = (a.m_total + maps.krows - 1) / maps.krows;
     if (a.splits < 1 || kb_total < a.splits) return false;
     // every CTA must be resident at once (they wait for each other's partials): one CTA per SM with this much shared memory
-    return a.tiles * a.splits <= sm_count() && wgrad_stages(a.taps, a.kin, with_bias, maps.krows) >= 2;
+    return a.tiles * a.splits <= sm_count() && wgrad_stages(a.taps, a.kin, with_bias, maps.krows, maps.win_rows) >= 2;
 }
 
 int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_layers, cudaStream_t stream) {
@@ -703,8 +705,8 @@ int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_lay
         }
     }
     P.a = args; P.n_layers = n_layers;
-    const int stages = wgrad_stages(args.taps, args.kin, with_bias, args.krows);
-    size_t smem = wgrad_smem_bytes(args.taps, args.kin, with_bias, args.krows);
+    const int stages = wgrad_stages(args.taps, args.kin, with_bias, args.krows, args.win_rows);
+    size_t smem = wgrad_smem_bytes(args.taps, args.kin, with_bias, args.krows, args.win_rows);
     if (smem < 120 * 1024) smem = 120 * 1024;  // one CTA per SM (see wgrad_chain_ok)
     static size_t configured = 0;
     if (smem > configured) {
