@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/alphago_b200.h"  // AG_OK / AG_E* codes
 
@@ -43,15 +44,27 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 template <typename... P, typename... A>
-inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
+inline cudaError_t launch_k_opt(bool early, void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = (early && pdl_enabled()) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, P(args)...);
+}
+template <typename... P, typename... A>
+inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
+    return launch_k_opt(true, kernel, grid, block, smem, stream, args...);
+}
+// for kernels whose CTAs wait for each other (the layer chains): launched only once everything before them in the stream has
+// finished and left the SMs, so the whole grid becomes resident at once
+template <typename... P, typename... A>
+inline cudaError_t launch_k_whole(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
+    static int early = -1;
+    if (early < 0) { const char* e = getenv("AG_CHAIN_PDL"); early = (e && e[0] == '1') ? 1 : 0; }
+    return launch_k_opt(early == 1, kernel, grid, block, smem, stream, args...);
 }
 #endif
 

@@ -532,7 +532,6 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
     const int n_clusters = gridDim.x / 2, cluster_id = blockIdx.x / 2;
     const int total_tiles = P.total_tiles;
 
-    pdl_trigger();
     if (threadIdx.x == 0) {
         for (int s = 0; s < kWinSlots; s++) { tc::mbar_init(&bars->a_full[s], 1); tc::mbar_init(&bars->a_empty[s], 1); }
         for (int s = 0; s < kBStages; s++) { tc::mbar_init(&bars->b_full[s], 1); tc::mbar_init(&bars->b_empty[s], 1); }
@@ -671,6 +670,10 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
             }
         }
     }
+    // Only now may the kernels behind this one start: a dependent that launched while some of OUR pairs were still waiting for
+    // an SM would fill the SMs with CTAs that wait for us, and the tiles those pairs own would never be computed (seen as
+    // a dependency timeout with the trigger at the top of the kernel).
+    pdl_trigger();
     tc::fence_before_sync();
     __syncthreads();
     tc::cluster_sync_all();  // the peer's smem and barriers stay alive until the leader's last UMMA / arrival is done
@@ -851,7 +854,7 @@ int conv_chain_launch(const ChainParams& P, unsigned int* d_flags, unsigned int 
     if (clusters > max_clusters) clusters = max_clusters;
     if (clusters > P.total_tiles) clusters = P.total_tiles;
     if (clusters < 1) { set_error("conv chain: no CTA pair fits on this device"); return AG_ECUDA; }
-    launch_k(conv_chain_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, P, d_flags, epoch, win_bytes, b_bytes, bstages);
+    launch_k_whole(conv_chain_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, P, d_flags, epoch, win_bytes, b_bytes, bstages);
     AG_LAUNCH_CHECK("conv_chain_kernel");
     return AG_OK;
 }

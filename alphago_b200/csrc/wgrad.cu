@@ -368,7 +368,6 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
     const int kb_total = (p.m_total + p.krows - 1) / p.krows;
     const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
 
-    pdl_trigger();
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; s++) { tc::mbar_init(&bars->full[s], 1); tc::mbar_init(&bars->empty[s], 1); }
         tc::mbar_init(&bars->acc_full, 1);
@@ -543,6 +542,7 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
             }
         }
     }
+    pdl_trigger();  // not earlier: every CTA of this grid must be resident before anything queued behind it may take SMs
     tc::fence_before_sync();
     __syncthreads();
     if (warp == 1) {
@@ -713,7 +713,7 @@ int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_lay
         AG_CUDA(cudaFuncSetAttribute(wgrad_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    launch_k(wgrad_chain_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, P, stages);
+    launch_k_whole(wgrad_chain_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, P, stages);
     AG_LAUNCH_CHECK("wgrad_chain_kernel");
     return AG_OK;
 }

@@ -291,3 +291,20 @@ def test_forward_and_backward_are_bitwise_repeatable():
             assert np.array_equal(first[0], probs), "forward differs at repetition %d" % it
             assert np.array_equal(first[1], grads), "gradients differ at repetition %d" % it
     net.close()
+
+
+def test_chained_forward_survives_back_to_back_launches():
+    """Regression: the chained launch needs all its CTA pairs resident at once, so it must not start early behind the
+    small kernels queued in front of it (seen as a dependency timeout after a few hundred unsynchronised forwards at
+    batch 128).  800 forwards without a host sync in between, outputs identical throughout."""
+    import torch
+    net = nn.ConvNet(19, 49, [192] * 12, [5] + [3] * 11, head=nn.VALUE_HEAD, max_batch=128)
+    net.init_uniform(1)
+    x = torch.from_numpy((np.random.RandomState(128).rand(128, 49, 19, 19) < 0.3).astype(np.uint8)).cuda()
+    first = net.forward(x).clone()
+    for i in range(800):
+        out = net.forward(x)
+        if i % 200 == 199:
+            assert torch.equal(out, first)
+    torch.cuda.synchronize()
+    net.close()
