@@ -348,17 +348,21 @@ constexpr int kResolveWarps = 8;
 __global__ void __launch_bounds__(kResolveWarps * 32)
 ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko,
                       int npos, int size, int n_planes, int cap_plane, int esc_plane, uint8_t* __restrict__ g_out,
-                      unsigned int* __restrict__ counter) {
+                      unsigned int* __restrict__ counter, int slices) {
     __shared__ LadderFrame s_frames[kResolveWarps][kLadderDepth + 2];
     __shared__ uint16_t s_list[kResolveWarps][2 * MAXN];  // kind << 9 | point
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = size * size;
     WBoard B;
     while (true) {
-        unsigned int pos = 0;
-        if (lane == 0) pos = atomicAdd(counter, 1u);
-        pos = __shfl_sync(0xffffffffu, pos, 0);
-        if (pos >= (unsigned)npos) break;
+        // work unit = (position, slice): a small batch is cut into `slices` shares of each position's candidates (by point),
+        // so that one position with many deep read-outs does not become the whole launch's critical path
+        unsigned int unit = 0;
+        if (lane == 0) unit = atomicAdd(counter, 1u);
+        unit = __shfl_sync(0xffffffffu, unit, 0);
+        if (unit >= (unsigned)npos * (unsigned)slices) break;
+        const unsigned int pos = unit / (unsigned)slices;
+        const int slice = (int)(unit - pos * (unsigned)slices);
         uint8_t* planes = g_out + (size_t)pos * n_planes * n;
         int count = 0;
         for (int kind = 0; kind < 2; kind++) {
@@ -366,7 +370,9 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restri
             if (pl < 0) continue;
             for (int p0 = 0; p0 < n; p0 += 32) {
                 const int p = p0 + lane;
-                const bool mark = p < n && planes[(size_t)pl * n + p] != 0;
+                // a share = the candidates at points p with p % slices == slice: other warps are overwriting the marks of their
+                // own shares with answers at the same time, so membership must not depend on the other marks
+                const bool mark = p < n && (p % slices) == slice && planes[(size_t)pl * n + p] != 0;
                 const unsigned bal = __ballot_sync(0xffffffffu, mark);
                 if (mark) s_list[warp][count + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)(kind << 9 | p);
                 count += __popc(bal);
@@ -426,10 +432,13 @@ int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player,
     if (!counters) AG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_ladder_counters));
     unsigned int* ctr = counters + (next_counter++ & 15);
     AG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned int), stream));
+    int slices = 16384 / (npos > 0 ? npos : 1);   // enough work units to fill the machine even for a handful of positions
+    slices = slices < 1 ? 1 : (slices > 16 ? 16 : slices);
     int rgrid = sm_count() * 8;
-    int need = (npos + enc::kResolveWarps - 1) / enc::kResolveWarps;
+    int need = (npos * slices + enc::kResolveWarps - 1) / enc::kResolveWarps;
     if (rgrid > need) rgrid = need;
-    enc::ladder_resolve_kernel<<<rgrid, enc::kResolveWarps * 32, 0, stream>>>(board, player, ko, npos, size, tab.n_planes, cap_plane, esc_plane, out, ctr);
+    enc::ladder_resolve_kernel<<<rgrid, enc::kResolveWarps * 32, 0, stream>>>(board, player, ko, npos, size, tab.n_planes, cap_plane, esc_plane, out, ctr,
+                                                                              slices);
     AG_LAUNCH_CHECK("ladder_resolve_kernel");
     for (int j = 0; j < tab.n_planes; j++) {  // repeated ladder features
         int src = tab.arr[j] == enc::C_LADCAP ? cap_plane : (tab.arr[j] == enc::C_LADESC ? esc_plane : -1);
