@@ -1,0 +1,204 @@
+"""SGF files -> training dataset, drop-in for AlphaGo/preprocessing/game_converter.py:12-218 (the step
+before the hot path).
+
+Same class, methods, command line and file contract: `states` uint8 (N, F, size, size), `actions` uint8 (N, 2) as (x, y),
+group `file_offsets[name.replace('/', ':')] = [start, count]` (game_converter.py:71-88,122-125); passes are skipped, an
+illegal move drops the rest of that game, an unparsable or wrong-size file is skipped with a warning.  What changes is
+where the planes come from: positions are replayed on the host rules engine and PACKED (board, stone ages, player, ko:
+726 bytes each); the planes of thousands of positions at a time are then produced by one launch of the CUDA encoder
+instead of one Python feature pass per position.
+"""
+import os
+import warnings
+
+import numpy as np
+
+from . import go
+from .preprocessing import Preprocess, pack_state
+from .util import ParseException, sgf_iter_states
+
+
+class SizeMismatchError(Exception):
+    pass
+
+
+class game_converter(object):   # the reference's own (lower-case) class name, game_converter.py:16
+
+    def __init__(self, features, batch=4096):
+        self.feature_processor = Preprocess(features)
+        self.n_features = self.feature_processor.output_dim
+        self.batch = int(batch)   # positions per encoder launch in the bulk path
+
+    # ------------------------------------------------------------------ reference-shaped generator
+    def convert_game(self, file_name, bd_size):
+        """Read the given SGF file into an iterable of (input, output) pairs: input = (1, F, size, size) one-hot planes of
+        the position, output = the move played there as (x, y); passes are skipped; SizeMismatchError if the game is not
+        played on bd_size (game_converter.py:22-40)"""
+        with open(file_name, "r") as file_object:
+            state_action_iterator = sgf_iter_states(file_object.read())
+        for (state, move, player) in state_action_iterator:
+            if state.size != bd_size:
+                raise SizeMismatchError()
+            if move != go.PASS_MOVE:
+                yield (self.feature_processor.state_to_tensor(state), move)
+
+    # ------------------------------------------------------------------ bulk path
+    def pack_game(self, file_name, bd_size):
+        """The same positions as convert_game, packed for the encoder instead of encoded: returns (packed, actions, error)
+        with packed = list of (board int8[n], age uint8[n], player, ko), actions = list of (x, y), error = the exception
+        that ended the game early (None if it ran to its end).  Pairs produced before an error are kept, as the
+        reference keeps what it had written (game_converter.py:103-123)."""
+        packed, actions, error = [], [], None
+        try:
+            with open(file_name, "r") as file_object:
+                text = file_object.read()
+            for (state, move, player) in sgf_iter_states(text):
+                if state.size != bd_size:
+                    raise SizeMismatchError()
+                if move != go.PASS_MOVE:
+                    b, a, pl, ko = pack_state(state)
+                    packed.append((b.copy(), a.copy(), pl, ko))
+                    actions.append(move)
+        except Exception as e:   # classified by the caller
+            error = e
+        return packed, actions, error
+
+    def encode_packed_positions(self, packed, bd_size):
+        """list of packed positions -> uint8 planes (N, F, size, size) on the host, `self.batch` positions per launch"""
+        n = len(packed)
+        out = np.empty((n, self.n_features, bd_size, bd_size), np.uint8)
+        for s in range(0, n, self.batch):
+            chunk = packed[s:s + self.batch]
+            board = np.stack([p[0] for p in chunk])
+            age = np.stack([p[1] for p in chunk])
+            player = np.asarray([p[2] for p in chunk], np.int8)
+            ko = np.asarray([p[3] for p in chunk], np.int16)
+            out[s:s + len(chunk)] = self.feature_processor.encode_host(board, age, player, ko, bd_size)
+        return out
+
+    def sgfs_to_hdf5(self, sgf_files, hdf5_file, bd_size=19, ignore_errors=True, verbose=False):
+        """Convert all files in the iterable sgf_files into one dataset file (game_converter.py:42-140).
+
+        The resulting file has `states` (n_data, n_features, size, size), `actions` (n_data, 2) and the group
+        `file_offsets` mapping file names ('/' -> ':') to [index, length]; it is written under a hidden temporary name
+        and renamed on success.  With h5py installed it is the reference's HDF5 (LZF-compressed chunks of 64 / 1024
+        rows); without it the same three members are written as an .npz archive under the given name (what
+        supervised_policy_trainer.open_dataset and hdf5_lite.open_file read back)."""
+        tmp_file = os.path.join(os.path.dirname(hdf5_file), ".tmp." + os.path.basename(hdf5_file))
+        names, offsets = [], []
+        pending, all_actions, blocks = [], [], []
+        next_idx = 0
+        try:
+            for file_name in sgf_files:
+                if verbose:
+                    print(file_name)
+                packed, actions, error = self.pack_game(file_name, bd_size)
+                if error is not None:
+                    if isinstance(error, go.IllegalMove):
+                        warnings.warn("Illegal Move encountered in %s\n\tdropping the remainder of the game" % file_name)
+                    elif isinstance(error, ParseException):
+                        warnings.warn("Could not parse %s\n\tdropping game" % file_name)
+                    elif isinstance(error, SizeMismatchError):
+                        warnings.warn("Skipping %s; wrong board size" % file_name)
+                    elif ignore_errors:
+                        warnings.warn("Unkown exception with file %s\n\t%s" % (file_name, error))
+                    else:
+                        raise error
+                n_pairs = len(packed)
+                if n_pairs > 0:
+                    names.append(file_name.replace("/", ":"))   # '/' has special meaning in HDF5 key names
+                    offsets.append([next_idx, n_pairs])
+                    pending.extend(packed)
+                    all_actions.extend(actions)
+                    next_idx += n_pairs
+                    if verbose:
+                        print("\t%d state/action pairs extracted" % n_pairs)
+                elif verbose:
+                    print("\t-no usable data-")
+                if len(pending) >= self.batch:
+                    blocks.append(self.encode_packed_positions(pending, bd_size))
+                    pending = []
+            if pending:
+                blocks.append(self.encode_packed_positions(pending, bd_size))
+            states = np.concatenate(blocks) if blocks else np.zeros((0, self.n_features, bd_size, bd_size), np.uint8)
+            acts = np.asarray(all_actions, np.uint8).reshape(-1, 2)
+            _write_dataset(tmp_file, states, acts, names, np.asarray(offsets, np.int64).reshape(-1, 2))
+        except Exception:
+            print("sgfs_to_hdf5 failed")
+            if os.path.exists(tmp_file):
+                os.remove(tmp_file)
+            raise
+        if verbose:
+            print("finished. renaming %s to %s" % (tmp_file, hdf5_file))
+        os.rename(tmp_file, hdf5_file)
+
+
+def _write_dataset(path, states, actions, names, offsets):
+    try:
+        import h5py
+    except ImportError:
+        h5py = None
+    if h5py is not None:
+        n_feat, size = states.shape[1], states.shape[2]
+        with h5py.File(path, "w") as f:
+            f.create_dataset("states", data=states, dtype=np.uint8, maxshape=(None, n_feat, size, size),
+                             chunks=(64, n_feat, size, size), compression="lzf")
+            f.create_dataset("actions", data=actions, dtype=np.uint8, maxshape=(None, 2), chunks=(1024, 2), compression="lzf")
+            g = f.require_group("file_offsets")
+            for name, off in zip(names, offsets):
+                g[name] = [int(off[0]), int(off[1])]
+        return
+    with open(path, "wb") as f:   # np.savez would append ".npz" to a bare name
+        np.savez_compressed(f, states=states, actions=actions, file_offsets_names=np.asarray(names), file_offsets=offsets)
+
+
+def run_game_converter(cmd_line_args=None):
+    """Run conversions. command-line args may be passed in as a list (game_converter.py:143-214)"""
+    import argparse
+    import sys
+
+    parser = argparse.ArgumentParser(
+        description="Prepare SGF Go game files for training the neural network model.",
+        epilog="Available features are: board, ones, turns_since, liberties, capture_size, self_atari_size, "
+               "liberties_after, ladder_capture, ladder_escape, sensibleness, and zeros.")
+    parser.add_argument("--features", "-f", help="Comma-separated list of features to compute and store or 'all'", default="all")
+    parser.add_argument("--outfile", "-o", help="Destination to write data (hdf5 file)", required=True)
+    parser.add_argument("--recurse", "-R", help="Set to recurse through directories searching for SGF files", default=False, action="store_true")
+    parser.add_argument("--directory", "-d", help="Directory containing SGF files to process. if not present, expects files from stdin", default=None)
+    parser.add_argument("--size", "-s", help="Size of the game board. SGFs not matching this are discarded with a warning", type=int, default=19)
+    parser.add_argument("--verbose", "-v", help="Turn on verbose mode", default=False, action="store_true")
+    args = parser.parse_args(cmd_line_args)
+
+    if args.features.lower() == "all":
+        # the reference's 'all' leaves the two ladder features out because it cannot compute them
+        # (game_converter.py:166-177); the list is kept so that files stay interchangeable -- ask for them by name
+        feature_list = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size", "liberties_after",
+                        "sensibleness", "zeros"]
+    else:
+        feature_list = args.features.split(",")
+    if args.verbose:
+        print("using features", feature_list)
+
+    converter = game_converter(feature_list)
+
+    def _is_sgf(fname):
+        return fname.strip()[-4:] == ".sgf"
+
+    def _walk_all_sgfs(root):
+        for (dirpath, dirname, files) in os.walk(root):
+            for filename in files:
+                if _is_sgf(filename):
+                    yield os.path.join(dirpath, filename)
+
+    def _list_sgfs(path):
+        return (os.path.join(path, f) for f in os.listdir(path) if _is_sgf(f))
+
+    if args.directory:
+        files = _walk_all_sgfs(args.directory) if args.recurse else _list_sgfs(args.directory)
+    else:
+        files = (f.strip() for f in sys.stdin if _is_sgf(f))
+    converter.sgfs_to_hdf5(files, args.outfile, bd_size=args.size, verbose=args.verbose)
+
+
+if __name__ == "__main__":
+    run_game_converter()

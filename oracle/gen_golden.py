@@ -188,9 +188,26 @@ def export_reference_hdf5_fixture():
     print("ref_hdf5_fixture.npz written", offsets.tolist())
 
 
+def export_reference_sgf_fixtures():
+    """Game records the reference keeps for its own converter tests (tests/test_data/sgf: the five AlphaGo - Lee Sedol
+    games behind alphago-vs-lee-sedol-features.hdf5, and ab_aw.sgf with set-up stones) copied to tests/golden/sgf as
+    test INPUT data for alphago_b200/game_converter.py.  Run: python oracle/gen_golden.py sgf"""
+    import shutil
+    src = os.path.join(ref_shim.REFERENCE_ROOT, "tests", "test_data", "sgf")
+    dst = os.path.join(OUT, "sgf")
+    os.makedirs(dst, exist_ok=True)
+    for name in sorted(os.listdir(src)):
+        if name.endswith(".sgf") and (name == "ab_aw.sgf" or "Sedol" in name):
+            shutil.copyfile(os.path.join(src, name), os.path.join(dst, name))
+            print("copied", name)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "hdf5":
         export_reference_hdf5_fixture()
+    elif len(sys.argv) > 1 and sys.argv[1] == "sgf":
+        export_reference_sgf_fixtures()
     else:
         main()
         export_reference_hdf5_fixture()
+
