@@ -17,10 +17,12 @@ namespace enc {
 
 constexpr unsigned kFullWarp = 0xffffffffu;
 
-struct WMasks { uint32_t all, col_first, col_last; };  // this lane's word of: board points, column y = 0, column y = size-1
+// this lane's word of: board points, column y = 0, column y = size-1; and the next lane's column-0 word / the previous lane's
+// last-column word (so that one pair of shuffles serves all four shifts of a dilation)
+struct WMasks { uint32_t all, col_first, col_last, col_first_next, col_last_prev; };
 
 __device__ __forceinline__ WMasks wmasks_make(int size, int lane) {
-    WMasks m = {0u, 0u, 0u};
+    WMasks m = {0u, 0u, 0u, 0u, 0u};
     for (int b = 0; b < 32; b++) {
         const int p = lane * 32 + b;
         if (p < size * size) {
@@ -30,6 +32,10 @@ __device__ __forceinline__ WMasks wmasks_make(int size, int lane) {
             if (y == size - 1) m.col_last |= 1u << b;
         }
     }
+    m.col_first_next = __shfl_down_sync(0xffffffffu, m.col_first, 1);
+    m.col_last_prev = __shfl_up_sync(0xffffffffu, m.col_last, 1);
+    if (lane == 31) m.col_first_next = 0;
+    if (lane == 0) m.col_last_prev = 0;
     return m;
 }
 
@@ -70,9 +76,13 @@ struct WBoard {
 };
 
 __device__ __forceinline__ uint32_t wl_dilate(const WBoard& B, uint32_t g) {
-    const uint32_t up = wb_shr(g, B.size, B.lane), down = wb_shl(g, B.size, B.lane);   // x -+ 1
-    const uint32_t left = wb_shr(g & ~B.m.col_first, 1, B.lane);                        // y - 1 (not from column 0)
-    const uint32_t right = wb_shl(g & ~B.m.col_last, 1, B.lane);                        // y + 1 (not from the last column)
+    uint32_t prev = __shfl_up_sync(kFullWarp, g, 1), next = __shfl_down_sync(kFullWarp, g, 1);
+    if (B.lane == 0) prev = 0;
+    if (B.lane == 31) next = 0;
+    const uint32_t up = (g >> B.size) | (next << (32 - B.size));                                           // x - 1
+    const uint32_t down = (g << B.size) | (prev >> (32 - B.size));                                         // x + 1
+    const uint32_t left = ((g & ~B.m.col_first) >> 1) | ((next & ~B.m.col_first_next) << 31);              // y - 1 (not from column 0)
+    const uint32_t right = ((g & ~B.m.col_last) << 1) | ((prev & ~B.m.col_last_prev) >> 31);               // y + 1 (not from the last column)
     return (up | down | left | right) & B.m.all;
 }
 __device__ __forceinline__ int wl_colour(const WBoard& B, int p) {
