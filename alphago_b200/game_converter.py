@@ -63,17 +63,30 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
             error = e
         return packed, actions, error
 
-    def encode_packed_positions(self, packed, bd_size):
-        """list of packed positions -> uint8 planes (N, F, size, size) on the host, `self.batch` positions per launch"""
+    def encode_packed_positions(self, packed, bd_size, bits=False):
+        """list of packed positions -> uint8 planes (N, F, size, size) on the host, `self.batch` positions per launch.
+        bits=True: each position's planes come back bit-packed (np.packbits order, (N, ceil(F*size*size/8))): an eighth
+        of the device->host traffic and of what the archive writer has to compress."""
+        import torch
         n = len(packed)
-        out = np.empty((n, self.n_features, bd_size, bd_size), np.uint8)
+        row = self.n_features * bd_size * bd_size
+        out = np.empty((n, (row + 7) // 8), np.uint8) if bits else np.empty((n, self.n_features, bd_size, bd_size), np.uint8)
         for s in range(0, n, self.batch):
             chunk = packed[s:s + self.batch]
-            board = np.stack([p[0] for p in chunk])
-            age = np.stack([p[1] for p in chunk])
-            player = np.asarray([p[2] for p in chunk], np.int8)
-            ko = np.asarray([p[3] for p in chunk], np.int16)
-            out[s:s + len(chunk)] = self.feature_processor.encode_host(board, age, player, ko, bd_size)
+            m = len(chunk)
+            board = torch.from_numpy(np.stack([p[0] for p in chunk])).cuda(non_blocking=True)
+            age = torch.from_numpy(np.stack([p[1] for p in chunk])).cuda(non_blocking=True)
+            player = torch.from_numpy(np.asarray([p[2] for p in chunk], np.int8)).cuda(non_blocking=True)
+            ko = torch.from_numpy(np.asarray([p[3] for p in chunk], np.int16)).cuda(non_blocking=True)
+            planes = self.feature_processor.encode_packed(board, age, player, ko, bd_size)
+            if bits:
+                flat = planes.reshape(m, row)
+                if row % 8:
+                    flat = torch.nn.functional.pad(flat, (0, 8 - row % 8))
+                w = torch.tensor([128, 64, 32, 16, 8, 4, 2, 1], dtype=torch.int32, device=flat.device)
+                out[s:s + m] = (flat.reshape(m, -1, 8).to(torch.int32) * w).sum(-1).to(torch.uint8).cpu().numpy()
+            else:
+                out[s:s + m] = planes.cpu().numpy()
         return out
 
     def sgfs_to_hdf5(self, sgf_files, hdf5_file, bd_size=19, ignore_errors=True, verbose=False):
@@ -82,11 +95,12 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
         The resulting file has `states` (n_data, n_features, size, size), `actions` (n_data, 2) and the group
         `file_offsets` mapping file names ('/' -> ':') to [index, length]; it is written under a hidden temporary name
         and renamed on success.  With h5py installed it is the reference's HDF5 (LZF-compressed chunks of 64 / 1024
-        rows); without it the same three members are written as an .npz archive under the given name (what
-        supervised_policy_trainer.open_dataset and hdf5_lite.open_file read back)."""
+        rows); without it the same three members are written as an .npz archive under the given name, the planes
+        bit-packed (supervised_policy_trainer.open_dataset reads either)."""
         tmp_file = os.path.join(os.path.dirname(hdf5_file), ".tmp." + os.path.basename(hdf5_file))
         names, offsets = [], []
         pending, all_actions, blocks = [], [], []
+        bits = not _have_h5py()   # the archive fallback stores the one-hot planes bit-packed
         next_idx = 0
         try:
             for file_name in sgf_files:
@@ -116,13 +130,17 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
                 elif verbose:
                     print("\t-no usable data-")
                 if len(pending) >= self.batch:
-                    blocks.append(self.encode_packed_positions(pending, bd_size))
+                    blocks.append(self.encode_packed_positions(pending, bd_size, bits=bits))
                     pending = []
             if pending:
-                blocks.append(self.encode_packed_positions(pending, bd_size))
-            states = np.concatenate(blocks) if blocks else np.zeros((0, self.n_features, bd_size, bd_size), np.uint8)
+                blocks.append(self.encode_packed_positions(pending, bd_size, bits=bits))
+            shape = (next_idx, self.n_features, bd_size, bd_size)
+            if blocks:
+                states = np.concatenate(blocks)
+            else:
+                states = np.zeros((0, (shape[1] * bd_size * bd_size + 7) // 8) if bits else shape, np.uint8)
             acts = np.asarray(all_actions, np.uint8).reshape(-1, 2)
-            _write_dataset(tmp_file, states, acts, names, np.asarray(offsets, np.int64).reshape(-1, 2))
+            _write_dataset(tmp_file, states, shape, acts, names, np.asarray(offsets, np.int64).reshape(-1, 2))
         except Exception:
             print("sgfs_to_hdf5 failed")
             if os.path.exists(tmp_file):
@@ -133,13 +151,19 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
         os.rename(tmp_file, hdf5_file)
 
 
-def _write_dataset(path, states, actions, names, offsets):
+def _have_h5py():
     try:
-        import h5py
+        import h5py  # noqa: F401
+        return True
     except ImportError:
-        h5py = None
-    if h5py is not None:
-        n_feat, size = states.shape[1], states.shape[2]
+        return False
+
+
+def _write_dataset(path, states, shape, actions, names, offsets):
+    """states: uint8 planes of `shape` (h5py present) or their bit-packed rows (archive fallback)"""
+    if _have_h5py():
+        import h5py
+        n_feat, size = shape[1], shape[2]
         with h5py.File(path, "w") as f:
             f.create_dataset("states", data=states, dtype=np.uint8, maxshape=(None, n_feat, size, size),
                              chunks=(64, n_feat, size, size), compression="lzf")
@@ -148,8 +172,15 @@ def _write_dataset(path, states, actions, names, offsets):
             for name, off in zip(names, offsets):
                 g[name] = [int(off[0]), int(off[1])]
         return
-    with open(path, "wb") as f:   # np.savez would append ".npz" to a bare name
-        np.savez_compressed(f, states=states, actions=actions, file_offsets_names=np.asarray(names), file_offsets=offsets)
+    # an .npz archive (np.load reads it), members written one by one with the fastest deflate level; the planes are stored
+    # bit-packed (`states_bits` + `states_shape`; supervised_policy_trainer.open_dataset unpacks them)
+    import zipfile
+    members = {"states_bits": states, "states_shape": np.asarray(shape, np.int64), "actions": actions,
+               "file_offsets_names": np.asarray(names), "file_offsets": offsets}
+    with zipfile.ZipFile(path, "w", compression=zipfile.ZIP_DEFLATED, compresslevel=1, allowZip64=True) as z:
+        for name, arr in members.items():
+            with z.open(name + ".npy", "w", force_zip64=True) as f:
+                np.lib.format.write_array(f, np.ascontiguousarray(arr), allow_pickle=False)
 
 
 def run_game_converter(cmd_line_args=None):

@@ -44,6 +44,10 @@ def open_dataset(path):
         magic = f.read(4)
     if magic[:2] == b"PK":
         z = np.load(path)
+        if "states_bits" in z.files:   # the converter's archive: one-hot planes bit-packed
+            shape = tuple(int(v) for v in z["states_shape"])
+            row = int(np.prod(shape[1:]))
+            return np.unpackbits(z["states_bits"], axis=1)[:, :row].reshape(shape), z["actions"]
         return z["states"], z["actions"]
     from . import hdf5_lite
     f = hdf5_lite.open_file(path, "r")
