@@ -86,8 +86,25 @@ class SLTrainer(object):
         if self._out is None or self._out.shape[0] != n:
             self._out = torch.empty((n, planes, size, size), dtype=torch.uint8, device="cuda")
             self._labels = torch.empty(n, dtype=torch.int32, device="cuda")
-        idx = torch.from_numpy(np.ascontiguousarray(index, np.int64)).cuda(non_blocking=True)
-        tf = torch.from_numpy(np.ascontiguousarray(transform, np.uint8)).cuda(non_blocking=True)
+        # gather indices (int64) and symmetry codes (uint8) travel in ONE pinned staging buffer / one copy per step; two
+        # staging buffers alternate so that the copy queued for step k is not overwritten while step k+1 is prepared
+        if getattr(self, "_stage_n", None) != n:
+            self._stage = [torch.empty(9 * n, dtype=torch.uint8).pin_memory() for _ in range(2)]
+            self._stage_dev = [torch.empty(9 * n, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            self._stage_ev = [None, None]
+            self._stage_n, self._stage_k = n, 0
+        k = self._stage_k = self._stage_k ^ 1
+        if self._stage_ev[k] is not None:
+            self._stage_ev[k].synchronize()
+        h = self._stage[k].numpy()
+        h[:8 * n].view(np.int64)[:] = index
+        h[8 * n:] = transform
+        self._stage_dev[k].copy_(self._stage[k], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._stage_ev[k] = ev
+        idx = self._stage_dev[k][:8 * n].view(torch.int64)
+        tf = self._stage_dev[k][8 * n:]
         _lib.check(_lib.lib().ag_augment(C.c_void_p(d_states.data_ptr()), C.c_void_p(d_actions.data_ptr()),
                                          C.c_void_p(idx.data_ptr()), C.c_void_p(tf.data_ptr()), n, planes, size,
                                          C.c_void_p(self._out.data_ptr()), C.c_void_p(self._labels.data_ptr()),
