@@ -76,13 +76,13 @@ struct WBoard {
 };
 
 __device__ __forceinline__ uint32_t wl_dilate(const WBoard& B, uint32_t g) {
-    uint32_t prev = __shfl_up_sync(kFullWarp, g, 1), next = __shfl_down_sync(kFullWarp, g, 1);
-    if (B.lane == 0) prev = 0;
-    if (B.lane == 31) next = 0;
-    const uint32_t up = (g >> B.size) | (next << (32 - B.size));                                           // x - 1
-    const uint32_t down = (g << B.size) | (prev >> (32 - B.size));                                         // x + 1
-    const uint32_t left = ((g & ~B.m.col_first) >> 1) | ((next & ~B.m.col_first_next) << 31);              // y - 1 (not from column 0)
-    const uint32_t right = ((g & ~B.m.col_last) << 1) | ((prev & ~B.m.col_last_prev) >> 31);               // y + 1 (not from the last column)
+    // rotate instead of shift-with-fill: lane 0's "previous" word is lane 31's, which is zero like every lane >= 12, and what
+    // lanes >= 12 compute is masked away by m.all; every shift across the word boundary is one funnel shift
+    const uint32_t prev = __shfl_sync(kFullWarp, g, (B.lane + 31) & 31), next = __shfl_sync(kFullWarp, g, (B.lane + 1) & 31);
+    const uint32_t up = __funnelshift_r(g, next, B.size);                                                   // x - 1
+    const uint32_t down = __funnelshift_l(prev, g, B.size);                                                 // x + 1
+    const uint32_t left = __funnelshift_r(g & ~B.m.col_first, next & ~B.m.col_first_next, 1);               // y - 1 (not from column 0)
+    const uint32_t right = __funnelshift_l(prev & ~B.m.col_last_prev, g & ~B.m.col_last, 1);                // y + 1 (not from the last column)
     return (up | down | left | right) & B.m.all;
 }
 __device__ __forceinline__ int wl_colour(const WBoard& B, int p) {
