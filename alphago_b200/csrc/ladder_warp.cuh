@@ -266,6 +266,7 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
 }
 
 // load a position (int8 board) into the warp's bitboards: 32 points per ballot
+// (B.m, B.size and B.lane are per-launch constants: set once by the caller with wmasks_make)
 __device__ __forceinline__ void wl_load(WBoard& B, const int8_t* board, int size, int player, int ko, int lane) {
     const int n = size * size;
     uint32_t bw = 0, ww = 0;
@@ -276,8 +277,7 @@ __device__ __forceinline__ void wl_load(WBoard& B, const int8_t* board, int size
         if (lane == w) { bw = b; ww = wt; }
     }
     B.blk = bw; B.wht = ww;
-    B.m = wmasks_make(size, lane);
-    B.size = size; B.player = player; B.ko = ko; B.lane = lane; B.undo_top = 0;
+    B.player = player; B.ko = ko; B.undo_top = 0;
 }
 
 }  // namespace enc
