@@ -22,3 +22,22 @@ for b in (128, 64, 256, 100, 128):
     torch.cuda.synchronize()
     print("batch", b, "reps", reps, "mismatching checks", bad, flush=True)
 print("done")
+
+# ---- training soak: the chained data gradients and weight gradients, thousands of unsynchronised steps, two batch sizes
+from alphago_b200.training import SLTrainer
+
+for b in (256, 96):
+    tnet = nn.ConvNet(19, 48, [192] * 12, [5] + [3] * 11, max_batch=256)
+    tnet.init_uniform(1)
+    tr = SLTrainer(tnet, lr=0.003, decay=0.0001)
+    rng = np.random.RandomState(b)
+    x = torch.from_numpy((rng.rand(b, 48, 19, 19) < 0.3).astype(np.uint8)).cuda()
+    y = torch.from_numpy(rng.randint(0, 361, b).astype(np.int32)).cuda()
+    for i in range(reps):
+        tr.step(x, y)
+    torch.cuda.synchronize()
+    loss, acc = tr.pop_metrics(b * reps)
+    print("train batch", b, "steps", reps, "mean loss %.4f acc %.4f" % (loss, acc), flush=True)
+    assert np.isfinite(loss)
+    tnet.close()
+print("training soak done")
