@@ -620,9 +620,10 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
         c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && (c.taps * (c.ldout / 64) + 3) / 4 <= kWgradCounterStride;
     }
-    // the arrival counters count in units of this batch's split factors: start over
-    AG_CUDA(cudaMemsetAsync(net->wgrad_counters, 0, sizeof(unsigned int) * net->n_conv * kWgradCounterStride, 0));
-    AG_CUDA(cudaStreamSynchronize(0));
+    // the arrival counters count in units of this batch's split factors: start over.  (Batch-size changes are rare; the device
+    // is drained first so that no weight-gradient launch of the old batch size, on whatever stream, still uses them.)
+    AG_CUDA(cudaDeviceSynchronize());
+    AG_CUDA(cudaMemset(net->wgrad_counters, 0, sizeof(unsigned int) * net->n_conv * kWgradCounterStride));
     for (auto& c : net->L) c.wgrad_chain_count = 0;
     net->wgrad_n = n;
     return AG_OK;
