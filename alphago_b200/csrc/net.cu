@@ -59,7 +59,7 @@ __global__ void pack_input_kernel(const uint8_t* __restrict__ planes, int n, int
 //   dlogit = (probs - onehot) * inv_batch; G[p][c] = dlogit[p] * w[c] * (X[p][c] > 0)
 //   per-image partials of dw[c], db, dpos[p] go to `partial` (reduced by head_reduce_kernel)
 constexpr int kHeadThreads = 384;
-__global__ void __launch_bounds__(kHeadThreads, 2)
+__global__ void __launch_bounds__(kHeadThreads)
 policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float* __restrict__ w, const float* __restrict__ bias,
                    const float* __restrict__ pos_bias, float* __restrict__ probs, const int32_t* __restrict__ labels,
                    float inv_batch, bf16* __restrict__ G, float* __restrict__ partial, float* __restrict__ loss_acc,
@@ -76,7 +76,7 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     __syncthreads();
     const int groups = ld / 8;  // 16-byte groups per row; lanes >= groups idle (ld <= 256)
     const float b0 = bias[0];
-    constexpr int U = 8;  // rows in flight per warp: the loop is bound by load latency, not bandwidth
+    constexpr int U = 5;  // rows in flight per warp (measured: 8 with two CTAs per SM forced was slower, 40.8 vs 38.2 us): the loop is bound by load latency, not bandwidth
     for (int p0 = warp; p0 < pts; p0 += nwarps * U) {
         uint4 v[U];
 #pragma unroll
