@@ -516,6 +516,19 @@ __device__ __forceinline__ int chain_layer_of(const ChainParams& P, int g, int l
     return l;
 }
 
+// first GEMM row of half-tile h of a layer, and the half-tile that holds GEMM row r (see ChainLayer::tiles_img)
+__device__ __forceinline__ int chain_tile_row(int h, int tiles_img, int img_stride) {
+    if (tiles_img == 0) return h * kTileM;
+    const int img = h / tiles_img;
+    return img * img_stride + (h - img * tiles_img) * kTileM;
+}
+__device__ __forceinline__ int chain_row_tile(int r, int tiles_img, int img_stride) {
+    if (tiles_img == 0) return r / kTileM;
+    const int img = r / img_stride;
+    const int part = (r - img * img_stride) / kTileM;
+    return img * tiles_img + (part < tiles_img ? part : tiles_img - 1);
+}
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restrict__ flags, const unsigned int epoch, const int win_bytes,
                   const int b_bytes_max, const int kBStages) {
@@ -555,7 +568,7 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
             const ChainLayer& L = P.layers[l];
             const ConvArgs& p = L.a;
             const int half_n = p.n / 2, b_bytes = half_n * 128, win_box = p.win_rows * 128;
-            const int m0 = (g - L.tile0) * 2 * kTileM + (int)rank * kTileM;
+            const int m0 = chain_tile_row((g - L.tile0) * 2 + (int)rank, L.tiles_img, p.in.img_stride);
             if (L.dep) {
                 // rows [m0 - halo, m0 + 128 + halo) of the input must be final: the 128-row tiles of the layer before that wrote them
                 int lo = m0 - p.halo, hi = m0 + kTileM - 1 + p.halo;
@@ -566,7 +579,8 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
                 if (lo < 0) lo = 0;
                 if (hi > L.prev_rows - 1) hi = L.prev_rows - 1;
                 const unsigned int* f = flags + P.layers[l - 1].flag0;
-                for (int j = lo / kTileM + lane; j <= hi / kTileM; j += 32) chain_wait_flag(f + j, epoch);
+                const int j0 = chain_row_tile(lo, L.prev_tiles_img, L.prev_in_img_stride), j1 = chain_row_tile(hi, L.prev_tiles_img, L.prev_in_img_stride);
+                for (int j = j0 + lane; j <= j1; j += 32) chain_wait_flag(f + j, epoch);
                 __syncwarp();
                 asm volatile("fence.proxy.async.global;" ::: "memory");  // the generic-proxy stores just acquired, before TMA reads them
             }
@@ -656,7 +670,8 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
             }
             const int buf = it & 1;
             const int tile128 = (g - L.tile0) * 2 + (int)rank;
-            epilogue_tile(L.a, s_bias, tile128 * kTileM + q * 32 + lane, tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride,
+            epilogue_tile(L.a, s_bias, chain_tile_row(tile128, L.tiles_img, L.a.in.img_stride) + q * 32 + lane,
+                          tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccStride,
                           &bars->acc_full[buf], (it >> 1) & 1);
             tc::fence_before_sync();
             tc::mbar_arrive_cluster(buf ? empty_remote1 : empty_remote0);  // the leader's accumulator-empty barrier

@@ -67,8 +67,13 @@ struct __align__(64) ChainLayer {
     int flag0;             // index of its first flag
     int dep;               // 0: input comes from outside the chain; 1: from the layer before, same row space; 2: from the layer
                            // before, whose GEMM rows live in another layout than its output (first layer 5x5): wait by image
-    int prev_in_img_stride;  // dep 2: img_stride of the previous layer's GEMM rows
+    int prev_in_img_stride;  // img_stride of the previous layer's GEMM rows
     int prev_rows;           // GEMM rows of the previous layer (bounds its flags)
+    // Image-aligned tiling: 0 = half-tile h covers GEMM rows [128h, 128h+128); k > 0 = every image has k half-tiles of its
+    // own, starting at the image's first row (3 x 128 = 384 rows cover the 19 x 20 = 380 rows of an image that produce
+    // output; the 20-slot zero row behind it is never computed: 4 % fewer tiles than 400 / 128 per image)
+    int tiles_img;
+    int prev_tiles_img;      // the same of the layer before (maps its rows to its half-tile flags)
 };
 
 

@@ -549,6 +549,20 @@ static void bwd_conv_args(ag_net* net, int l, int n, ConvArgs* a) {
     }
 }
 
+// half-tiles per image when a layer's tiles are aligned to images (0: plain 128-row tiling), see ChainLayer::tiles_img
+static int chain_tiles_img(const PixelLayout& L) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("AG_CHAIN_IMG_TILES"); on = (e && e[0] == '0') ? 0 : 1; }
+    const int k = (L.size * L.row_stride + 127) / 128;   // rows of an image that produce output
+    return (on && k * 128 < L.img_stride) ? k : 0;
+}
+
+static void chain_set_tiles(ChainLayer& e, int n_images) {
+    e.tiles_img = chain_tiles_img(e.a.in);
+    const int halves = e.tiles_img ? n_images * e.tiles_img : (e.a.m_total + 127) / 128;
+    e.n_pairs = (halves + 1) / 2;
+}
+
 // kernel-parameter tables of the two layer chains for batch n, split into launches of <= kChainMaxLayers layers
 static void chain_append(std::vector<ChainParams>& out, const ChainLayer& e_in, int* flag0) {
     if (out.empty() || out.back().n_layers == kChainMaxLayers) {
@@ -578,11 +592,12 @@ static int net_build_chains(ag_net* net, int n) {
         e.tmap_aw = c.tm_in_win; e.tmap_bh = c.tm_wf_half;
         fwd_conv_args(net, l, n, &e.a);
         e.a.win_rows = conv_window_rows(e.a.off, e.a.taps); e.a.halo = (e.a.win_rows - 128) / 2;
-        e.n_pairs = (e.a.m_total + 255) / 256;
+        chain_set_tiles(e, n);
         if (l > 0) {
             ConvLayer& pv = net->L[l - 1];
             e.dep = (pv.lin.img_stride == pv.lout.img_stride && pv.lin.row_stride == pv.lout.row_stride) ? 1 : 2;
             e.prev_in_img_stride = pv.lin.img_stride; e.prev_rows = n * pv.lin.img_stride;
+            e.prev_tiles_img = chain_tiles_img(pv.lin);
         }
         chain_append(net->chain_fwd_p, e, &flag0);
     }
@@ -595,12 +610,23 @@ static int net_build_chains(ag_net* net, int n) {
         e.tmap_aw = c.tm_g_win; e.tmap_bh = c.tm_wb_half;
         bwd_conv_args(net, l, n, &e.a);
         e.a.win_rows = conv_window_rows(e.a.off, e.a.taps); e.a.halo = (e.a.win_rows - 128) / 2;
-        e.n_pairs = (e.a.m_total + 255) / 256;
-        if (k > 0) { e.dep = 1; e.prev_in_img_stride = c.lout.img_stride; e.prev_rows = n * c.lout.img_stride; }  // G rows all live in lay_mid
+        chain_set_tiles(e, n);
+        if (k > 0) {  // G rows all live in lay_mid
+            e.dep = 1; e.prev_in_img_stride = c.lout.img_stride; e.prev_rows = n * c.lout.img_stride;
+            e.prev_tiles_img = chain_tiles_img(c.lout);
+        }
         chain_append(net->chain_bwd_p, e, &flag0);
     }
     net->chain_n = n;
     return AG_OK;
+}
+
+// K blocks per image for the weight gradient when they are aligned to images (0: linear), see WgradArgs::kb_img
+static int wgrad_kb_img(const PixelLayout& L, int krows) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("AG_WGRAD_IMG_BLOCKS"); on = (e && e[0] == '0') ? 0 : 1; }
+    const int k = (L.size * L.row_stride + krows - 1) / krows;
+    return (on && k * krows < L.img_stride) ? k : 0;
 }
 
 static int net_build_wgrad_maps(ag_net* net, int n) {
@@ -618,6 +644,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         WgradArgs w;
         memset(&w, 0, sizeof(w));
         w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
+        w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
         c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && (c.taps * (c.ldout / 64) + 3) / 4 <= kWgradCounterStride;
     }
     // the arrival counters count in units of this batch's split factors: start over.  (Batch-size changes are rare; the device
@@ -982,6 +1009,7 @@ static int net_wgrad_one(ag_net* net, int layer, int n, cudaStream_t st) {
     memset(&w, 0, sizeof(w));
     w.m_total = (int)rows; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
     w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
+    w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
     const bool fused_bias = c.kin + 16 <= 256;  // the bias gradient rides in the weight-gradient GEMM as an extra column of ones
     w.bias_scratch = fused_bias ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
     int rc = wgrad_launch(c.tm_wg, w, c.gw, fused_bias ? c.gb : nullptr, st);
@@ -1029,6 +1057,7 @@ static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) 
         memset(&w, 0, sizeof(w));
         w.m_total = n * first.lin.img_stride; w.taps = first.taps; memcpy(w.off, first.off_fwd, sizeof(int) * first.taps);
         w.ldout = first.ldout; w.kin = first.kin; w.splits = first.wgrad_splits;
+        w.kb_img = wgrad_kb_img(first.lin, first.tm_wg.krows); w.img_stride = first.lin.img_stride;
         int rc = wgrad_chain_launch(w, e, cnt, st);
         if (rc) return rc;
     }
@@ -1150,6 +1179,7 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         w.m_total = n * c.lin.img_stride; w.taps = c.taps; memcpy(w.off, c.off_fwd, sizeof(int) * c.taps);
         w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits; w.scratch = net->wgrad_scratch;
         w.bias_scratch = c.kin + 16 <= 256 ? net->wgrad_scratch + net->wgrad_scratch_floats : nullptr;
+        w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
         return wgrad_launch(c.tm_wg, w, c.gw, w.bias_scratch ? c.gb : nullptr, st);
     }
     if (mode == 1 && layer > 0) {

@@ -125,7 +125,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     WgradPlan* plan = reinterpret_cast<WgradPlan*>(bars + 1);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform by construction
 
-    const int kb_total = (p.m_total + p.krows - 1) / p.krows;
+    const int kb_total = p.kb_img ? (p.m_total / p.img_stride) * p.kb_img : (p.m_total + p.krows - 1) / p.krows;
     const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
 
     pdl_trigger();
@@ -164,7 +164,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (tc::elect_one()) {
                 uint8_t* s = base + stage * stage_bytes;
                 tc::mbar_expect_tx(&bars->full[stage], tx_bytes);
-                const int m0 = kb * p.krows;
+                const int m0 = p.kb_img ? (kb / p.kb_img) * p.img_stride + (kb % p.kb_img) * p.krows : kb * p.krows;
                 for (int w = 0; w < n_win; w++)  // rows outside the tensor read as zeros
                     tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
                 for (int j = 0; j < nb; j++) {
@@ -365,7 +365,7 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
     uint64_t* acc_empty = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(plan + 1) + 7) & ~uintptr_t(7));
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
 
-    const int kb_total = (p.m_total + p.krows - 1) / p.krows;
+    const int kb_total = p.kb_img ? (p.m_total / p.img_stride) * p.kb_img : (p.m_total + p.krows - 1) / p.krows;
     const int kb0 = (int)((long long)kb_total * split / p.splits), kb1 = (int)((long long)kb_total * (split + 1) / p.splits);
 
     if (threadIdx.x == 0) {
@@ -403,7 +403,7 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
                 if (tc::elect_one()) {
                     uint8_t* s = base + stage * stage_bytes;
                     tc::mbar_expect_tx(&bars->full[stage], tx_bytes);
-                    const int m0 = kb * p.krows;
+                    const int m0 = p.kb_img ? (kb / p.kb_img) * p.img_stride + (kb % p.kb_img) * p.krows : kb * p.krows;
                     for (int w = 0; w < n_win; w++)  // rows outside the tensor read as zeros
                         tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
                     for (int c = 0; c < xchunks; c++)
@@ -644,6 +644,7 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     }
     args.tiles = wgrad_tiling(args.taps, args.ldout, args.kin, &args.tpg, &args.groups);
     if (args.splits < 1) args.splits = 1;
+    if (args.kb_img && (args.img_stride < 1 || args.m_total % args.img_stride != 0 || args.kb_img * maps.krows > args.img_stride)) args.kb_img = 0;
     static size_t configured = 0;
     if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
     if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
@@ -678,7 +679,7 @@ bool wgrad_chain_ok(const WgradArgs& a_in, const WgradMaps& maps, bool with_bias
     a.tiles = wgrad_tiling(a.taps, a.ldout, a.kin, &a.tpg, &a.groups);
     if (a.tpg != 1 || a.kin % 64 || a.ldout % 64 || a.kin > 256) return false;
     if (with_bias && a.kin + 16 > 256) return false;
-    const int kb_total = (a.m_total + maps.krows - 1) / maps.krows;
+    const int kb_total = a.kb_img ? (a.m_total / a.img_stride) * a.kb_img : (a.m_total + maps.krows - 1) / maps.krows;
     if (a.splits < 1 || kb_total < a.splits) return false;
     // every CTA must be resident at once (they wait for each other's partials): one CTA per SM with this much shared memory
     return a.tiles * a.splits <= sm_count() && wgrad_stages(a.taps, a.kin, with_bias, maps.krows, maps.win_rows) >= 2;
@@ -692,6 +693,7 @@ int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_lay
     args.tiles = wgrad_tiling(args.taps, args.ldout, args.kin, &args.tpg, &args.groups);
     args.win_rows = entries[0].maps->win_rows;
     args.krows = entries[0].maps->krows;
+    if (args.kb_img && (args.img_stride < 1 || args.m_total % args.img_stride != 0 || args.kb_img * args.krows > args.img_stride)) args.kb_img = 0;
     args.debug = 0;
     const bool with_bias = entries[0].bias_scratch != nullptr;
     for (int i = 0; i < n_layers; i++) {

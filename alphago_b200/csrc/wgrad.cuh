@@ -20,6 +20,10 @@ struct WgradArgs {
     int tiles;     // filled by wgrad_launch
     int tpg;       // filled by wgrad_launch: taps per B operand (1 = shifted-G tiling, >= 2 = taps-in-N tiling, see wgrad.cu)
     int groups;    // filled by wgrad_launch: tap groups (taps-in-N tiling)
+    int kb_img;    // 0: K blocks tile the rows linearly; k > 0: every image has k K blocks of its own starting at its first row
+                   // (6 x 64 = 384 rows cover the 380 rows of a 19 x 20 image that can be non-zero; the zero row behind them is
+                   // skipped: 4 % fewer UMMAs).  Set by the caller together with img_stride; both operands share the layout.
+    int img_stride;
     int win_rows;  // filled by wgrad_launch from the maps
     int krows;     // filled by wgrad_launch from the maps: pixel rows per pipeline stage (32 or 64)
     int debug;     // experiments only (AG_WGRAD_DEBUG)
