@@ -177,7 +177,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
-        const uint32_t idesc = tc::idesc_bf16(128, umma_n, 1, 1);
+        // the ones column (N + 16) only where an accumulator holds a slot whose column sums are wanted (an unshifted slot):
+        // the other accumulators run with N = the X columns alone (3 of 14 accumulators of a 3x3 192-filter layer need it)
+        uint32_t idesc_acc[2];
+        for (int a = 0; a < 2; a++) {
+            const int lo = plan->lo[a], hi = plan->hi[a];
+            const bool ones = with_bias && ((plan->slot_off[lo] >= 0 && plan->slot_bias[lo] >= 0) || (hi >= 0 && plan->slot_bias[hi] >= 0));
+            idesc_acc[a] = tc::idesc_bf16(128, ones ? umma_n : acc_cols, 1, 1);
+        }
         const bool second = a_live > 2;  // the second accumulator has at least one live half
         // A operand of accumulator a: rows 0-63 from slot lo, rows 64-127 from slot hi (LBO = their distance)
         uint32_t a_off[2], a_lbo[2];
@@ -204,9 +211,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                 const uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
 #pragma unroll 4
                 for (int k = 0; k < ksteps; k++) {  // 16 pixel rows per UMMA: +2048 B
-                    tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                    tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc_acc[0], (kb > kb0) || (k > 0));
                     if (second)
-                        tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                        tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc_acc[1], (kb > kb0) || (k > 0));
                 }
                 tc::umma_commit(&bars->empty[stage]);
                 if (kb == kb1 - 1) tc::umma_commit(&bars->acc_full);
@@ -414,7 +421,14 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
             }
         }
     } else if (warp == 1) {
-        const uint32_t idesc = tc::idesc_bf16(128, umma_n, 1, 1);
+        // the ones column (N + 16) only where an accumulator holds a slot whose column sums are wanted (an unshifted slot):
+        // the other accumulators run with N = the X columns alone (3 of 14 accumulators of a 3x3 192-filter layer need it)
+        uint32_t idesc_acc[2];
+        for (int a = 0; a < 2; a++) {
+            const int lo = plan->lo[a], hi = plan->hi[a];
+            const bool ones = with_bias && ((plan->slot_off[lo] >= 0 && plan->slot_bias[lo] >= 0) || (hi >= 0 && plan->slot_bias[hi] >= 0));
+            idesc_acc[a] = tc::idesc_bf16(128, ones ? umma_n : acc_cols, 1, 1);
+        }
         const bool second = a_live > 2;
         uint32_t a_off[2], a_lbo[2];
         for (int a = 0; a < 2; a++) {
@@ -439,9 +453,9 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
                     const uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
 #pragma unroll 4
                     for (int k = 0; k < ksteps; k++) {  // 16 pixel rows per UMMA: +2048 B
-                        tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                        tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc_acc[0], (kb > kb0) || (k > 0));
                         if (second)
-                            tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc, (kb > kb0) || (k > 0));
+                            tc::umma_bf16(tmem_base + kAccStride, adesc1 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc_acc[1], (kb > kb0) || (k > 0));
                     }
                     tc::umma_commit(&bars->empty[stage]);
                     if (kb == kb1 - 1) tc::umma_commit(&bars->acc_full);
