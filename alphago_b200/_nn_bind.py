@@ -17,6 +17,7 @@ def bind(L):
     L.ag_net_backward_layer.argtypes = [vp, i, i, vp]
     L.ag_net_backward_range.argtypes = [vp, i, i, i, vp]
     L.ag_net_set_sm_budget.argtypes = [vp, i]
+    L.ag_net_set_loss.argtypes = [vp, i]
     L.ag_net_grads.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_longlong), vp]
     L.ag_net_sgd.argtypes = [vp, C.c_float, C.c_float, C.c_float, vp]
     L.ag_net_train_step.argtypes = [vp, vp, vp, i, C.c_float, C.c_float, vp, vp]

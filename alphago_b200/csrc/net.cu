@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(kHeadThreads)
 policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const float* __restrict__ w, const float* __restrict__ bias,
                    const float* __restrict__ pos_bias, float* __restrict__ probs, const int32_t* __restrict__ labels,
                    float inv_batch, bf16* __restrict__ G, float* __restrict__ partial, float* __restrict__ loss_acc,
-                   float* __restrict__ dlogits_out) {
+                   float* __restrict__ dlogits_out, int loss_kind) {
     pdl_trigger();
     pdl_wait();
     __shared__ float s_logit[368];
@@ -141,16 +141,47 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
             if (ov > bv || (ov == bv && ob < best)) { bv = ov; best = ob; }
         }
         if (lane == 0) {
-            float pl = fminf(fmaxf(s_logit[label], 1e-7f), 1.f - 1e-7f);
-            atomicAdd(&loss_acc[0], -logf(pl));
+            if (loss_kind == 0) {
+                float pl = fminf(fmaxf(s_logit[label], 1e-7f), 1.f - 1e-7f);
+                atomicAdd(&loss_acc[0], -logf(pl));
+            }
             atomicAdd(&loss_acc[1], best == label ? 1.f : 0.f);
         }
     }
     __syncthreads();
+    // Keras' binary_crossentropy on the softmax output (reinforcement_policy_trainer.py:109): per sample the MEAN over the pts
+    // outputs of -(y log p + (1-y) log(1-p)), p clipped to [1e-7, 1-1e-7] (no gradient where the clip is active).
+    // With a_j = dL/dp_j the logit gradient is p_k (a_k - sum_j p_j a_j).
+    float bce_s = 0.f;
+    if (loss_kind == 1) {
+        float ls = 0.f, ps = 0.f;
+        for (int p = threadIdx.x; p < pts; p += kHeadThreads) {
+            const float pr = s_logit[p], pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
+            const bool on = p == label, inside = pr > 1e-7f && pr < 1.f - 1e-7f;
+            ls += on ? -logf(pc) : -logf(1.f - pc);
+            const float a = inside ? (on ? -1.f / pc : 1.f / (1.f - pc)) : 0.f;
+            ps += pr * a;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { ls += __shfl_xor_sync(0xffffffffu, ls, o); ps += __shfl_xor_sync(0xffffffffu, ps, o); }
+        __shared__ float s_bce[2][kHeadThreads / 32];
+        if (lane == 0) { s_bce[0][warp] = ls; s_bce[1][warp] = ps; }
+        __syncthreads();
+        ls = 0.f;
+        for (int i = 0; i < nwarps; i++) { ls += s_bce[0][i]; bce_s += s_bce[1][i]; }
+        if (threadIdx.x == 0) atomicAdd(&loss_acc[0], ls / pts);
+    }
     // dlogit in place
     float dbl = 0.f;
     for (int p = threadIdx.x; p < pts; p += kHeadThreads) {
-        float d = (s_logit[p] - (p == label ? 1.f : 0.f)) * inv_batch;
+        float d;
+        if (loss_kind == 0) d = (s_logit[p] - (p == label ? 1.f : 0.f)) * inv_batch;
+        else {
+            const float pr = s_logit[p], pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
+            const bool inside = pr > 1e-7f && pr < 1.f - 1e-7f;
+            const float a = inside ? (p == label ? -1.f / pc : 1.f / (1.f - pc)) : 0.f;
+            d = pr * (a - bce_s) * (inv_batch / pts);
+        }
         s_logit[p] = d;
         dbl += d;
         if (dlogits_out) dlogits_out[(size_t)img * pts + p] = d;
@@ -488,6 +519,7 @@ struct ag_net {
     std::vector<long long> grad_offsets;  // start of each conv layer's slice, then head, then end
     int wgrad_n = -1;
     int sm_budget = 0;   // SMs the weight-gradient launches may fill (0 = all)
+    int loss_kind = 0;   // 0 categorical cross-entropy (SL trainer), 1 Keras binary cross-entropy on the softmax output (RL trainer)
     int colsum_blocks = 0;
     long long iterations = 0;
     void* sgd_table = nullptr;      // device copy of the SGD kernel's per-layer table
@@ -963,7 +995,7 @@ int ag_net_forward(ag_net* net, const uint8_t* d_planes, int n, float* d_out, vo
     ConvLayer& cl = net->L[net->n_conv - 1];
     if (net->head_kind == 0) {
         launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
-                                                      d_out, nullptr, 0.f, nullptr, nullptr, nullptr, nullptr);
+                                                      d_out, nullptr, 0.f, nullptr, nullptr, nullptr, nullptr, 0);
         AG_LAUNCH_CHECK("policy_head_kernel");
     } else {
         launch_k(value_head_kernel, dim3(n), dim3(256), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->d1w, net->d1b, net->d2w, net->d2b,
@@ -992,7 +1024,7 @@ int ag_net_forward_loss(ag_net* net, const uint8_t* d_planes, const int32_t* d_l
     bf16* G = (last == 0 && net->x0_grad) ? net->x0_grad : net->gbuf[last];
     if (last == 0 && net->x0_grad) { set_error("single-layer nets with a wide first filter are not trainable"); return AG_ESTATE; }
     launch_k(policy_head_kernel, dim3(n), dim3(kHeadThreads), 0, st, cl.act, cl.ldout, cl.lout, net->hw, net->hb, net->use_pos_bias ? net->hpos : nullptr,
-                                                  d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr);
+                                                  d_probs, d_labels, 1.f / n, G, net->head_partial, d_loss_acc, nullptr, net->loss_kind);
     AG_LAUNCH_CHECK("policy_head_kernel");
     launch_k(head_reduce_kernel, dim3((625 + 7) / 8), dim3(256), 0, st, net->head_partial, n, cl.ldout, net->board * net->board, net->g_hw, net->g_hb,
                                                         net->use_pos_bias ? net->g_hpos : nullptr);
@@ -1138,6 +1170,15 @@ int ag_net_set_sm_budget(ag_net* net, int sms) {
     if (sms < 0) { set_error("ag_net_set_sm_budget: negative"); return AG_EINVAL; }
     net->sm_budget = sms;
     net->wgrad_n = -1;  // re-plan the split factors at the next forward_loss
+    return AG_OK;
+}
+
+// Loss the head kernel differentiates: 0 = categorical cross-entropy (supervised_policy_trainer.py:200), 1 = Keras'
+// binary_crossentropy applied to the 361 softmax outputs (reinforcement_policy_trainer.py:109).  d_loss_acc[0] accumulates
+// that loss; [1] stays the argmax-match count.
+int ag_net_set_loss(ag_net* net, int kind) {
+    if (kind != 0 && kind != 1) { set_error("ag_net_set_loss: kind %d (0 categorical, 1 binary cross-entropy)", kind); return AG_EINVAL; }
+    net->loss_kind = kind;
     return AG_OK;
 }
 

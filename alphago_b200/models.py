@@ -45,9 +45,14 @@ class _Scalar(object):
 
 
 class _SGD(object):
+    """stands in for keras.optimizers.SGD (spt.py:199, rpt.py:108): exported as `SGD`"""
+
     def __init__(self, lr=0.01, momentum=0.0, decay=0.0):
         self.lr, self.momentum, self.decay = _Scalar(lr), float(momentum), float(decay)
         self.iterations = 0
+
+
+SGD = _SGD
 
 
 def _conv_layer_json(name, nb_filter, width, activation, input_shape=None):
@@ -120,6 +125,8 @@ class SequentialModel(object):
         self.max_batch = int(max(n, 2 * self.max_batch))
         self.net = nn.ConvNet(self.board, self.in_planes, self.filters, self.widths, head=self.head, max_batch=self.max_batch)
         self.set_weights(weights)
+        if self.head == nn.POLICY_HEAD and getattr(self, "loss", None) == "binary_crossentropy":
+            self.net.set_loss(1)
         self._trainer = None
 
     # ------------------------------------------------------------------ Keras surface
@@ -188,14 +195,20 @@ class SequentialModel(object):
         return out if self.head == nn.POLICY_HEAD else out.reshape(-1, 1)
 
     def compile(self, loss=None, optimizer=None, metrics=None):
+        """Keras' compile as far as the two trainers use it: loss 'categorical_crossentropy' (spt.py:200, the default) or
+        'binary_crossentropy' (rpt.py:109), an SGD-like optimizer object with .lr/.momentum/.decay"""
+        if loss not in (None, "categorical_crossentropy", "binary_crossentropy"):
+            raise ValueError("unsupported loss %r" % (loss,))
         self.loss = loss
+        if self.head == nn.POLICY_HEAD:
+            self.net.set_loss(1 if loss == "binary_crossentropy" else 0)
         if optimizer is None or isinstance(optimizer, str):
             optimizer = _SGD()
         self.optimizer = optimizer
 
     def fit(self, X, Y, nb_epoch=1, batch_size=32, verbose=0):
-        """SGD on (X planes, Y one-hot moves) -- the call the RL trainer makes (rpt.py:102).  Cross-entropy
-        against the arg-max of each Y row; a negative optimizer.lr flips the update as rpt.py:95-101 intends."""
+        """SGD on (X planes, Y one-hot moves) -- the call the RL trainer makes (rpt.py:102).  The compiled loss against the
+        arg-max of each Y row; a negative optimizer.lr flips the update as rpt.py:95-101 intends."""
         import torch
         from .training import SLTrainer
         if self.optimizer is None:

@@ -119,6 +119,10 @@ class ConvNet(object):
                                                 lr, momentum, C.c_void_p(loss_acc.data_ptr()), _lib.current_stream()),
                    "ag_net_train_step")
 
+    def set_loss(self, kind):
+        """0 = categorical cross-entropy, 1 = Keras binary cross-entropy on the softmax outputs; see ag_net_set_loss"""
+        _lib.check(_lib.lib().ag_net_set_loss(self._h, int(kind)), "ag_net_set_loss")
+
     def set_sm_budget(self, sms):
         """SMs the weight-gradient launches may fill (0 = all); see ag_net_set_sm_budget"""
         _lib.check(_lib.lib().ag_net_set_sm_budget(self._h, int(sms)), "ag_net_set_sm_budget")

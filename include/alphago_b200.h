@@ -131,6 +131,10 @@ int ag_net_backward_range(ag_net* net, int hi, int lo, int n, void* stream);
 /* SMs the weight-gradient launches may fill (0 = all).  No counterpart in the reference (Keras/Theano schedule their own
  * kernels); data-parallel training leaves a few SMs to the gradient all-reduce that runs beside the backward pass. */
 int ag_net_set_sm_budget(ag_net* net, int sms);
+/* loss differentiated by ag_net_forward_loss: 0 = categorical cross-entropy (compile(loss='categorical_crossentropy'),
+ * supervised_policy_trainer.py:200), 1 = Keras binary_crossentropy on the softmax outputs
+ * (compile(loss='binary_crossentropy'), reinforcement_policy_trainer.py:109) */
+int ag_net_set_loss(ag_net* net, int kind);
 /* the flat fp32 gradient buffer (device) data-parallel training all-reduces; h_offsets gets n_conv+2 offsets */
 int ag_net_grads(ag_net* net, float** d_grads, long long* count, long long* h_offsets);
 /* fused SGD(+momentum) over all parameters; gradients are multiplied by grad_scale first

@@ -96,11 +96,22 @@ def forward(params, planes, emulate_bf16=False, dtype=torch.float32, want_grad=F
     return out
 
 
-def loss_and_grads(params, planes, labels, emulate_bf16=False, dtype=torch.float32):
+def loss_and_grads(params, planes, labels, emulate_bf16=False, dtype=torch.float32, loss_kind="categorical"):
     """categorical cross-entropy (mean over the batch, Keras clips probabilities to [1e-7, 1-1e-7])
-    + accuracy + gradients of every parameter (spt.py:199-200)."""
+    + accuracy + gradients of every parameter (spt.py:199-200).  loss_kind="binary": Keras 1.0's binary_crossentropy on
+    the softmax outputs against the one-hot move (reinforcement_policy_trainer.py:109): per sample the mean over the
+    outputs of -(y log p + (1-y) log(1-p)) with p clipped to [1e-7, 1-1e-7], mean over the batch."""
     out = forward(params, planes, emulate_bf16, dtype, want_grad=True)
     lab = torch.as_tensor(np.asarray(labels), dtype=torch.long)
+    if loss_kind == "binary":
+        pr = torch.softmax(out["logits"], dim=1)
+        pc = pr.clamp(1e-7, 1 - 1e-7)
+        y = F.one_hot(lab, pr.shape[1]).to(pr.dtype)
+        loss = (-(y * torch.log(pc) + (1 - y) * torch.log(1 - pc))).mean(1).mean()
+        loss.backward()
+        acc = (out["probs"].argmax(1) == lab).double().mean()
+        grads = [t.grad.numpy() for t in out["tensors"]]
+        return float(loss.detach()), float(acc), grads, out
     p = out["probs"].gather(1, lab[:, None])[:, 0]
     loss = -torch.log(p.clamp(1e-7, 1 - 1e-7)).mean()
     # gradient of the unclipped softmax-CE, which is what Theano's fused op yields

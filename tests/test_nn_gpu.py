@@ -308,3 +308,43 @@ def test_chained_forward_survives_back_to_back_launches():
             assert torch.equal(out, first)
     torch.cuda.synchronize()
     net.close()
+
+
+def test_binary_crossentropy_backward_matches_oracle():
+    """the RL trainer's loss (reinforcement_policy_trainer.py:109: Keras binary_crossentropy on the 361 softmax outputs):
+    loss value and every gradient against torch autograd of the same expression; a negative learning rate (the reference's
+    way of pushing a lost game's moves down, rpt:98-101) then moves the weights the other way"""
+    import torch
+    board, planes, filters, widths, batch = 19, 48, [64, 64, 64], [5, 3, 3], 12
+    params = no.make_params(planes, filters, widths, seed=13, bias_scale=0.05)
+    params["head_w"] = (params["head_w"] * 20).astype(np.float32)
+    x = rand_planes(batch, planes, board, 7)
+    labels = np.random.RandomState(5).randint(0, board * board, batch).astype(np.int32)
+    net = make_net(board, planes, filters, widths, params, max_batch=batch)
+    net.set_loss(1)
+    acc = torch.zeros(2, device="cuda")
+    net.forward_loss(torch.from_numpy(x).cuda(), torch.from_numpy(labels).cuda(), acc)
+    net.backward_range(len(filters) - 1, 0, batch)
+    torch.cuda.synchronize()
+    loss, accuracy, grads, out = no.loss_and_grads(params, x, labels, emulate_bf16=True, loss_kind="binary")
+    got_loss, got_correct = acc.cpu().numpy()
+    assert abs(got_loss / batch - loss) <= 2e-3 * max(1e-3, abs(loss))
+    assert got_correct == round(accuracy * batch)
+    got = grads_from_flat(net, net.grad_tensor().cpu().numpy())
+    names = []
+    for l in range(len(filters)):
+        names += ["conv%d.w" % l, "conv%d.b" % l]
+    names += ["head.w", "head.b"]
+    for name, g, want in zip(names, got, grads):
+        if name == "head.b":
+            assert abs(float(g[0])) < 1e-6 and abs(float(want[0])) < 1e-6
+            continue
+        assert rel_err(g, want) < 3e-2 and cosine(g, want) > 0.999, "%s rel %g cos %g" % (name, rel_err(g, want), cosine(g, want))
+    w_before = net.get_conv(1)[0].copy()
+    net.sgd(-0.5, 0.0, 1.0)
+    w_after = net.get_conv(1)[0]
+    step = w_after - w_before
+    assert cosine(step, got[2]) > 0.99   # w - (-lr) g: the weights moved ALONG the gradient
+    with pytest.raises(Exception):
+        net.set_loss(7)
+    net.close()
