@@ -64,3 +64,38 @@ class ProbabilisticPolicyPlayer(object):
         for i, move_probs in enumerate(all_moves_distributions):
             move_list[i] = go.PASS_MOVE if len(move_probs) == 0 else self._sample(move_probs)
         return move_list
+
+    def get_moves_fast(self, states):
+        """get_moves without per-move Python objects: the candidate mask is the encoder's own `sensibleness` plane (legal and
+        not the mover's eye, preprocessing.py:155-161), the policy is raised to 1/temperature, renormalised and sampled
+        on the device (torch.multinomial: a different random stream from get_moves' np.random.choice, same distribution).
+        Needs 'sensibleness' among the policy's features; returns a list of (x, y) / PASS_MOVE."""
+        import torch
+        from .preprocessing import FEATURE_SIZES, pack_state
+        pre = self.policy.preprocessor
+        off = 0
+        for f in pre.feature_list:
+            if f.lower() == "sensibleness":
+                break
+            off += FEATURE_SIZES[f.lower()]
+        else:
+            raise ValueError("get_moves_fast needs the 'sensibleness' feature plane")
+        n = len(states)
+        if n == 0:
+            return []
+        size = states[0].size
+        packed = [pack_state(st) for st in states]
+        board = torch.from_numpy(np.stack([p[0] for p in packed])).cuda(non_blocking=True)
+        age = torch.from_numpy(np.stack([p[1] for p in packed])).cuda(non_blocking=True)
+        player = torch.from_numpy(np.asarray([p[2] for p in packed], np.int8)).cuda(non_blocking=True)
+        ko = torch.from_numpy(np.asarray([p[3] for p in packed], np.int16)).cuda(non_blocking=True)
+        planes = pre.encode_packed(board, age, player, ko, size)
+        probs = self.policy.model.forward_device(planes)
+        mask = planes[:, off].reshape(n, -1) > 0
+        w = (probs.clamp_min(1e-30) ** self.beta) * mask
+        any_move = mask.any(1)
+        w = torch.where(any_move[:, None], w, torch.ones_like(w))   # rows without a sensible move: sampled, then turned into a pass
+        choice = torch.multinomial(w, 1)[:, 0].cpu().numpy()
+        has = any_move.cpu().numpy()
+        return [divmod(int(c), size) if h else go.PASS_MOVE for c, h in zip(choice, has)]
+

@@ -28,11 +28,12 @@ from .preprocessing import Preprocess, pack_state
 from .util import flatten_idx
 
 
-def make_training_pairs(player, opp, features, mini_batch_size, reference_quirks=True, max_plies=None):
+def make_training_pairs(player, opp, features, mini_batch_size, reference_quirks=True, max_plies=None, fast=False):
     """Make training pairs for a batch of matches.  Returns (X_list, y_list, winners): per game the uint8 planes
     (n_moves, F, size, size) of the positions the learner moved in, the one-hot moves (n_moves, size*size), and
     `GameState.get_winner()`.  After the call `make_training_pairs.player_color` holds the learner's colour.
-    max_plies (not in the reference) ends games early for tests."""
+    max_plies (not in the reference) ends games early for tests; fast=True lets the players pick their moves with
+    `get_moves_fast` (masking and sampling on the device) instead of per-state Python move lists."""
     preprocessor = Preprocess(features)
     bsize = player.policy.model.input_shape[-1]
     bsize_flat = bsize * bsize
@@ -55,10 +56,10 @@ def make_training_pairs(player, opp, features, mini_batch_size, reference_quirks
     plies = 0
     while True:
         prev = [pack_state(st) for st in states]   # cache states before moves (copies: the engine packs into new arrays)
-        do_move(prev, player1.get_moves(states))
+        do_move(prev, player1.get_moves_fast(states) if fast else player1.get_moves(states))
         if not reference_quirks:
             prev = [pack_state(st) for st in states]
-        do_move(prev, player2.get_moves(states))
+        do_move(prev, player2.get_moves_fast(states) if fast else player2.get_moves(states))
         plies += 2
         if all(st.is_end_of_game for st in states) or (max_plies is not None and plies >= max_plies):
             break

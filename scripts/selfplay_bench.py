@@ -31,6 +31,12 @@ for games in (16, 128):
     train_batch(pl, X, y, w, 0.001)
     torch.cuda.synchronize()
     t2 = time.time()
+    make_training_pairs(pl, pl, FEATS, games, max_plies=8, fast=True)
+    torch.cuda.synchronize()
+    t3 = time.time()
+    make_training_pairs(pl, pl, FEATS, games, max_plies=plies, fast=True)
+    torch.cuda.synchronize()
+    t4 = time.time()
     rows.append({"games": games, "plies_per_game": plies, "selfplay_plies_per_s": round(games * plies / (t1 - t0), 1),
-                 "selfplay_s": round(t1 - t0, 3), "update_s": round(t2 - t1, 3), "training_pairs": int(sum(len(a) for a in X))})
+                 "selfplay_s": round(t1 - t0, 3), "fast_selfplay_plies_per_s": round(games * plies / (t4 - t3), 1), "update_s": round(t2 - t1, 3), "training_pairs": int(sum(len(a) for a in X))})
 print(json.dumps({"what": "make_training_pairs + train_batch, 19x19, 12 x 128-filter policy vs itself", "rows": rows}))

@@ -70,6 +70,21 @@ def test_make_training_pairs_and_train_batch():
     assert abs(learner.policy.model.optimizer.lr.get_value()) == 0.05
 
 
+def test_fast_move_selection_is_sensible():
+    import torch
+    pl = ProbabilisticPolicyPlayer(_policy(6), temperature=0.7)
+    torch.manual_seed(0)
+    np.random.seed(2)
+    X, y, w = make_training_pairs(pl, pl, FEATS, 5, reference_quirks=False, max_plies=60, fast=True)
+    assert all(len(a) > 0 for a in X)
+    assert all(X_[i, 2].reshape(-1)[y_[i].argmax()] == 1 for X_, y_ in zip(X, y) for i in range(len(X_)))   # played on empty points
+    st = go.GameState(7)
+    for mv in [(3, 3), (3, 4), (2, 2), (4, 4)]:
+        st.do_move(mv)
+    for m in pl.get_moves_fast([st] * 8):
+        assert m in st.get_legal_moves(include_eyes=False)
+
+
 def test_run_loop_plays_to_the_end_on_a_small_board():
     learner = ProbabilisticPolicyPlayer(_policy(4, board=5))
     args = argparse.Namespace(learning_rate=0.02, iterations=1, save_every=2, game_batch_size=3)
