@@ -623,6 +623,7 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
                 for (int kc = 0; kc < p.kchunks; kc++) {
                     tc::mbar_wait(&bars->a_full[ai], aph);
                     const uint64_t a_desc0 = tc::desc_kmajor_sw128(tc::smem_u32(base + ai * win_bytes)) + (uint64_t)(p.halo * 8);  // window row `halo`
+                    const int ksteps = (kc == p.kchunks - 1 && p.ksteps_last > 0) ? p.ksteps_last : 4;
                     for (int t0 = 0; t0 < p.taps; t0 += kTapsPerStage) {
                         const int nt = min(kTapsPerStage, p.taps - t0);
                         if (!ready) tc::mbar_wait(&bars->b_full[bi], bph);
@@ -636,7 +637,7 @@ conv_chain_kernel(const __grid_constant__ ChainParams P, unsigned int* __restric
                                     const uint64_t bdesc = b_desc0 + (uint64_t)(j * (b_bytes >> 4));
 #pragma unroll
                                     for (int k = 0; k < 4; k++)
-                                        tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t0 | j | k) != 0);
+                                        if (k < ksteps) tc::umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kc | t0 | j | k) != 0);
                                 }
                             }
                             tc::umma_commit_pair(&bars->b_empty[bi]);

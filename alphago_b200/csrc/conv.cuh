@@ -40,6 +40,8 @@ struct ConvArgs {
     int out_ld;
     int relu;
     int halo, win_rows;   // filled by conv_gemm_launch (window kernel): largest |off|, rows of the activation window box
+    int ksteps_last;      // chain kernel: K=16 steps worth issuing in the LAST 64-channel slice (0 = all 4): the channels behind
+                          // the real ones are zero padding (48 input planes fill 3 of the first layer's 4 steps)
     int debug;            // measurement only (AG_CONV_DEBUG): 1 = skip A loads, 2 = skip B loads, 4 = skip epilogue memory traffic
 };
 

@@ -623,6 +623,7 @@ static int net_build_chains(ag_net* net, int n) {
         ConvLayer& c = net->L[l];
         e.tmap_aw = c.tm_in_win; e.tmap_bh = c.tm_wf_half;
         fwd_conv_args(net, l, n, &e.a);
+        e.a.ksteps_last = (c.cin % 64) ? ((c.cin % 64) + 15) / 16 : 0;   // input channels past cin are zero padding
         e.a.win_rows = conv_window_rows(e.a.off, e.a.taps); e.a.halo = (e.a.win_rows - 128) / 2;
         chain_set_tiles(e, n);
         if (l > 0) {
