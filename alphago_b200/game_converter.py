@@ -89,19 +89,23 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
                 out[s:s + m] = planes.cpu().numpy()
         return out
 
-    def sgfs_to_hdf5(self, sgf_files, hdf5_file, bd_size=19, ignore_errors=True, verbose=False):
+    def sgfs_to_hdf5(self, sgf_files, hdf5_file, bd_size=19, ignore_errors=True, verbose=False, container="hdf5"):
         """Convert all files in the iterable sgf_files into one dataset file (game_converter.py:42-140).
 
         The resulting file has `states` (n_data, n_features, size, size), `actions` (n_data, 2) and the group
         `file_offsets` mapping file names ('/' -> ':') to [index, length]; it is written under a hidden temporary name
-        and renamed on success.  With h5py installed it is the reference's HDF5 (LZF-compressed chunks of 64 / 1024
-        rows); without it the same three members are written as an .npz archive under the given name, the planes
-        bit-packed (supervised_policy_trainer.open_dataset reads either)."""
+        and renamed on success.  container="hdf5" (default) is the reference's HDF5 layout -- extendable datasets in
+        compressed chunks of 64 / 1024 rows -- written through h5py where it is importable, else through
+        hdf5_lite's writer; each encoded block is appended as it comes off the device, so memory holds one block, not
+        the dataset.  container="npz" writes the same three members as an .npz archive with the planes bit-packed
+        (smaller and faster to write; supervised_policy_trainer.open_dataset reads either)."""
+        if container not in ("hdf5", "npz"):
+            raise ValueError("container must be 'hdf5' or 'npz'")
         tmp_file = os.path.join(os.path.dirname(hdf5_file), ".tmp." + os.path.basename(hdf5_file))
         names, offsets = [], []
         pending, all_actions, blocks = [], [], []
-        bits = not _have_h5py()   # the archive fallback stores the one-hot planes bit-packed
         next_idx = 0
+        sink = _Hdf5Sink(tmp_file, self.n_features, bd_size) if container == "hdf5" else None
         try:
             for file_name in sgf_files:
                 if verbose:
@@ -130,19 +134,30 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
                 elif verbose:
                     print("\t-no usable data-")
                 if len(pending) >= self.batch:
-                    blocks.append(self.encode_packed_positions(pending, bd_size, bits=bits))
+                    block = self.encode_packed_positions(pending, bd_size, bits=True)   # bit-packed over the bus either way
                     pending = []
+                    if sink is not None:
+                        sink.append_states(block)
+                    else:
+                        blocks.append(block)
             if pending:
-                blocks.append(self.encode_packed_positions(pending, bd_size, bits=bits))
+                block = self.encode_packed_positions(pending, bd_size, bits=True)
+                if sink is not None:
+                    sink.append_states(block)
+                else:
+                    blocks.append(block)
             shape = (next_idx, self.n_features, bd_size, bd_size)
-            if blocks:
-                states = np.concatenate(blocks)
-            else:
-                states = np.zeros((0, (shape[1] * bd_size * bd_size + 7) // 8) if bits else shape, np.uint8)
             acts = np.asarray(all_actions, np.uint8).reshape(-1, 2)
-            _write_dataset(tmp_file, states, shape, acts, names, np.asarray(offsets, np.int64).reshape(-1, 2))
+            offs = np.asarray(offsets, np.int64).reshape(-1, 2)
+            if sink is not None:
+                sink.finish(acts, names, offs)
+            else:
+                states = np.concatenate(blocks) if blocks else np.zeros((0, (shape[1] * bd_size * bd_size + 7) // 8), np.uint8)
+                _write_archive(tmp_file, states, shape, acts, names, offs)
         except Exception:
             print("sgfs_to_hdf5 failed")
+            if sink is not None:
+                sink.abandon()
             if os.path.exists(tmp_file):
                 os.remove(tmp_file)
             raise
@@ -151,29 +166,58 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
         os.rename(tmp_file, hdf5_file)
 
 
-def _have_h5py():
-    try:
-        import h5py  # noqa: F401
-        return True
-    except ImportError:
-        return False
+class _Hdf5Sink(object):
+    """the dataset file while it grows: the reference's three members (game_converter.py:71-88), filled block by block
+    through h5py's resize-and-assign calls -- h5py itself where importable, hdf5_lite's writer (same calls) otherwise.
+    Blocks are unpacked, deflated and written by one background thread (zlib and numpy release the interpreter lock),
+    so the file keeps up while the caller replays the next games."""
+
+    def __init__(self, path, n_features, size):
+        from concurrent.futures import ThreadPoolExecutor
+        from . import hdf5_lite
+        self.row = (n_features, size, size)
+        self.f = hdf5_lite.open_file(path, "w")
+        self.states = self.f.create_dataset("states", shape=(0,) + self.row, dtype=np.uint8, maxshape=(None,) + self.row,
+                                            chunks=(64,) + self.row, compression="lzf")
+        self.n = 0
+        self.worker = ThreadPoolExecutor(max_workers=1)   # one thread: blocks stay in order
+        self.jobs = []
+
+    def _write(self, bits):
+        m = len(bits)
+        planes = np.unpackbits(bits, axis=1)[:, :int(np.prod(self.row))].reshape((m,) + self.row)
+        self.states.resize(self.n + m, axis=0)
+        self.states[self.n:self.n + m] = planes
+        self.n += m
+
+    def append_states(self, bits):
+        """rows of bit-packed planes (np.packbits order) as they come back from the device"""
+        while len(self.jobs) > 2:            # bounded backlog: at most three blocks in memory
+            self.jobs.pop(0).result()
+        self.jobs.append(self.worker.submit(self._write, bits))
+
+    def finish(self, actions, names, offsets):
+        for j in self.jobs:
+            j.result()                        # re-raises what the writer thread hit
+        self.worker.shutdown()
+        assert len(actions) == self.n
+        self.f.create_dataset("actions", data=actions, dtype=np.uint8, maxshape=(None, 2), chunks=(1024, 2), compression="lzf")
+        g = self.f.require_group("file_offsets")
+        for name, off in zip(names, offsets):
+            g[name] = [int(off[0]), int(off[1])]
+        self.f.close()
+
+    def abandon(self):
+        self.worker.shutdown(wait=True, cancel_futures=True)
+        try:
+            self.f.close()
+        except Exception:
+            pass
 
 
-def _write_dataset(path, states, shape, actions, names, offsets):
-    """states: uint8 planes of `shape` (h5py present) or their bit-packed rows (archive fallback)"""
-    if _have_h5py():
-        import h5py
-        n_feat, size = shape[1], shape[2]
-        with h5py.File(path, "w") as f:
-            f.create_dataset("states", data=states, dtype=np.uint8, maxshape=(None, n_feat, size, size),
-                             chunks=(64, n_feat, size, size), compression="lzf")
-            f.create_dataset("actions", data=actions, dtype=np.uint8, maxshape=(None, 2), chunks=(1024, 2), compression="lzf")
-            g = f.require_group("file_offsets")
-            for name, off in zip(names, offsets):
-                g[name] = [int(off[0]), int(off[1])]
-        return
-    # an .npz archive (np.load reads it), members written one by one with the fastest deflate level; the planes are stored
-    # bit-packed (`states_bits` + `states_shape`; supervised_policy_trainer.open_dataset unpacks them)
+def _write_archive(path, states, shape, actions, names, offsets):
+    """an .npz archive (np.load reads it), members written one by one with the fastest deflate level; the planes are stored
+    bit-packed (`states_bits` + `states_shape`; supervised_policy_trainer.open_dataset unpacks them)"""
     import zipfile
     members = {"states_bits": states, "states_shape": np.asarray(shape, np.int64), "actions": actions,
                "file_offsets_names": np.asarray(names), "file_offsets": offsets}
@@ -198,6 +242,8 @@ def run_game_converter(cmd_line_args=None):
     parser.add_argument("--directory", "-d", help="Directory containing SGF files to process. if not present, expects files from stdin", default=None)
     parser.add_argument("--size", "-s", help="Size of the game board. SGFs not matching this are discarded with a warning", type=int, default=19)
     parser.add_argument("--verbose", "-v", help="Turn on verbose mode", default=False, action="store_true")
+    parser.add_argument("--container", help="File format of --outfile: hdf5 (the reference's layout; default) or npz (bit-packed archive, "
+                        "faster to write; the trainer reads both)", choices=["hdf5", "npz"], default="hdf5")   # not in the reference
     args = parser.parse_args(cmd_line_args)
 
     if args.features.lower() == "all":
@@ -228,7 +274,7 @@ def run_game_converter(cmd_line_args=None):
         files = _walk_all_sgfs(args.directory) if args.recurse else _list_sgfs(args.directory)
     else:
         files = (f.strip() for f in sys.stdin if _is_sgf(f))
-    converter.sgfs_to_hdf5(files, args.outfile, bd_size=args.size, verbose=args.verbose)
+    converter.sgfs_to_hdf5(files, args.outfile, bd_size=args.size, verbose=args.verbose, container=args.container)
 
 
 if __name__ == "__main__":

@@ -1,18 +1,31 @@
-"""Minimal read-only HDF5 for the reference's dataset files, for images without h5py.
+"""Minimal HDF5 for the reference's dataset and weight files, for images without h5py: a reader and a writer.
 
-Covers what `game_converter.py:67-88` / Keras 1.0 `save_weights` produce with h5py 2.x defaults (HDF5 1.8 "earliest"
+Reader: what `game_converter.py:67-88` / Keras 1.0 `save_weights` produce with h5py 2.x defaults (HDF5 1.8 "earliest"
 format): superblock v0/v1, symbol-table groups (v1 B-tree + local heap), v1 object headers with continuation
 blocks, fixed-point / IEEE-float / fixed-length-string datatypes, contiguous, compact and chunked layouts (v1 chunk
 B-tree) with the gzip (1), shuffle (2) and LZF (32000) filters, and v1-v3 attribute messages.  That is the on-disk
 contract of the SL trainer (`states` uint8 (N,F,19,19) LZF-chunked, `actions` uint8 (N,2), group `file_offsets`;
-supervised_policy_trainer.py:128-129).  `open_file()` prefers h5py when it is importable.
+supervised_policy_trainer.py:128-129).
+
+Writer (`File(path, "w")`, the subset of h5py's API that game_converter.py:67-88,122-125 and Keras 1.0's save_weights
+use: create_dataset / create_group / require_group / group[name] = array / .attrs[name] = value): the same "earliest"
+format, laid out the way libhdf5 lays out the reference's own fixture file (superblock v0, v1 object headers, one local
+heap + v1 B-tree of symbol nodes per group, contiguous datasets, chunked datasets behind a v1 chunk B-tree).  Chunks are
+compressed with the deflate filter (id 1), which every libhdf5 build carries; the reference's converter asks for LZF,
+a filter that ships with h5py only -- same datasets, shapes and types either way.  Data goes to the file as it is
+handed over, metadata at close().  No libhdf5 is available in this image to cross-check the files: the writer is
+checked by this module's reader (which is itself pinned on the reference's real file) in tests/test_hdf5_lite.py.
+
+`open_file()` prefers h5py when it is importable.
 """
+import os
 import struct
 import zlib
 
 import numpy as np
 
 UNDEF = 0xFFFFFFFFFFFFFFFF
+MAGIC = b"\x89HDF\r\n\x1a\n"
 
 
 def lzf_decompress(src, out_len):
@@ -219,6 +232,8 @@ class Dataset(object):
         """rows [lo, hi) along the first axis"""
         if self.layout != 2:
             count = int(np.prod(self.shape)) if self.shape else 1
+            if count == 0 or self.data_addr == UNDEF:   # nothing allocated: empty, or never written (fill value)
+                return np.zeros(self.shape, self.dtype)[lo:hi]
             full = np.frombuffer(self.f.b, self.dtype, count=count, offset=self.data_addr).reshape(self.shape)
             return full[lo:hi]
         out = np.zeros((hi - lo,) + self.shape[1:], self.dtype)
@@ -314,13 +329,11 @@ class Group(object):
         return node
 
 
-class File(Group):
-    def __init__(self, path, mode="r"):
-        if mode != "r":
-            raise NotImplementedError("hdf5_lite is read-only")
+class _ReadFile(Group):
+    def __init__(self, path):
         with open(path, "rb") as fh:
             buf = memoryview(fh.read())
-        if bytes(buf[:8]) != b"\x89HDF\r\n\x1a\n":
+        if bytes(buf[:8]) != MAGIC:
             raise ValueError("%s is not an HDF5 file" % path)
         ver = buf[8]
         if ver not in (0, 1) or buf[13] != 8 or buf[14] != 8:
@@ -340,8 +353,434 @@ class File(Group):
         return False
 
 
+# ------------------------------------------------------------------------------------------------ writer
+GROUP_LEAF_K, GROUP_NODE_K, CHUNK_NODE_K = 4, 16, 32   # libhdf5 defaults (the superblock v0 stores the first two)
+
+
+def _pad8(b):
+    return b + b"\0" * (-len(b) % 8)
+
+
+def _enc_datatype(dt):
+    dt = np.dtype(dt)
+    if dt.kind in "ui" and dt.itemsize in (1, 2, 4, 8) and dt.byteorder in "<|=":
+        return struct.pack("<BBBBIHH", 0x10, 0x08 if dt.kind == "i" else 0, 0, 0, dt.itemsize, 0, 8 * dt.itemsize)
+    if dt.kind == "f" and dt.itemsize in (4, 8) and dt.byteorder in "<=":
+        if dt.itemsize == 4:
+            return struct.pack("<BBBBIHHBBBBI", 0x11, 0x20, 31, 0, 4, 0, 32, 23, 8, 0, 23, 127)
+        return struct.pack("<BBBBIHHBBBBI", 0x11, 0x20, 63, 0, 8, 0, 64, 52, 11, 0, 52, 1023)
+    if dt.kind == "S":
+        return struct.pack("<BBBBI", 0x13, 0x01, 0, 0, max(dt.itemsize, 1))   # null-padded ASCII, as h5py writes numpy S arrays
+    raise NotImplementedError("cannot write dtype %r" % dt)
+
+
+def _enc_dataspace(shape, maxshape=None):
+    maxshape = shape if maxshape is None else maxshape
+    out = struct.pack("<BBBBI", 1, len(shape), 1 if shape else 0, 0, 0)
+    out += b"".join(struct.pack("<Q", int(d)) for d in shape)
+    if shape:
+        out += b"".join(struct.pack("<Q", UNDEF if m is None else int(m)) for m in maxshape)
+    return out
+
+
+def _as_array(value):
+    if isinstance(value, str):
+        value = value.encode("utf8")
+    arr = np.asarray(value)
+    if arr.dtype.kind == "U":
+        arr = np.char.encode(arr, "utf8")
+    if arr.dtype.kind == "O":
+        raise NotImplementedError("variable-length data")
+    if arr.dtype == np.bool_:
+        arr = arr.astype(np.uint8)
+    return arr
+
+
+class _WAttrs(dict):
+    def __setitem__(self, name, value):
+        dict.__setitem__(self, name, _as_array(value))
+
+    def messages(self):
+        out = []
+        for name, arr in self.items():
+            nm, dt, sp = name.encode("utf8") + b"\0", _enc_datatype(arr.dtype), _enc_dataspace(arr.shape)
+            body = struct.pack("<BBHHH", 1, 0, len(nm), len(dt), len(sp)) + _pad8(nm) + _pad8(dt) + _pad8(sp) + np.ascontiguousarray(arr).tobytes()
+            if len(body) > 0xFFF0:
+                raise NotImplementedError("attribute %r is too large for an object header message" % name)
+            out.append((0x000C, 0, body))
+        return out
+
+
+class _WNode(object):
+    def __init__(self, f, name):
+        self.f, self.name, self.attrs = f, name, _WAttrs()
+
+
+class WDataset(_WNode):
+    """Contiguous datasets and datasets chunked in several dimensions are written when created (`data` is the whole
+    array).  Datasets chunked along the first axis only -- the converter's `states` and `actions` -- can also grow the
+    way game_converter.py:100-105 fills them: `resize()` and then `ds[i] = row` / `ds[lo:hi] = rows` in ascending order;
+    every completed chunk is deflated and appended to the file at once, so memory holds one chunk, not the dataset."""
+
+    def __init__(self, f, name, shape, dtype, data, maxshape, chunks, compression, compression_opts):
+        _WNode.__init__(self, f, name)
+        self.shape, self.dtype = tuple(int(v) for v in shape), np.dtype(dtype)
+        _enc_datatype(self.dtype)
+        self.maxshape = tuple(maxshape) if maxshape is not None else None
+        if self.maxshape is not None and len(self.maxshape) != len(self.shape):
+            raise ValueError("maxshape must have the rank of the data")
+        if chunks is None and (compression or (self.maxshape and any(m is None or m > s for m, s in zip(self.maxshape, self.shape)))):
+            chunks = tuple(max(1, s) for s in self.shape)
+        self.chunks = tuple(int(c) for c in chunks) if chunks else None
+        if self.chunks and (not self.shape or len(self.chunks) != len(self.shape) or min(self.chunks) < 1):
+            raise ValueError("bad chunk shape %r for data of shape %r" % (chunks, self.shape))
+        if compression not in (None, False, "gzip", "lzf", "deflate"):
+            raise NotImplementedError("compression %r" % (compression,))
+        # "lzf" is accepted for the reference's call (game_converter.py:73-74) and stored as deflate level 1 (module docstring)
+        self.level = None if not compression else (1 if compression == "lzf" else int(compression_opts) if compression_opts is not None else 4)
+        self.index, self._next, self._pending, self._npending = [], 0, [], 0
+        self._rowwise = bool(self.chunks) and self.chunks[1:] == self.shape[1:]
+        if self.chunks is None:
+            arr = np.zeros(self.shape, self.dtype) if data is None else data
+            self.addr = f._append(arr.tobytes()) if arr.size else UNDEF
+            self.nbytes = arr.nbytes
+        elif data is not None:
+            if self._rowwise:
+                self[0:self.shape[0]] = data
+            else:
+                self._write_chunks(data)
+        elif not self._rowwise and int(np.prod(self.shape)):
+            self._write_chunks(np.zeros(self.shape, self.dtype))
+
+    def __len__(self):
+        return self.shape[0]
+
+    def resize(self, size, axis=None):
+        if not self._rowwise or self.maxshape is None:
+            raise TypeError("only datasets chunked along their first axis, created with maxshape, can be resized")
+        size = (int(size),) + self.shape[1:] if axis is not None or np.ndim(size) == 0 else tuple(int(v) for v in size)
+        if axis not in (None, 0) or size[1:] != self.shape[1:]:
+            raise NotImplementedError("resize along the first axis only")
+        if size[0] < self._next or (self.maxshape[0] is not None and size[0] > self.maxshape[0]):
+            raise ValueError("cannot resize to %d rows (%d already written)" % (size[0], self._next))
+        self.shape = size
+
+    def __setitem__(self, key, value):
+        self.f._check_open()
+        if not self._rowwise:
+            raise NotImplementedError("this dataset was written when it was created")
+        if isinstance(key, (int, np.integer)):
+            lo, hi = int(key), int(key) + 1
+        elif isinstance(key, slice) and key.step in (None, 1):
+            lo, hi, _ = key.indices(self.shape[0])
+        elif key is Ellipsis:
+            lo, hi = 0, self.shape[0]
+        else:
+            raise NotImplementedError("rows are assigned by index or by contiguous slice")
+        if not 0 <= lo <= hi <= self.shape[0]:
+            raise IndexError("rows %d:%d are outside the dataset (%d rows; resize first)" % (lo, hi, self.shape[0]))
+        if hi == lo:
+            return
+        if lo != self._next:
+            raise NotImplementedError("rows must be written in ascending order without gaps (next row: %d, got %d)" % (self._next, lo))
+        rows = np.broadcast_to(np.asarray(value, self.dtype).reshape((-1,) + self.shape[1:]) if np.ndim(value) else np.asarray(value, self.dtype),
+                               (hi - lo,) + self.shape[1:])
+        self._pending.append(rows)
+        self._npending += hi - lo
+        self._next = hi
+        if self._npending >= self.chunks[0]:
+            self._flush(False)
+
+    def _pack(self, raw):
+        return zlib.compress(raw, self.level) if self.level is not None else raw   # zlib releases the GIL
+
+    def _flush(self, final):
+        """deflate and append every complete chunk of the pending rows (and, at the end, the partial one, zero-padded)"""
+        if not self._npending:
+            return
+        from concurrent.futures import ThreadPoolExecutor
+        c0 = self.chunks[0]
+        rows = self._pending[0] if len(self._pending) == 1 else np.concatenate(self._pending)
+        first = self._next - self._npending   # a multiple of c0: complete chunks leave at once
+        whole = self._npending // c0
+        pieces = [rows[i * c0:(i + 1) * c0] for i in range(whole)]
+        rest = rows[whole * c0:]
+        if final and len(rest):
+            pad = np.zeros((c0,) + self.shape[1:], self.dtype)
+            pad[:len(rest)] = rest
+            pieces.append(pad)
+            rest = rest[:0]
+        tail = (0,) * (len(self.shape) - 1)
+        with ThreadPoolExecutor(max_workers=max(1, min(16, os.cpu_count() or 1, len(pieces)))) as pool:
+            for i, blob in enumerate(pool.map(lambda p: self._pack(np.ascontiguousarray(p).tobytes()), pieces)):
+                self.index.append(((first + i * c0,) + tail, self.f._append(blob), len(blob)))
+        self._pending, self._npending = ([np.array(rest)], len(rest)) if len(rest) else ([], 0)
+
+    def _write_chunks(self, arr):
+        from concurrent.futures import ThreadPoolExecutor
+        grids = [range(0, s, c) for s, c in zip(self.shape, self.chunks)]
+        offs = [()]
+        for g in grids:
+            offs = [o + (v,) for o in offs for v in g]   # row-major = the B-tree's key order
+        full = tuple(self.chunks)
+
+        def cut(o):
+            sl = tuple(slice(v, min(v + c, s)) for v, c, s in zip(o, full, self.shape))
+            piece = arr[sl]
+            if piece.shape != full:   # edge chunks are stored whole
+                whole = np.zeros(full, arr.dtype)
+                whole[tuple(slice(0, n) for n in piece.shape)] = piece
+                piece = whole
+            return self._pack(np.ascontiguousarray(piece).tobytes())
+
+        with ThreadPoolExecutor(max_workers=min(16, (os.cpu_count() or 1))) as pool:
+            for o, blob in zip(offs, pool.map(cut, offs)):
+                self.index.append((o, self.f._append(blob), len(blob)))
+
+    def _chunk_btree(self):
+        """v1 B-tree (node type 1) over self.index; returns the root's address (UNDEF without chunks)"""
+        if not self.index:
+            return UNDEF
+        nd = len(self.shape) + 1
+        key = lambda size, offs, tail=0: struct.pack("<II", size, 0) + b"".join(struct.pack("<Q", v) for v in offs) + struct.pack("<Q", tail)
+        # the key behind the last chunk: one chunk further in every dimension (what libhdf5 leaves there)
+        end_key = key(0, [o + c for o, c in zip(self.index[-1][0], self.chunks)], self.dtype.itemsize)
+        # level 0 entries: (first key, child address); one node holds up to 2K children
+        entries = [(key(n, o), a) for o, a, n in self.index]
+        level = 0
+        node_size = 24 + (2 * CHUNK_NODE_K) * 8 + (2 * CHUNK_NODE_K + 1) * (8 + 8 * nd)
+        while True:
+            groups = [entries[i:i + 2 * CHUNK_NODE_K] for i in range(0, len(entries), 2 * CHUNK_NODE_K)]
+            addrs = [self.f._reserve(node_size) for _ in groups]
+            nxt = []
+            for gi, grp in enumerate(groups):
+                body = b"TREE" + struct.pack("<BBH", 1, level, len(grp))
+                body += struct.pack("<QQ", addrs[gi - 1] if gi > 0 else UNDEF, addrs[gi + 1] if gi + 1 < len(groups) else UNDEF)
+                for k, a in grp:
+                    body += k + struct.pack("<Q", a)
+                body += groups[gi + 1][0][0] if gi + 1 < len(groups) else end_key
+                self.f._fill(addrs[gi], body.ljust(node_size, b"\0"))
+                nxt.append((grp[0][0], addrs[gi]))
+            if len(groups) == 1:
+                return addrs[0]
+            entries, level = nxt, level + 1
+
+    def _emit(self):
+        self._flush(True)
+        esize = self.dtype.itemsize
+        msgs = [(0x0001, 0, _enc_dataspace(self.shape, self.maxshape)), (0x0003, 1, _enc_datatype(self.dtype))]
+        if self.chunks is None:
+            msgs.append((0x0005, 1, bytes([2, 2, 2, 1]) + struct.pack("<I", 0)))   # allocate late, fill if set, default fill value
+            msgs.append((0x0008, 1, struct.pack("<BBQQ", 3, 1, self.addr, self.nbytes)))
+        else:
+            msgs.append((0x0005, 1, bytes([2, 3, 0, 1]) + struct.pack("<I", 0)))   # allocate incrementally
+            if self.level is not None:
+                msgs.append((0x000B, 1, struct.pack("<BB6x", 1, 1) + struct.pack("<HHHH", 1, 8, 1, 1) + b"deflate\0" + struct.pack("<II", self.level, 0)))
+            msgs.append((0x0008, 1, struct.pack("<BBBQ", 3, 2, len(self.shape) + 1, self._chunk_btree()) +
+                         b"".join(struct.pack("<I", c) for c in self.chunks) + struct.pack("<I", esize)))
+        msgs.append((0x0012, 0, struct.pack("<B3xI", 1, self.f._mtime)))
+        return self.f._object_header(msgs + self.attrs.messages()), None
+
+
+class WGroup(_WNode):
+    def __init__(self, f, name):
+        _WNode.__init__(self, f, name)
+        self._links = {}
+
+    def _split(self, name, create):
+        parts = [p for p in name.split("/") if p]
+        if not parts:
+            raise ValueError("empty name")
+        node = self
+        for p in parts[:-1]:
+            if p not in node._links:
+                if not create:
+                    raise KeyError(name)
+                node._links[p] = WGroup(self.f, p)
+            node = node._links[p]
+            if not isinstance(node, WGroup):
+                raise ValueError("%s is not a group" % p)
+        return node, parts[-1]
+
+    def create_group(self, name):
+        node, leaf = self._split(name, True)
+        if leaf in node._links:
+            raise ValueError("unable to create group (name already exists): %s" % name)
+        node._links[leaf] = WGroup(self.f, leaf)
+        return node._links[leaf]
+
+    def require_group(self, name):
+        node, leaf = self._split(name, True)
+        if leaf not in node._links:
+            node._links[leaf] = WGroup(self.f, leaf)
+        if not isinstance(node._links[leaf], WGroup):
+            raise TypeError("incompatible object (dataset) already exists: %s" % name)
+        return node._links[leaf]
+
+    def create_dataset(self, name, shape=None, dtype=None, data=None, maxshape=None, chunks=None, compression=None,
+                       compression_opts=None, **_ignored):
+        if data is not None:
+            data = _as_array(data)
+            if dtype is not None:
+                data = data.astype(dtype, copy=False)
+            if shape is not None:
+                data = data.reshape(shape)
+            data = np.require(data, requirements="C")   # (ascontiguousarray would turn a scalar into a vector)
+            shape, dtype = data.shape, data.dtype
+        elif shape is None:
+            raise TypeError("one of data or shape must be given")
+        else:
+            shape, dtype = tuple(np.atleast_1d(shape)) if np.ndim(shape) else (int(shape),), np.dtype(dtype or np.float32)
+        node, leaf = self._split(name, True)
+        if leaf in node._links:
+            raise ValueError("unable to create dataset (name already exists): %s" % name)
+        self.f._check_open()
+        node._links[leaf] = WDataset(self.f, leaf, shape, dtype, data, maxshape, chunks if chunks is not True else None, compression, compression_opts)
+        return node._links[leaf]
+
+    def require_dataset(self, name, shape, dtype, exact=False, **kwds):
+        """the dataset of that name, created if it is not there yet (game_converter.py:71-86)"""
+        if name in self:
+            ds = self[name]
+            if not isinstance(ds, WDataset) or ds.shape != tuple(shape):
+                raise TypeError("shapes do not match (existing %r vs new %r)" % (getattr(ds, "shape", None), tuple(shape)))
+            return ds
+        return self.create_dataset(name, shape=shape, dtype=dtype, **kwds)
+
+    def __setitem__(self, name, value):
+        self.create_dataset(name, data=value)
+
+    def __getitem__(self, name):
+        node, leaf = self._split(name, False)
+        return node._links[leaf]
+
+    def __contains__(self, name):
+        try:
+            self[name]
+            return True
+        except KeyError:
+            return False
+
+    def keys(self):
+        return sorted(self._links)
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def _emit(self):
+        """children first, then this group's heap, symbol nodes, B-tree and object header; returns (header, (btree, heap))"""
+        f = self.f
+        names = sorted(self._links, key=lambda n: n.encode("utf8"))   # strcmp order
+        heap, offs = bytearray(8), {}
+        for n in names:
+            offs[n] = len(heap)
+            heap += _pad8(n.encode("utf8") + b"\0")
+        symbols = []
+        for n in names:
+            child = self._links[n]
+            addr, cache = child._emit()
+            scratch = struct.pack("<QQ", *cache) if cache else bytes(16)
+            symbols.append((offs[n], struct.pack("<QQII", offs[n], addr, 1 if cache else 0, 0) + scratch))
+        heap_addr = f._append(b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap), 1, f._end() + 32) + bytes(heap))   # 1 = no free block
+        per = 2 * GROUP_LEAF_K
+        snod_size = 8 + per * 40
+        entries = []   # (heap offset of the largest name below, child address)
+        for i in range(0, len(symbols), per):
+            grp = symbols[i:i + per]
+            body = b"SNOD" + struct.pack("<BBH", 1, 0, len(grp)) + b"".join(e for _, e in grp)
+            entries.append((grp[-1][0], f._append(body.ljust(snod_size, b"\0"))))
+        level, node_size = 0, 24 + (2 * GROUP_NODE_K) * 8 + (2 * GROUP_NODE_K + 1) * 8
+        while True:
+            groups = [entries[i:i + 2 * GROUP_NODE_K] for i in range(0, len(entries), 2 * GROUP_NODE_K)] or [[]]   # an empty group: a leaf without entries
+            addrs = [f._reserve(node_size) for _ in groups]
+            nxt = []
+            for gi, grp in enumerate(groups):
+                body = b"TREE" + struct.pack("<BBH", 0, level, len(grp))
+                body += struct.pack("<QQ", addrs[gi - 1] if gi > 0 else UNDEF, addrs[gi + 1] if gi + 1 < len(groups) else UNDEF)
+                body += struct.pack("<Q", groups[gi - 1][-1][0] if gi > 0 else 0)   # left key: largest name before this node
+                for k, a in grp:
+                    body += struct.pack("<QQ", a, k)
+                f._fill(addrs[gi], body.ljust(node_size, b"\0"))
+                nxt.append((grp[-1][0] if grp else 0, addrs[gi]))
+            if len(groups) == 1:
+                break
+            entries, level = nxt, level + 1
+        btree = addrs[0]
+        header = f._object_header([(0x0011, 0, struct.pack("<QQ", btree, heap_addr))] + self.attrs.messages())
+        return header, (btree, heap_addr)
+
+
+class _WriteFile(WGroup):
+    def __init__(self, path):
+        import time
+        WGroup.__init__(self, self, "/")
+        self._fh = open(path, "wb")
+        self._fh.write(bytes(96))   # the superblock goes in at close()
+        self._pos = 96
+        self._mtime = int(time.time()) & 0xFFFFFFFF
+        self._closed = False
+
+    # ---- file space: append-only, 8-byte aligned
+    def _check_open(self):
+        if self._closed:
+            raise ValueError("file is closed")
+
+    def _end(self):
+        return self._pos
+
+    def _append(self, blob):
+        addr = self._pos
+        blob = _pad8(bytes(blob))
+        self._fh.write(blob)
+        self._pos += len(blob)
+        return addr
+
+    def _reserve(self, size):
+        return self._append(bytes(size))
+
+    def _fill(self, addr, blob):
+        self._fh.seek(addr)
+        self._fh.write(blob)
+        self._fh.seek(self._pos)
+
+    def _object_header(self, msgs):
+        body = b""
+        for mtype, flags, data in msgs:
+            data = _pad8(data)
+            body += struct.pack("<HHB3x", mtype, len(data), flags) + data
+        return self._append(struct.pack("<BBHII4x", 1, 0, len(msgs), 1, len(body)) + body)
+
+    def close(self):
+        if self._closed:
+            return
+        root, (btree, heap) = self._emit()
+        sb = MAGIC + bytes([0, 0, 0, 0, 0, 8, 8, 0]) + struct.pack("<HHI", GROUP_LEAF_K, GROUP_NODE_K, 0)
+        sb += struct.pack("<QQQQ", 0, UNDEF, self._pos, UNDEF)
+        sb += struct.pack("<QQII", 0, root, 1, 0) + struct.pack("<QQ", btree, heap)
+        assert len(sb) == 96
+        self._fill(0, sb)
+        self._fh.close()
+        self._closed = True
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+        return False
+
+
+def File(path, mode="r"):
+    """reader (mode "r") or writer (mode "w") for the subset of HDF5 described in the module docstring"""
+    if mode == "r":
+        return _ReadFile(path)
+    if mode == "w":
+        return _WriteFile(path)
+    raise NotImplementedError("hdf5_lite opens files with mode 'r' or 'w', not %r" % mode)
+
+
 def open_file(path, mode="r"):
-    """h5py.File when h5py is importable, else the read-only reader above"""
+    """h5py.File when h5py is importable, else this module's reader / writer"""
     try:
         import h5py
         return h5py.File(path, mode)

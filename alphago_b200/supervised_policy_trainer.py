@@ -38,7 +38,7 @@ class MetadataWriter(object):
 
 def open_dataset(path):
     """(states, actions) array-likes from an HDF5 file in the converter's layout (game_converter.py:71-88) or an .npz
-    archive with the same two members (what game_converter writes where h5py is missing, under whatever name it was
+    archive with the same two members (what game_converter writes with container="npz", under whatever name it was
     given: the file's first bytes decide, not its suffix)"""
     with open(path, "rb") as f:
         magic = f.read(4)

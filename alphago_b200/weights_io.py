@@ -1,26 +1,29 @@
 """Weight files for `SequentialModel.save_weights / load_weights` (policy.py:165-167,188-190;
 ModelCheckpoint "weights.{epoch:05d}.hdf5", supervised_policy_trainer.py:161-162).
 
-With h5py importable the file is Keras 1.0's HDF5 layout (root attr `layer_names`; one group per
-layer with attr `weight_names` and one dataset per array), so files move between this package and
-the reference.  Without h5py (it is not in this image) the SAME path holds a NumPy .npz archive with
-the same names; `load` sniffs the magic bytes, so either kind loads wherever it can be read.
+The file is HDF5 in the layout of Keras 1.0's `save_weights`, so files move between this package and the reference:
+root attribute `layer_names` (every layer of the Sequential, in order, the weightless Flatten / Activation included,
+because Keras 1.0's loader wants one entry per layer), one group per layer with the attribute `weight_names`, and one
+float32 dataset per array (`<layer>_W`, `<layer>_b`).  It is written through h5py where that is importable and through
+`hdf5_lite`'s writer otherwise (h5py is not in this image).  `load` goes by names, not by position, so files that hold
+only the weight-owning layers load too; so do the `.npz` archives earlier versions of this package wrote under the same
+file names (the first bytes decide, not the suffix).
 """
-import io
 import zipfile
 
 import numpy as np
 
-HDF5_MAGIC = b"\x89HDF\r\n\x1a\n"
+from . import hdf5_lite
+
+HDF5_MAGIC = hdf5_lite.MAGIC
 
 
-def _layer_names(layers):
-    """[(layer name, [weight names])] for the layers that own weights, in Keras order"""
+def _layer_table(layers):
+    """[(layer name, [weight names])] for every layer, in Keras order (weightless layers have an empty list)"""
     out = []
     for l in layers:
-        if l["class_name"] in ("Convolution2D", "Dense"):
-            n = l["config"]["name"]
-            out.append((n, [n + "_W", n + "_b"]))
+        n = l["config"]["name"]
+        out.append((n, [n + "_W", n + "_b"] if l["class_name"] in ("Convolution2D", "Dense") else []))
     return out
 
 
@@ -33,41 +36,32 @@ def have_h5py():
 
 
 def save(path, layers, weights):
-    names = _layer_names(layers)
-    assert len(weights) == 2 * len(names)
-    if have_h5py():
-        import h5py
-        with h5py.File(path, "w") as f:
-            f.attrs["layer_names"] = [n.encode("utf8") for n, _ in names]
-            for i, (n, wn) in enumerate(names):
-                g = f.create_group(n)
-                g.attrs["weight_names"] = [w.encode("utf8") for w in wn]
-                for j, w in enumerate(wn):
-                    g.create_dataset(w, data=np.asarray(weights[2 * i + j], np.float32))
-        return
-    arrays = {}
-    for i, (n, wn) in enumerate(names):
-        for j, w in enumerate(wn):
-            arrays[n + "/" + w] = np.asarray(weights[2 * i + j], np.float32)
-    buf = io.BytesIO()
-    np.savez(buf, **arrays)
-    with open(path, "wb") as f:
-        f.write(buf.getvalue())
+    table = _layer_table(layers)
+    assert len(weights) == sum(len(wn) for _, wn in table)
+    k = 0
+    with hdf5_lite.open_file(path, "w") as f:
+        f.attrs["layer_names"] = [n.encode("utf8") for n, _ in table]
+        for n, wn in table:
+            g = f.create_group(n)
+            g.attrs["weight_names"] = [w.encode("utf8") for w in wn]
+            for w in wn:
+                g.create_dataset(w, data=np.asarray(weights[k], np.float32))
+                k += 1
 
 
 def load(path, layers):
-    names = _layer_names(layers)
+    names = [(n, wn) for n, wn in _layer_table(layers) if wn]
     with open(path, "rb") as f:
         magic = f.read(8)
     out = []
     if magic == HDF5_MAGIC:
-        if not have_h5py():
-            raise ImportError("%s is an HDF5 file and h5py is not installed" % path)
-        import h5py
-        with h5py.File(path, "r") as f:
+        f = hdf5_lite.open_file(path, "r")
+        try:
             for n, wn in names:
                 for w in wn:
-                    out.append(np.asarray(f[n][w], np.float32))
+                    out.append(np.asarray(f[n][w][()], np.float32))
+        finally:
+            f.close()
         return out
     if not zipfile.is_zipfile(path):
         raise ValueError("%s is neither an HDF5 nor an .npz weight file" % path)

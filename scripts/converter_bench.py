@@ -38,8 +38,12 @@ conv.encode_packed_positions(packed, 19, bits=True)
 t_bits = time.time() - t0
 with tempfile.TemporaryDirectory() as d:
     t0 = time.time()
-    conv.sgfs_to_hdf5(files, os.path.join(d, "out.h5"), bd_size=19)
+    conv.sgfs_to_hdf5(files, os.path.join(d, "out.h5"), bd_size=19)   # the reference's HDF5 layout (default)
     t_all = time.time() - t0
+    hdf5_bytes = os.path.getsize(os.path.join(d, "out.h5"))
+    t0 = time.time()
+    conv.sgfs_to_hdf5(files, os.path.join(d, "out.npz"), bd_size=19, container="npz")   # bit-packed archive
+    t_npz = time.time() - t0
 n = len(packed)
 s = min(n, 2048)
 board = np.stack([p[0] for p in packed[:s]]); age = np.stack([p[1] for p in packed[:s]])
@@ -53,6 +57,7 @@ print(json.dumps({"positions": n, "planes": int(planes.shape[1]),
                   "host_replay_pack_positions_per_s": round(n / t_pack, 1),
                   "encode_incl_copies_positions_per_s": round(n / t_enc, 1),
                   "encode_bitpacked_incl_copies_positions_per_s": round(n / t_bits, 1),
-                  "sgfs_to_hdf5_positions_per_s": round(n / t_all, 1),
+                  "sgfs_to_hdf5_positions_per_s": round(n / t_all, 1), "hdf5_file_bytes": hdf5_bytes,
+                  "sgfs_to_npz_archive_positions_per_s": round(n / t_npz, 1),
                   "cpu_oracle_encode_positions_per_s": round(s / t_cpu, 1), "cpu_cores": cores,
                   "bit_exact_vs_oracle_on": s}))
