@@ -678,7 +678,9 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         memset(&w, 0, sizeof(w));
         w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
         w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
-        c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && (c.taps * (c.ldout / 64) + 3) / 4 <= kWgradCounterStride;
+        const int wg_tiles = (c.taps * (c.ldout / 64) + 3) / 4;   // the chained kernel keeps whole-accumulator partials: 256 rows x kin per tile
+        c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && wg_tiles <= kWgradCounterStride &&
+                        (size_t)c.wgrad_splits * wg_tiles * 256 * c.kin <= net->wgrad_scratch_floats;
     }
     // the arrival counters count in units of this batch's split factors: start over.  (Batch-size changes are rare; the device
     // is drained first so that no weight-gradient launch of the old batch size, on whatever stream, still uses them.)

@@ -156,7 +156,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
         // producer: warp-wide loop, one elected lane issues the TMA (uniform control flow, see conv.cu)
         const int n_win = plan->n_win;
         const CUtensorMap* gmap = windowed ? &tmap_gw : &tmap_g;
-        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : chunk_bytes) + b_chunks * chunk_bytes);
+        // measurement only (AG_WGRAD_DEBUG & 4): fetch just the X chunks a CTA of a pair would (half of N, rounded up to chunks)
+        const int xload = (p.debug & 4) ? (xchunks * 32 + 63) / 64 : xchunks;
+        const uint32_t tx_bytes = (uint32_t)(n_win * (windowed ? p.win_rows * 128 : chunk_bytes) + (b_chunks - nb * (xchunks - xload)) * chunk_bytes);
         int stage = 0;
         uint32_t phase = 0;
         for (int kb = kb0; kb < kb1; kb++) {
@@ -169,7 +171,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     tc::tma_load_2d(s + plan->win_off[w], gmap, &bars->full[stage], plan->win_col[w], m0 - plan->win_shift[w]);
                 for (int j = 0; j < nb; j++) {
                     const int xrow = taps_in_n ? m0 + p.off[grp * p.tpg + j] : m0;
-                    for (int c = 0; c < xchunks; c++)
+                    for (int c = 0; c < xload; c++)
                         tc::tma_load_2d(s + a_region + (j * xchunks + c) * chunk_bytes, &tmap_x, &bars->full[stage], c * 64, xrow);
                 }
             }
@@ -184,6 +186,12 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             const int lo = plan->lo[a], hi = plan->hi[a];
             const bool ones = with_bias && ((plan->slot_off[lo] >= 0 && plan->slot_bias[lo] >= 0) || (hi >= 0 && plan->slot_bias[hi] >= 0));
             idesc_acc[a] = tc::idesc_bf16(128, ones ? umma_n : acc_cols, 1, 1);
+            // measurement only (AG_WGRAD_DEBUG & 2): UMMAs of half the width = the operand bytes one CTA of a pair would read
+            // (& 8: each issued twice = the tensor work of the full width on top); results are wrong in these modes
+            if (p.debug & 2) idesc_acc[a] = tc::idesc_bf16(128, acc_cols / 2, 1, 1);
+            // & 8 / & 16: read A / B as if it were K-major (same bytes fetched, different order); & 32: M = 64
+            if (p.debug & (8 | 16 | 32))
+                idesc_acc[a] = tc::idesc_bf16((p.debug & 32) ? 64 : 128, (p.debug & 2) ? acc_cols / 2 : acc_cols, (p.debug & 8) ? 0 : 1, (p.debug & 16) ? 0 : 1);
         }
         const bool second = a_live > 2;  // the second accumulator has at least one live half
         // A operand of accumulator a: rows 0-63 from slot lo, rows 64-127 from slot hi (LBO = their distance)
@@ -208,7 +216,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     adesc0 |= (uint64_t)(((s + a_off[0]) >> 7) & 7) << 49;
                     adesc1 |= (uint64_t)(((s + a_off[1]) >> 7) & 7) << 49;
                 }
-                const uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
+                uint64_t bdesc = tc::desc_mnmajor_sw128(s + a_region, chunk_bytes);
+                if (p.debug & 8) { adesc0 = tc::desc_kmajor_sw128(s + a_off[0]); adesc1 = tc::desc_kmajor_sw128(s + a_off[1]); }
+                if (p.debug & 16) bdesc = tc::desc_kmajor_sw128(s + a_region);
 #pragma unroll 4
                 for (int k = 0; k < ksteps; k++) {  // 16 pixel rows per UMMA: +2048 B
                     tc::umma_bf16(tmem_base, adesc0 + (2048 >> 4) * k, bdesc + (2048 >> 4) * k, idesc_acc[0], (kb > kb0) || (k > 0));
@@ -245,7 +255,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
 #pragma unroll
                     for (int j = 0; j < 32; j++) v[j] = 0;
                 }
-                if (valid) {
+                if (valid && !(p.debug & 64)) {  // & 64 (measurement only): leave the partial stores out
                     float* d = dst + c0;
                     if (taps_in_n) {  // column c0 = (tap within the group) * kin + ci
                         const int j = c0 / p.kin;
@@ -329,7 +339,7 @@ wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, s
 constexpr int kWgradChainMax = 16;
 struct WgradChainLayer {
     CUtensorMap g, gw, x;
-    float* scratch;        // this layer's partial buffer [splits][taps*ldout][kin]
+    float* scratch;        // this layer's partial buffer [splits][tiles][2 accumulators][kin/4][128 rows][4] (TMEM order)
     float* bias_scratch;   // [splits][ldout]
     float* dw;             // [taps][ldout][kin]
     float* db;             // [ldout]
@@ -469,9 +479,10 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
         // epilogue warps: partial out of TMEM, then this CTA's share of the tile's split reduction
         const int q = warp & 3, et = threadIdx.x - 64;
         const int r = q * 32 + lane;
-        const size_t count4 = (size_t)p.taps * p.ldout * p.kin / 4;
         const int kin4 = p.kin / 4;
-        const int units = a_live * 64 * kin4;  // float4 elements of this tile's dW rows
+        const int tile_units = 2 * kin4 * 128;                    // float4 elements of one CTA's partial (both accumulators)
+        const size_t split_units = (size_t)p.tiles * tile_units;  // ... of one split's partials
+        const int units = (a_live > 2 ? 2 : 1) * kin4 * 128;      // ... of this tile's live accumulators
         const int u0 = (int)((long long)units * split / p.splits), u1 = (int)((long long)units * (split + 1) / p.splits);
         for (int li = 0; li < P.n_layers; li++) {
             const WgradChainLayer& L = P.layers[li];
@@ -481,8 +492,10 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
                 if (a * 2 >= a_live) break;  // warp-uniform
                 const int slot = (r >> 6) ? plan->hi[a] : plan->lo[a];
                 const bool valid = slot >= 0;
-                const int srow = valid ? plan->slot_row[slot] : 0;
-                float* dst = L.scratch + ((size_t)split * p.taps * p.ldout + (size_t)srow + (r & 63)) * p.kin;
+                // partials are kept in the order the accumulator comes out of TMEM, [accumulator][4-column group][row][4]:
+                // a warp's 32 rows of one column group are 512 contiguous bytes (row-major partials would scatter every
+                // store over 32 lines: 5.3 us of this epilogue per layer, during which the next layer's UMMAs wait for TMEM)
+                uint4* dst = reinterpret_cast<uint4*>(L.scratch) + ((size_t)split * p.tiles + tile) * tile_units + (size_t)a * kin4 * 128 + r;
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * kAccStride;
                 for (int c0 = 0; c0 < acc_cols; c0 += 32) {
                     uint32_t v[32];
@@ -491,7 +504,7 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
                     if (valid) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4)
-                            *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                            dst[(size_t)((c0 + j) >> 2) * 128] = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                     }
                 }
                 if (with_bias && valid && plan->slot_bias[slot] >= 0) {
@@ -526,16 +539,19 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
             // ---- this CTA's share of the tile: units [u0, u1), four interleaved partial sums added in order
             const float4* s4 = reinterpret_cast<const float4*>(L.scratch);
             float4* d4 = reinterpret_cast<float4*>(L.dw);
-            for (int u = u0 + et; u < u1; u += 128) {
-                const int sl = u / (64 * kin4);
-                const int rem = u - sl * 64 * kin4;
-                const size_t i = (size_t)(plan->slot_row[sl] + rem / kin4) * kin4 + (rem % kin4);
+            for (int u = u0 + et; u < u1; u += 128) {   // u = (accumulator, column group, row): the partials' own order
+                const int ua = u / (kin4 * 128);
+                const int c4 = (u >> 7) - ua * kin4, row = u & 127;
+                const int sl = (row >> 6) ? plan->hi[ua] : plan->lo[ua];
+                if (sl < 0) continue;                    // dead half of the last tile
+                const size_t i = (size_t)(plan->slot_row[sl] + (row & 63)) * kin4 + c4;   // dW is [tap][co][ci]
+                const float4* src = s4 + (size_t)tile * tile_units + u;
                 float4 acc[kReduceWays];
 #pragma unroll
                 for (int w = 0; w < kReduceWays; w++) {
                     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
                     for (int s = w; s < p.splits; s += kReduceWays) {
-                        const float4 b = ldcg4(s4 + (size_t)s * count4 + i);
+                        const float4 b = ldcg4(src + (size_t)s * split_units);
                         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
                     }
                     acc[w] = a;

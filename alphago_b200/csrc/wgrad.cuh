@@ -47,7 +47,8 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
 // One layer of a chained weight-gradient launch (wgrad.cu, wgrad_chain_kernel): same geometry for all, own buffers each.
 struct WgradChainEntry {
     const WgradMaps* maps;
-    float* scratch;            // [splits][taps*ldout][kin]; consecutive entries must alternate between two buffers
+    float* scratch;            // splits * tiles * 256 * kin floats (tiles = ceil(taps * ldout / 256)), laid out by the kernel;
+                               // consecutive entries must alternate between two buffers
     float* bias_scratch;       // [splits][ldout] or nullptr (then db is not produced)
     float* dw;
     float* db;
