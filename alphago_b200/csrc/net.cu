@@ -1217,6 +1217,12 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
         return AG_OK;
     }
     if (net->wgrad_n != n) { set_error("ag_net_run_layer: run ag_net_forward_loss with this batch first"); return AG_ESTATE; }
+    if (mode == 5) {  // the weight gradients of every hidden layer as the step launches them: one chained launch (`layer` ignored)
+        if (net->n_conv < 3) { set_error("ag_net_run_layer: no hidden layers"); return AG_EINVAL; }
+        for (int l = 1; l + 1 < net->n_conv; l++)
+            if (!net->L[l].wgrad_chain) { set_error("ag_net_run_layer: layer %d does not run chained", l); return AG_ESTATE; }
+        return net_wgrad_range(net, net->n_conv - 2, 1, n, st);
+    }
     if (mode == 2) {
         WgradArgs w;
         memset(&w, 0, sizeof(w));

@@ -270,7 +270,8 @@ class TrainWorkload(object):
         cases = [(3, "conv_chain_kernel(forward stack, 12 layers)", self.batch * FWD_FLOP_PER_POSITION),
                  (4, "conv_chain_kernel(data gradients, 11 layers)", self.batch * DGRAD_FLOP_PER_POSITION),
                  (0, "conv_gemm_win_kernel(fwd 3x3, one layer)", f3), (1, "conv_gemm_win_kernel(dgrad 3x3, one layer)", f3),
-                 (2, "wgrad_kernel+reduce(3x3, one layer)", f3)]
+                 (5, "wgrad_chain_kernel(weight gradients of the 11 3x3 layers, split reduction included)", 11 * f3),
+                 (2, "wgrad_kernel+reduce(3x3, one layer, stand-alone)", f3)]
         for mode, name, flop in cases:
             # "timed alone" means burst conditions, which is what the burst peak it is divided by was measured under: let the
             # power governor settle after the long step loop (under sustained load the SM clock sits near 1.65 GHz)

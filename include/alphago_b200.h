@@ -179,7 +179,8 @@ int ag_augment(const uint8_t* d_states, const uint8_t* d_actions, const int64_t*
                int batch, int planes, int size, uint8_t* d_out, int32_t* d_labels, void* stream);
 /* measurement hook for bench.py's per-kernel roofline: re-run one kernel of the step on the buffers in place.
  * mode 0 = forward conv of `layer`, 1 = its data gradient, 2 = its weight gradient, 3 = the whole forward conv stack as
- * one chained launch, 4 = the whole data-gradient chain (3 and 4 ignore `layer`; AG_ESTATE when the net runs unchained) */
+ * one chained launch, 4 = the whole data-gradient chain, 5 = the weight gradients of every hidden layer as one chained
+ * launch (3, 4 and 5 ignore `layer`; AG_ESTATE when the net runs unchained) */
 int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream);
 /* test/debug readback (synchronous, allocates): kind 0 = activations of conv layer, 1 = its pre-activation
  * gradient, as fp32 [n][cout][board][board] on the host */
