@@ -25,6 +25,8 @@ def bind(L):
     L.ag_net_run_layer.argtypes = [vp, i, i, i, vp]
     L.ag_wgrad_scratch_bytes.restype = C.c_size_t
     L.ag_wgrad_scratch_bytes.argtypes = [i, i, i, C.c_longlong]
+    L.ag_wgrad_partial_bytes.restype = C.c_size_t
+    L.ag_wgrad_partial_bytes.argtypes = [i, i, i]
     L.ag_wgrad.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, C.c_size_t, vp, vp]
     L.ag_wgrad_static_max_bytes.restype = C.c_size_t
     L.ag_wgrad_static.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, vp]

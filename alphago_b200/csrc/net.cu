@@ -672,7 +672,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         int rc = wgrad_make_maps(&c.tm_wg, g, xin, rows, c.ldout, c.kin, c.taps, c.off_fwd);
         if (rc) return rc;
         c.wgrad_splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows, net->sm_budget);
-        size_t need = (size_t)c.wgrad_splits * c.wcount;
+        size_t need = (size_t)c.wgrad_splits * wgrad_partial_floats(c.taps, c.ldout, c.kin);
         if (need > net->wgrad_scratch_floats) { set_error("wgrad scratch too small"); return AG_ESTATE; }
         WgradArgs w;
         memset(&w, 0, sizeof(w));
@@ -734,7 +734,8 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
         gcount += c.wcount + c.ldout;
         size_t rows_in = (size_t)max_batch * c.lin.img_stride;
         int splits = wgrad_plan_splits(c.taps, c.ldout, c.kin, (int)rows_in, 0);
-        if ((size_t)kWgradMaxSplits * c.wcount > scratch) scratch = (size_t)kWgradMaxSplits * c.wcount;
+        const size_t partials = (size_t)kWgradMaxSplits * wgrad_partial_floats(c.taps, c.ldout, c.kin);
+        if (partials > scratch) scratch = partials;
         (void)splits;
     }
     net->grad_offsets.push_back((long long)gcount);  // head slice

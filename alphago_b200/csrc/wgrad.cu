@@ -52,6 +52,9 @@ struct WgradPlan {
     int lo[2], hi[2];        // slots behind rows 0-63 / 64-127 of each accumulator (hi = -1: dead half); lo has the lower address
 };
 
+// float4 elements of one CTA's partial: two accumulators of 128 rows x (the widest B operand of the tiling) columns
+__host__ __device__ __forceinline__ int wgrad_tile_units(const WgradArgs& p) { return 2 * ((p.tpg > 1 ? p.tpg : 1) * p.kin / 4) * 128; }
+
 // Per-CTA constants (see WgradPlan), worked out once by one thread.
 __device__ __forceinline__ void wgrad_make_plan(const WgradArgs& p, WgradPlan* plan, const bool taps_in_n, const bool windowed,
                                                 const int chunk_bytes, const int a_first, const int a_live) {
@@ -243,8 +246,10 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (a * 2 >= a_live) break;  // warp-uniform
             const int slot = (r >> 6) ? plan->hi[a] : plan->lo[a];  // warp-uniform: a warp's 32 rows share a half
             const bool valid = slot >= 0;
-            const int srow = valid ? plan->slot_row[slot] : 0;
-            float* dst = p.scratch + ((size_t)split * p.taps * p.ldout + (size_t)srow + (r & 63)) * p.kin;
+            // partials in the order the accumulator comes out of TMEM, [accumulator][4-column group][row][4] (wgrad_tile_units):
+            // a warp's 32 rows of one column group are 512 contiguous bytes; wgrad_reduce_kernel puts them where they belong
+            uint4* dst = reinterpret_cast<uint4*>(p.scratch) + ((size_t)split * p.tiles + tile) * wgrad_tile_units(p) +
+                         (size_t)a * (wgrad_tile_units(p) / 2) + r;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * kAccStride;
             for (int c0 = 0; c0 < acc_cols; c0 += 32) {
                 uint32_t v[32];
@@ -256,14 +261,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                     for (int j = 0; j < 32; j++) v[j] = 0;
                 }
                 if (valid && !(p.debug & 64)) {  // & 64 (measurement only): leave the partial stores out
-                    float* d = dst + c0;
-                    if (taps_in_n) {  // column c0 = (tap within the group) * kin + ci
-                        const int j = c0 / p.kin;
-                        d = dst + (size_t)(grp * p.tpg + j) * p.ldout * p.kin + (c0 - j * p.kin);
-                    }
 #pragma unroll
                     for (int j = 0; j < 32; j += 4)
-                        *reinterpret_cast<uint4*>(d + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        dst[(size_t)((c0 + j) >> 2) * 128] = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
             }
             if (with_bias && valid && plan->slot_bias[slot] >= 0) {
@@ -282,47 +282,66 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     }
 }
 
-// dW[i] = sum_s scratch[s][i] in a fixed association (deterministic): the block's 4 thread rows each sum every 4th
-// split (independent loads, all in flight together), then the four sums are added in order through shared memory.
-constexpr int kReduceCols = 64;   // float4 columns per block
+// dW = sum over the splits of the partials, in a fixed association (deterministic): the block's 4 thread rows each sum every
+// 4th split (independent loads, all in flight together), then the four sums are added in order through shared memory.  The partials are in accumulator order (see the
+// kernel's epilogue); a block works on one tile, rebuilds that tile's plan and sends every element to its place in
+// dW [tap][co][ci].  Blocks beyond the tiles' share (blockIdx.y = 0 only) also sum the bias column.
+constexpr int kReduceCols = 64;   // elements (float4) per block
 constexpr int kReduceWays = 4;
 __global__ void __launch_bounds__(kReduceCols * kReduceWays)
-wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw, size_t count4, int splits,
-                    const float* __restrict__ bias_scratch, float* __restrict__ db, int ldout) {
+wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict__ db) {
     pdl_trigger();
     pdl_wait();
+    __shared__ WgradPlan plan;
     __shared__ float4 part[kReduceWays][kReduceCols];
-    if (db && blockIdx.x == 0) {
-        for (int c = threadIdx.x; c < ldout; c += blockDim.x) {
+    const int tile = blockIdx.x;
+    const bool taps_in_n = p.tpg > 1;
+    const int cochunks = p.ldout / 64;
+    const int coquads = (cochunks + kASlots - 1) / kASlots;
+    const int grp = taps_in_n ? tile / coquads : 0;
+    const int a_first = (taps_in_n ? tile - grp * coquads : tile) * kASlots;
+    const int a_count = taps_in_n ? cochunks : p.taps * cochunks;
+    const int a_live = min(kASlots, a_count - a_first);
+    const int nb = taps_in_n ? min(p.tpg, p.taps - grp * p.tpg) : 1;
+    if (threadIdx.x == 0) wgrad_make_plan(p, &plan, taps_in_n, p.win_rows > 0, p.krows * 128, a_first, a_live);
+    if (db && tile == 0 && blockIdx.y == 0) {
+        for (int c = threadIdx.x; c < p.ldout; c += blockDim.x) {
             float t = 0.f;
-            for (int s = 0; s < splits; s++) t += bias_scratch[(size_t)s * ldout + c];
+            for (int s = 0; s < p.splits; s++) t += p.bias_scratch[(size_t)s * p.ldout + c];
             db[c] = t;
         }
     }
-    const float4* s4 = reinterpret_cast<const float4*>(scratch);
+    __syncthreads();
+    const int kin4 = p.kin / 4;
+    const int tile_units = wgrad_tile_units(p), acc_units = tile_units / 2;
+    const int cols4 = nb * kin4;                                   // live 4-column groups of this tile's accumulators
+    const size_t split_units = (size_t)p.tiles * tile_units;
+    const float4* s4 = reinterpret_cast<const float4*>(p.scratch) + (size_t)tile * tile_units;
     float4* d4 = reinterpret_cast<float4*>(dw);
     const int col = threadIdx.x % kReduceCols, way = threadIdx.x / kReduceCols;
-    for (size_t i0 = (size_t)blockIdx.x * kReduceCols; i0 < count4; i0 += (size_t)gridDim.x * kReduceCols) {
-        const size_t i = i0 + col;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < count4) {
+    // 64 consecutive elements = 64 rows of one half of one column group: live or dead together (block-uniform)
+    const int u = blockIdx.y * kReduceCols + col;
+    const int a = u / acc_units;
+    const int c4 = (u - a * acc_units) >> 7, row = u & 127;
+    const int sl = a * 2 < a_live ? ((row >> 6) ? plan.hi[a] : plan.lo[a]) : -1;
+    if (sl < 0 || c4 >= cols4) return;                             // dead half / columns of a short last tap group
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 8
-            for (int s = way; s < splits; s += kReduceWays) {
-                const float4 b = __ldg(s4 + (size_t)s * count4 + i);
-                a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-            }
-        }
-        part[way][col] = a;
-        __syncthreads();
-        if (way == 0 && i < count4) {
+    for (int s = way; s < p.splits; s += kReduceWays) {
+        const float4 b = __ldg(s4 + (size_t)s * split_units + u);
+        t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+    }
+    part[way][col] = t;
+    __syncthreads();
+    if (way == 0) {
 #pragma unroll
-            for (int w = 1; w < kReduceWays; w++) {
-                const float4 b = part[w][col];
-                a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-            }
-            d4[i] = a;
+        for (int w = 1; w < kReduceWays; w++) {
+            const float4 b = part[w][col];
+            t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
         }
-        __syncthreads();
+        const int j = c4 / kin4;                                    // tap within the group (taps in N), else 0
+        const size_t drow = (size_t)(taps_in_n ? (grp * p.tpg + j) * p.ldout : 0) + plan.slot_row[sl] + (row & 63);
+        d4[drow * kin4 + (c4 - j * kin4)] = t;
     }
 }
 
@@ -597,6 +616,15 @@ static int wgrad_tiling(int taps, int ldout, int kin, int* tpg, int* groups) {
     return (taps * (ldout / 64) + kASlots - 1) / kASlots;
 }
 
+// floats of ONE split's partials: every CTA tile keeps two whole accumulators (128 rows x the tiling's widest B operand), which
+// is a little more than the taps * ldout * kin elements of dW when the tiles do not divide them
+size_t wgrad_partial_floats(int taps, int ldout, int kin) {
+    WgradArgs a;
+    a.kin = kin;
+    const int tiles = wgrad_tiling(taps, ldout, kin, &a.tpg, &a.groups);
+    return (size_t)tiles * wgrad_tile_units(a) * 4;
+}
+
 // pixel rows per pipeline stage (one TMA box per operand chunk).  Measured (3x3, 192 channels, batch 256): 64 rows x 3
 // stages 65.9 us, 32 rows x 6 stages 83 us: the smaller boxes cost more than the deeper pipeline gains.
 static int wgrad_krows() {
@@ -691,11 +719,8 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     args.win_rows = maps.win_rows;
     launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, maps.g, maps.gw, maps.x, args, stages);
     AG_LAUNCH_CHECK("wgrad_kernel");
-    size_t count4 = (size_t)args.taps * args.ldout * args.kin / 4;
-    int grid = (int)((count4 + kReduceCols - 1) / kReduceCols);
-    if (grid > sm_count() * 16) grid = sm_count() * 16;
-    launch_k(wgrad_reduce_kernel, dim3(grid), dim3(kReduceCols * kReduceWays), 0, stream, args.scratch, dw, count4, args.splits, args.bias_scratch,
-             args.bias_scratch ? db : nullptr, args.ldout);
+    launch_k(wgrad_reduce_kernel, dim3(args.tiles, wgrad_tile_units(args) / kReduceCols), dim3(kReduceCols * kReduceWays), 0, stream, args, dw,
+             args.bias_scratch ? db : nullptr);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
     return AG_OK;
 }
@@ -773,7 +798,13 @@ extern "C" {
 // bytes of scratch ag_wgrad wants for this problem (the split-K partials)
 size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows) {
     if (ag::wgrad_check(rows, ldout, kin, 1) || width < 1 || width > 5) return 0;
-    return (size_t)ag::wgrad_plan_splits(width * width, ldout, kin, (int)rows, 0) * width * width * ldout * kin * sizeof(float);
+    return (size_t)ag::wgrad_plan_splits(width * width, ldout, kin, (int)rows, 0) * ag::wgrad_partial_floats(width * width, ldout, kin) * sizeof(float);
+}
+
+// bytes of one split's partials: the least scratch ag_wgrad can work with
+size_t ag_wgrad_partial_bytes(int width, int ldout, int kin) {
+    if (ag::wgrad_check(1, ldout, kin, 1) || width < 1 || width > 5) return 0;
+    return ag::wgrad_partial_floats(width * width, ldout, kin) * sizeof(float);
 }
 
 int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride, float* d_scratch,
@@ -785,7 +816,7 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
     rc = ag::wgrad_offsets(width, row_stride, a.off);
     if (rc) return rc;
     a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
-    const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
+    const size_t partial = ag::wgrad_partial_floats(a.taps, ldout, kin) * sizeof(float);
     a.splits = ag::wgrad_plan_splits(a.taps, ldout, kin, (int)rows, 0);
     if ((size_t)a.splits * partial > scratch_bytes) a.splits = (int)(scratch_bytes / partial);
     if (a.splits < 1 || !d_scratch) { ag::set_error("ag_wgrad: scratch of %zu bytes is smaller than one partial (%zu bytes)", scratch_bytes, partial); return AG_EINVAL; }
@@ -842,7 +873,7 @@ int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout,
     rc = ag::wgrad_offsets(width, row_stride, a.off);
     if (rc) return rc;
     a.m_total = (int)rows; a.taps = width * width; a.ldout = ldout; a.kin = kin;
-    const size_t partial = (size_t)a.taps * ldout * kin * sizeof(float);
+    const size_t partial = ag::wgrad_partial_floats(a.taps, ldout, kin) * sizeof(float);
     if (partial > AG_WGRAD_STATIC_SCRATCH_BYTES) {
         ag::set_error("ag_wgrad_static: one %dx%d x %d x %d gradient (%zu bytes) exceeds the built-in scratch of %u bytes; "
                       "use ag_wgrad with your own scratch", width, width, ldout, kin, partial, AG_WGRAD_STATIC_SCRATCH_BYTES);

@@ -27,10 +27,12 @@ struct WgradArgs {
     int win_rows;  // filled by wgrad_launch from the maps
     int krows;     // filled by wgrad_launch from the maps: pixel rows per pipeline stage (32 or 64)
     int debug;     // experiments only (AG_WGRAD_DEBUG)
-    float* scratch;  // [splits][taps*ldout][kin] fp32
+    float* scratch;  // splits * wgrad_partial_floats() fp32, laid out by the kernel
     float* bias_scratch;  // nullptr, or [splits][ldout] fp32: column sums of G (the bias gradient) ride along as one more B column
 };
 
+// floats of one split's partials in `scratch` (>= taps * ldout * kin: whole accumulators per CTA tile, see wgrad.cu)
+size_t wgrad_partial_floats(int taps, int ldout, int kin);
 // sm_budget: SMs the launch may fill (0 = all): data-parallel training leaves a few to the collective running beside it
 int wgrad_plan_splits(int taps, int ldout, int kin, int m_total, int sm_budget);
 // Tensor maps of one weight-gradient problem: G [rows][ldout] and X [rows][kin] with box [krows][64] and EXACTLY `rows`

@@ -150,8 +150,10 @@ int ag_net_train_step(ag_net* net, const uint8_t* d_planes, const int32_t* d_lab
  * both "padded pixel rows" (>= w/2 zero slots after every board row and zero rows after
  * every image); ldout, kin multiples of 64 (kin <= 256); width odd <= 5; d_dw fp32 [width*width][ldout][kin].
  * d_scratch holds the split-K partials: ag_wgrad_scratch_bytes() is the preferred size, anything down to one
- * partial (width*width*ldout*kin*4 bytes) works with fewer splits.  Deterministic (fixed-order reduction). */
+ * partial (ag_wgrad_partial_bytes(): whole accumulator tiles, a little over width*width*ldout*kin*4 bytes) works
+ * with fewer splits.  Deterministic (fixed-order reduction). */
 size_t ag_wgrad_scratch_bytes(int width, int ldout, int kin, long long rows);
+size_t ag_wgrad_partial_bytes(int width, int ldout, int kin);
 int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
              float* d_scratch, size_t scratch_bytes, float* d_dw, void* stream);
 /* ag_wgrad for callers that must not allocate.  (No counterpart in the reference: nothing there manages device
@@ -160,7 +162,7 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
  * library holds until the process exits.  Meant for code that runs inside someone else's memory plan -- a
  * pre-sized pool that must stay untouched, a serving loop where cudaMalloc would stall or fail, a process with a
  * fixed device-memory budget.  It calls no cudaMalloc/cudaFree and no allocating library routine.
- *   - a problem whose single partial (width*width*ldout*kin*4 bytes) is larger than the array is refused with
+ *   - a problem whose single partial (ag_wgrad_partial_bytes()) is larger than the array is refused with
  *     AG_EINVAL and a message naming both sizes; smaller problems use as many splits as fit
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
  *     current); make that first call before starting any stream capture

@@ -42,4 +42,4 @@ torch.cuda.synchronize()
 us = e0.elapsed_time(e1) / reps * 1e3
 flop = 2.0 * n * S * S * 9 * ch * ch
 print(json.dumps({"n": n, "debug": os.environ.get("AG_WGRAD_DEBUG", "0"), "us_per_layer": round(us, 2), "tflops": round(flop / us / 1e6, 1),
-                  "splits": nbytes // (9 * ch * ch * 4)}))
+                  "splits": nbytes // L.ag_wgrad_partial_bytes(width, ch, ch)}))

@@ -54,7 +54,7 @@ def via_ag_wgrad(scratch_splits=None):
         nbytes = L.ag_wgrad_scratch_bytes(width, ldout, kin, rows)
         assert nbytes > 0
         if scratch_splits is not None:
-            nbytes = scratch_splits * width * width * ldout * kin * 4
+            nbytes = scratch_splits * L.ag_wgrad_partial_bytes(width, ldout, kin)
         scratch = torch.empty(nbytes // 4, dtype=torch.float32, device="cuda")
         return L.ag_wgrad(C.c_void_p(dg.data_ptr()), C.c_void_p(dx.data_ptr()), rows, ldout, kin, width, rs,
                           C.c_void_p(scratch.data_ptr()), nbytes, C.c_void_p(dw.data_ptr()), _lib.current_stream())
