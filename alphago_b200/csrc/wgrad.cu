@@ -246,10 +246,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
             if (a * 2 >= a_live) break;  // warp-uniform
             const int slot = (r >> 6) ? plan->hi[a] : plan->lo[a];  // warp-uniform: a warp's 32 rows share a half
             const bool valid = slot >= 0;
-            // partials in the order the accumulator comes out of TMEM, [accumulator][4-column group][row][4] (wgrad_tile_units):
-            // a warp's 32 rows of one column group are 512 contiguous bytes; wgrad_reduce_kernel puts them where they belong
+            // partials as [4-column group][slot * 64 + row of the slot][4] (wgrad_tile_units): a warp's 32 rows of one column
+            // group are 512 contiguous bytes (row-major partials would scatter every store over 32 lines); wgrad_reduce_kernel
+            // puts them where they belong in dW
             uint4* dst = reinterpret_cast<uint4*>(p.scratch) + ((size_t)split * p.tiles + tile) * wgrad_tile_units(p) +
-                         (size_t)a * (wgrad_tile_units(p) / 2) + r;
+                         (valid ? slot : 0) * 64 + (r & 63);
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * kAccStride;
             for (int c0 = 0; c0 < acc_cols; c0 += 32) {
                 uint32_t v[32];
@@ -263,7 +264,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
                 if (valid && !(p.debug & 64)) {  // & 64 (measurement only): leave the partial stores out
 #pragma unroll
                     for (int j = 0; j < 32; j += 4)
-                        dst[(size_t)((c0 + j) >> 2) * 128] = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        dst[(size_t)((c0 + j) >> 2) * 256] = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
             }
             if (with_bias && valid && plan->slot_bias[slot] >= 0) {
@@ -283,16 +284,15 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
 }
 
 // dW = sum over the splits of the partials, in a fixed association (deterministic): the block's 4 thread rows each sum every
-// 4th split (independent loads, all in flight together), then the four sums are added in order through shared memory.  The partials are in accumulator order (see the
-// kernel's epilogue); a block works on one tile, rebuilds that tile's plan and sends every element to its place in
-// dW [tap][co][ci].  Blocks beyond the tiles' share (blockIdx.y = 0 only) also sum the bias column.
+// 4th split (independent loads, all in flight together), then the four sums are added in order through shared memory.
+// The partials are [split][tile][4-column group][slot * 64 + row][4] (see the kernel's epilogue); a block takes the 64 rows
+// of one slot for one column group and sends them to their place in dW [tap][co][ci].  Block (0, 0) also sums the bias column.
 constexpr int kReduceCols = 64;   // elements (float4) per block
 constexpr int kReduceWays = 4;
 __global__ void __launch_bounds__(kReduceCols * kReduceWays)
 wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict__ db) {
     pdl_trigger();
     pdl_wait();
-    __shared__ WgradPlan plan;
     __shared__ float4 part[kReduceWays][kReduceCols];
     const int tile = blockIdx.x;
     const bool taps_in_n = p.tpg > 1;
@@ -301,9 +301,7 @@ wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict
     const int grp = taps_in_n ? tile / coquads : 0;
     const int a_first = (taps_in_n ? tile - grp * coquads : tile) * kASlots;
     const int a_count = taps_in_n ? cochunks : p.taps * cochunks;
-    const int a_live = min(kASlots, a_count - a_first);
     const int nb = taps_in_n ? min(p.tpg, p.taps - grp * p.tpg) : 1;
-    if (threadIdx.x == 0) wgrad_make_plan(p, &plan, taps_in_n, p.win_rows > 0, p.krows * 128, a_first, a_live);
     if (db && tile == 0 && blockIdx.y == 0) {
         for (int c = threadIdx.x; c < p.ldout; c += blockDim.x) {
             float t = 0.f;
@@ -311,24 +309,21 @@ wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict
             db[c] = t;
         }
     }
-    __syncthreads();
     const int kin4 = p.kin / 4;
-    const int tile_units = wgrad_tile_units(p), acc_units = tile_units / 2;
-    const int cols4 = nb * kin4;                                   // live 4-column groups of this tile's accumulators
-    const size_t split_units = (size_t)p.tiles * tile_units;
-    const float4* s4 = reinterpret_cast<const float4*>(p.scratch) + (size_t)tile * tile_units;
-    float4* d4 = reinterpret_cast<float4*>(dw);
+    const int tile_units = wgrad_tile_units(p);
     const int col = threadIdx.x % kReduceCols, way = threadIdx.x / kReduceCols;
-    // 64 consecutive elements = 64 rows of one half of one column group: live or dead together (block-uniform)
-    const int u = blockIdx.y * kReduceCols + col;
-    const int a = u / acc_units;
-    const int c4 = (u - a * acc_units) >> 7, row = u & 127;
-    const int sl = a * 2 < a_live ? ((row >> 6) ? plan.hi[a] : plan.lo[a]) : -1;
-    if (sl < 0 || c4 >= cols4) return;                             // dead half / columns of a short last tap group
+    const int c4 = blockIdx.y >> 2, slot = blockIdx.y & 3;         // block-uniform
+    const int c = a_first + slot;                                   // (co chunk, tap) pair co-major, or the co chunk (taps in N)
+    if (c >= a_count || c4 >= nb * kin4) return;                   // dead slot / columns of a short last tap group
+    const int cc = taps_in_n ? c : c / p.taps;
+    const int j = c4 / kin4;                                        // tap within the group (taps in N), else 0
+    const int tap = taps_in_n ? grp * p.tpg + j : c - cc * p.taps;
+    const size_t split_units = (size_t)p.tiles * tile_units;
+    const float4* s4 = reinterpret_cast<const float4*>(p.scratch) + (size_t)tile * tile_units + (size_t)c4 * 256 + slot * 64 + col;
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 8
     for (int s = way; s < p.splits; s += kReduceWays) {
-        const float4 b = __ldg(s4 + (size_t)s * split_units + u);
+        const float4 b = __ldg(s4 + (size_t)s * split_units);
         t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
     }
     part[way][col] = t;
@@ -339,9 +334,7 @@ wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict
             const float4 b = part[w][col];
             t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
         }
-        const int j = c4 / kin4;                                    // tap within the group (taps in N), else 0
-        const size_t drow = (size_t)(taps_in_n ? (grp * p.tpg + j) * p.ldout : 0) + plan.slot_row[sl] + (row & 63);
-        d4[drow * kin4 + (c4 - j * kin4)] = t;
+        reinterpret_cast<float4*>(dw)[((size_t)tap * p.ldout + cc * 64 + col) * kin4 + (c4 - j * kin4)] = t;
     }
 }
 
