@@ -283,17 +283,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__
     }
 }
 
-// dW = sum over the splits of the partials, in a fixed association (deterministic): the block's 4 thread rows each sum every
-// 4th split (independent loads, all in flight together), then the four sums are added in order through shared memory.
-// The partials are [split][tile][4-column group][slot * 64 + row][4] (see the kernel's epilogue); a block takes the 64 rows
-// of one slot for one column group and sends them to their place in dW [tap][co][ci].  Block (0, 0) also sums the bias column.
-constexpr int kReduceCols = 64;   // elements (float4) per block
+// dW = sum over the splits of the partials, in a fixed association (deterministic, and the chained kernel's): the block's 4
+// thread rows each sum every 4th split (independent loads, all in flight together: the kernel lives on memory-level
+// parallelism), then the four sums are added in order through shared memory.
+// The partials are [split][tile][4-column group][slot * 64 + row][4] (see the kernel's epilogue); a block takes 16 rows of one
+// slot for four neighbouring column groups -- reads of 256-byte runs, writes of 64 contiguous bytes per dW row -- and sends
+// them to their place in dW [tap][co][ci].  Block (0, 0) also sums the bias column.
 constexpr int kReduceWays = 4;
-__global__ void __launch_bounds__(kReduceCols * kReduceWays)
+constexpr int kReduceElems = 64;   // float4 elements per block: 16 rows x 4 column groups
+__global__ void __launch_bounds__(kReduceElems * kReduceWays)
 wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict__ db) {
     pdl_trigger();
     pdl_wait();
-    __shared__ float4 part[kReduceWays][kReduceCols];
+    __shared__ float4 part[kReduceWays][kReduceElems];
     const int tile = blockIdx.x;
     const bool taps_in_n = p.tpg > 1;
     const int cochunks = p.ldout / 64;
@@ -311,30 +313,31 @@ wgrad_reduce_kernel(const WgradArgs p, float* __restrict__ dw, float* __restrict
     }
     const int kin4 = p.kin / 4;
     const int tile_units = wgrad_tile_units(p);
-    const int col = threadIdx.x % kReduceCols, way = threadIdx.x / kReduceCols;
-    const int c4 = blockIdx.y >> 2, slot = blockIdx.y & 3;         // block-uniform
+    const int e = threadIdx.x % kReduceElems, way = threadIdx.x / kReduceElems;
+    // blockIdx.y = (group of 4 column groups, slot, group of 16 rows); kin is a multiple of 64, so 4 | kin4
+    const int c4 = (blockIdx.y >> 4) * 4 + (e >> 4), slot = (blockIdx.y >> 2) & 3, row = (blockIdx.y & 3) * 16 + (e & 15);
     const int c = a_first + slot;                                   // (co chunk, tap) pair co-major, or the co chunk (taps in N)
-    if (c >= a_count || c4 >= nb * kin4) return;                   // dead slot / columns of a short last tap group
+    if (c >= a_count || (blockIdx.y >> 4) * 4 >= nb * kin4) return; // dead slot / columns of a short last tap group (block-uniform)
     const int cc = taps_in_n ? c : c / p.taps;
     const int j = c4 / kin4;                                        // tap within the group (taps in N), else 0
     const int tap = taps_in_n ? grp * p.tpg + j : c - cc * p.taps;
     const size_t split_units = (size_t)p.tiles * tile_units;
-    const float4* s4 = reinterpret_cast<const float4*>(p.scratch) + (size_t)tile * tile_units + (size_t)c4 * 256 + slot * 64 + col;
+    const float4* s4 = reinterpret_cast<const float4*>(p.scratch) + (size_t)tile * tile_units + (size_t)c4 * 256 + slot * 64 + row;
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 8
     for (int s = way; s < p.splits; s += kReduceWays) {
         const float4 b = __ldg(s4 + (size_t)s * split_units);
         t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
     }
-    part[way][col] = t;
+    part[way][e] = t;
     __syncthreads();
     if (way == 0) {
 #pragma unroll
         for (int w = 1; w < kReduceWays; w++) {
-            const float4 b = part[w][col];
+            const float4 b = part[w][e];
             t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
         }
-        reinterpret_cast<float4*>(dw)[((size_t)tap * p.ldout + cc * 64 + col) * kin4 + (c4 - j * kin4)] = t;
+        reinterpret_cast<float4*>(dw)[((size_t)tap * p.ldout + cc * 64 + row) * kin4 + (c4 - j * kin4)] = t;
     }
 }
 
@@ -712,7 +715,7 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     args.win_rows = maps.win_rows;
     launch_k(wgrad_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, maps.g, maps.gw, maps.x, args, stages);
     AG_LAUNCH_CHECK("wgrad_kernel");
-    launch_k(wgrad_reduce_kernel, dim3(args.tiles, wgrad_tile_units(args) / kReduceCols), dim3(kReduceCols * kReduceWays), 0, stream, args, dw,
+    launch_k(wgrad_reduce_kernel, dim3(args.tiles, wgrad_tile_units(args) / kReduceElems), dim3(kReduceElems * kReduceWays), 0, stream, args, dw,
              args.bias_scratch ? db : nullptr);
     AG_LAUNCH_CHECK("wgrad_reduce_kernel");
     return AG_OK;
