@@ -20,7 +20,13 @@ from oracle import go_oracle as og
 
 feats = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size", "liberties_after",
          "ladder_capture", "ladder_escape", "sensibleness", "zeros"]
-files = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "sgf", "*.sgf"))) * 8
+import shutil
+_src = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "sgf", "*.sgf")))
+_copies = tempfile.mkdtemp()   # eight copies under names of their own (one name per file in `file_offsets`, as in h5py)
+files = []
+for rep in range(8):
+    for f in _src:
+        files.append(shutil.copy(f, os.path.join(_copies, "%d-%s" % (rep, os.path.basename(f)))))
 conv = game_converter(feats)
 t0 = time.time()
 packed = []
