@@ -8,8 +8,8 @@
 // is the ROW index of both matrices, so both operands are MN-major: TMA brings [64 pixel rows][64
 // channels] boxes (128-byte swizzle) that the UMMA reads transposed.  A CTA owns two 128-row tiles of the
 // flattened (tap, co) axis = four 64-channel chunks, each loaded with its own tap shift, and a
-// contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tap*co][ci] and
-// wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
+// contiguous slice of the pixel rows; its fp32 partial goes to scratch [split][tile][...] in an order that makes the
+// epilogue's stores contiguous (see there) and wgrad_reduce sums the splits in a fixed order (deterministic, no atomics).
 //
 // Narrow inputs (kin <= 128: the first layer, 48 planes -> kin = 64) would leave most of the UMMA's N = 256 unused
 // that way (an M = 128 UMMA costs the same ~128 cycles for any N <= 256), so they use the mirrored tiling
