@@ -1,6 +1,7 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, smoke, bench, then ncu (only if everything before it exited 0)
-# or compute-sanitizer on a small case (if the tests failed).  Writes everything to gpurun_out/.
+# One GPU-box visit: parity tests, smoke, bench, then ncu (only if everything before it exited 0).
+# Writes everything to gpurun_out/.  (compute-sanitizer is not available on this pool: bad accesses are hunted with the
+# kernels' own bounded waits and traps, small cases and the CPU oracle.)
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.limit --format=csv > gpurun_out/gpu.txt 2>&1
 nproc >> gpurun_out/gpu.txt
@@ -17,8 +18,6 @@ if [ $PT -eq 0 ]; then
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $BENCH > gpurun_out/ncu_list.log 2>&1
   timeout 300 $BENCH > /dev/null 2>> gpurun_out/bench.err &&
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-encode_kernel}" -s 4 -c 2 -f -o gpurun_out/prof_${NCU_NAME:-encode} $BENCH > gpurun_out/ncu_full.log 2>&1
-else
-  timeout 600 compute-sanitizer --tool memcheck python -m pytest tests/test_encoder_gpu.py -m gpu -q -x -k "golden_planes or edge" -p no:cacheprovider > gpurun_out/sanitizer.log 2>&1
 fi
 tail -5 gpurun_out/pytest.log
 cat gpurun_out/bench.json 2>/dev/null
