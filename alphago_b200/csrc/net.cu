@@ -74,6 +74,9 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kHeadThreads / 32;
     for (int c = threadIdx.x; c < 256; c += kHeadThreads) s_w[c] = c < ld ? w[c] : 0.f;
     __syncthreads();
+    float wl[8];   // this lane's eight channel weights: loop-invariant, kept out of the row loops' shared-memory traffic
+#pragma unroll
+    for (int j = 0; j < 8; j++) wl[j] = s_w[(lane * 8 + j) & 255];
     const int groups = ld / 8;  // 16-byte groups per row; lanes >= groups idle (ld <= 256)
     const float b0 = bias[0];
     constexpr int U = 5;  // rows in flight per warp (measured: 8 with two CTAs per SM forced was slower, 40.8 vs 38.2 us): the loop is bound by load latency, not bandwidth
@@ -94,7 +97,7 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
             const bf16* vb = reinterpret_cast<const bf16*>(&v[u]);
             float acc = 0.f;
 #pragma unroll
-            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * s_w[(lane * 8 + j) & 255];
+            for (int j = 0; j < 8; j++) acc += __bfloat162float(vb[j]) * wl[j];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
             if (lane == 0 && p < pts) s_logit[p] = acc + b0 + (pos_bias ? pos_bias[p] : 0.f);
@@ -220,7 +223,7 @@ policy_head_kernel(const bf16* __restrict__ X, int ld, PixelLayout L, const floa
                 for (int j = 0; j < 8; j++) {
                     float xv = __bfloat162float(vb[j]);
                     dw[j] += d * xv;
-                    ob[j] = __float2bfloat16(xv > 0.f ? d * s_w[lane * 8 + j] : 0.f);
+                    ob[j] = __float2bfloat16(xv > 0.f ? d * wl[j] : 0.f);
                 }
                 *reinterpret_cast<uint4*>(G + roff[u]) = o;
             }
