@@ -58,6 +58,10 @@ def lib():
     L.ag_state_pack.argtypes = [vp, i8p, u8p, i8p, i16p]; L.ag_state_pack.restype = None
     L.ag_age_from_history.argtypes = [C.c_int, i8p, i16p, C.c_int, u8p]; L.ag_age_from_history.restype = None
     L.ag_playout_positions.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, i8p, u8p, i8p, i16p]
+    L.ag_lzf_decompress.restype = C.c_longlong
+    L.ag_lzf_decompress.argtypes = [C.c_char_p, C.c_size_t, vp, C.c_size_t]
+    L.ag_lzf_compress.restype = C.c_longlong
+    L.ag_lzf_compress.argtypes = [vp, C.c_size_t, vp, C.c_size_t]
     _bind_optional(L)
     _lib = L
     return L

@@ -169,7 +169,7 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
 class _Hdf5Sink(object):
     """the dataset file while it grows: the reference's three members (game_converter.py:71-88), filled block by block
     through h5py's resize-and-assign calls -- h5py itself where importable, hdf5_lite's writer (same calls) otherwise.
-    Blocks are unpacked, deflated and written by one background thread (zlib and numpy release the interpreter lock),
+    Blocks are unpacked, compressed and written by one background thread (the codecs and numpy release the interpreter lock),
     so the file keeps up while the caller replays the next games."""
 
     def __init__(self, path, n_features, size):

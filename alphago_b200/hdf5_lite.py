@@ -11,8 +11,10 @@ Writer (`File(path, "w")`, the subset of h5py's API that game_converter.py:67-88
 use: create_dataset / create_group / require_group / group[name] = array / .attrs[name] = value): the same "earliest"
 format, laid out the way libhdf5 lays out the reference's own fixture file (superblock v0, v1 object headers, one local
 heap + v1 B-tree of symbol nodes per group, contiguous datasets, chunked datasets behind a v1 chunk B-tree).  Chunks are
-compressed with the deflate filter (id 1), which every libhdf5 build carries; the reference's converter asks for LZF,
-a filter that ships with h5py only -- same datasets, shapes and types either way.  Data goes to the file as it is
+compressed with the filter asked for: `compression="lzf"` (the reference's converter) gives LZF chunks under h5py's
+filter id 32000 and client data, through the library's host codec (csrc/lzf.cu; deflate level 1 where the library is not
+built); `compression="gzip"` gives deflate (id 1).  A chunk LZF cannot shrink is stored raw with its filter-mask bit
+set, as libhdf5 does for an optional filter.  Data goes to the file as it is
 handed over, metadata at close().  No libhdf5 is available in this image to cross-check the files: the writer is
 checked by this module's reader (which is itself pinned on the reference's real file) in tests/test_hdf5_lite.py.
 
@@ -55,6 +57,43 @@ def lzf_decompress(src, out_len):
     if len(out) != out_len:
         raise ValueError("LZF stream decoded to %d bytes, expected %d" % (len(out), out_len))
     return bytes(out)
+
+
+def _native():
+    """libalphago_b200.so's host LZF codec (csrc/lzf.cu), or None where the library is not built: the reader then decodes in
+    Python (slow: seconds per MB) and the writer falls back to deflate chunks"""
+    try:
+        from . import _lib
+        return _lib.lib()
+    except Exception:
+        return None
+
+
+def lzf_decode(src, out_len):
+    """LZF stream -> bytes, natively when the library is there"""
+    L = _native()
+    if L is None:
+        return lzf_decompress(src, out_len)
+    import ctypes
+    out = ctypes.create_string_buffer(out_len)
+    n = L.ag_lzf_decompress(bytes(src), len(src), ctypes.cast(out, ctypes.c_void_p), out_len)
+    if n != out_len:
+        raise ValueError("LZF stream decoded to %d bytes, expected %d" % (n, out_len))
+    return out.raw
+
+
+def lzf_encode(raw):
+    """bytes -> LZF stream, or None when it would not be shorter than `raw` (the chunk is then stored unfiltered) or the
+    library is not built"""
+    L = _native()
+    if L is None or len(raw) < 4:
+        return None
+    import ctypes
+    cap = len(raw) - 1
+    out = ctypes.create_string_buffer(cap)
+    src = np.frombuffer(raw, np.uint8)
+    n = L.ag_lzf_compress(ctypes.c_void_p(src.ctypes.data), len(raw), ctypes.cast(out, ctypes.c_void_p), cap)
+    return out.raw[:n] if n > 0 else None
 
 
 class _Reader(object):
@@ -215,7 +254,7 @@ class Dataset(object):
                 if fmask & (1 << i):
                     continue
                 if fid == 32000:
-                    raw = lzf_decompress(raw, n * self.dtype.itemsize)
+                    raw = lzf_decode(raw, n * self.dtype.itemsize)
                 elif fid == 1:
                     raw = zlib.decompress(raw)
                 elif fid == 2:
@@ -436,8 +475,10 @@ class WDataset(_WNode):
             raise ValueError("bad chunk shape %r for data of shape %r" % (chunks, self.shape))
         if compression not in (None, False, "gzip", "lzf", "deflate"):
             raise NotImplementedError("compression %r" % (compression,))
-        # "lzf" is accepted for the reference's call (game_converter.py:73-74) and stored as deflate level 1 (module docstring)
-        self.level = None if not compression else (1 if compression == "lzf" else int(compression_opts) if compression_opts is not None else 4)
+        # "lzf" (the reference's call, game_converter.py:73-74) gives LZF chunks through the library's host codec, and deflate
+        # level 1 where the library is not built
+        self.lzf = compression == "lzf" and _native() is not None
+        self.level = None if not compression or self.lzf else (1 if compression == "lzf" else int(compression_opts) if compression_opts is not None else 4)
         self.index, self._next, self._pending, self._npending = [], 0, [], 0
         self._rowwise = bool(self.chunks) and self.chunks[1:] == self.shape[1:]
         if self.chunks is None:
@@ -492,7 +533,11 @@ class WDataset(_WNode):
             self._flush(False)
 
     def _pack(self, raw):
-        return zlib.compress(raw, self.level) if self.level is not None else raw   # zlib releases the GIL
+        """chunk bytes -> (stored bytes, filter mask); zlib and the native LZF codec release the interpreter lock"""
+        if self.lzf:
+            enc = lzf_encode(raw)
+            return (enc, 0) if enc is not None else (raw, 1)   # an optional filter that does not help is skipped for that chunk
+        return (zlib.compress(raw, self.level), 0) if self.level is not None else (raw, 0)
 
     def _flush(self, final):
         """deflate and append every complete chunk of the pending rows (and, at the end, the partial one, zero-padded)"""
@@ -512,8 +557,8 @@ class WDataset(_WNode):
             rest = rest[:0]
         tail = (0,) * (len(self.shape) - 1)
         with ThreadPoolExecutor(max_workers=max(1, min(16, os.cpu_count() or 1, len(pieces)))) as pool:
-            for i, blob in enumerate(pool.map(lambda p: self._pack(np.ascontiguousarray(p).tobytes()), pieces)):
-                self.index.append(((first + i * c0,) + tail, self.f._append(blob), len(blob)))
+            for i, (blob, mask) in enumerate(pool.map(lambda p: self._pack(np.ascontiguousarray(p).tobytes()), pieces)):
+                self.index.append(((first + i * c0,) + tail, self.f._append(blob), len(blob), mask))
         self._pending, self._npending = ([np.array(rest)], len(rest)) if len(rest) else ([], 0)
 
     def _write_chunks(self, arr):
@@ -534,19 +579,19 @@ class WDataset(_WNode):
             return self._pack(np.ascontiguousarray(piece).tobytes())
 
         with ThreadPoolExecutor(max_workers=min(16, (os.cpu_count() or 1))) as pool:
-            for o, blob in zip(offs, pool.map(cut, offs)):
-                self.index.append((o, self.f._append(blob), len(blob)))
+            for o, (blob, mask) in zip(offs, pool.map(cut, offs)):
+                self.index.append((o, self.f._append(blob), len(blob), mask))
 
     def _chunk_btree(self):
         """v1 B-tree (node type 1) over self.index; returns the root's address (UNDEF without chunks)"""
         if not self.index:
             return UNDEF
         nd = len(self.shape) + 1
-        key = lambda size, offs, tail=0: struct.pack("<II", size, 0) + b"".join(struct.pack("<Q", v) for v in offs) + struct.pack("<Q", tail)
+        key = lambda size, offs, tail=0, mask=0: struct.pack("<II", size, mask) + b"".join(struct.pack("<Q", v) for v in offs) + struct.pack("<Q", tail)
         # the key behind the last chunk: one chunk further in every dimension (what libhdf5 leaves there)
         end_key = key(0, [o + c for o, c in zip(self.index[-1][0], self.chunks)], self.dtype.itemsize)
         # level 0 entries: (first key, child address); one node holds up to 2K children
-        entries = [(key(n, o), a) for o, a, n in self.index]
+        entries = [(key(n, o, 0, m), a) for o, a, n, m in self.index]
         level = 0
         node_size = 24 + (2 * CHUNK_NODE_K) * 8 + (2 * CHUNK_NODE_K + 1) * (8 + 8 * nd)
         while True:
@@ -574,7 +619,11 @@ class WDataset(_WNode):
             msgs.append((0x0008, 1, struct.pack("<BBQQ", 3, 1, self.addr, self.nbytes)))
         else:
             msgs.append((0x0005, 1, bytes([2, 3, 0, 1]) + struct.pack("<I", 0)))   # allocate incrementally
-            if self.level is not None:
+            if self.lzf:   # h5py's registration of the filter: id 32000, optional, client data = (filter revision 4, liblzf 1.5, chunk bytes)
+                chunk_bytes = int(np.prod(self.chunks)) * esize
+                msgs.append((0x000B, 1, struct.pack("<BB6x", 1, 1) + struct.pack("<HHHH", 32000, 8, 1, 3) + b"lzf\0\0\0\0\0" +
+                             struct.pack("<IIII", 4, 0x0105, chunk_bytes, 0)))
+            elif self.level is not None:
                 msgs.append((0x000B, 1, struct.pack("<BB6x", 1, 1) + struct.pack("<HHHH", 1, 8, 1, 1) + b"deflate\0" + struct.pack("<II", self.level, 0)))
             msgs.append((0x0008, 1, struct.pack("<BBBQ", 3, 2, len(self.shape) + 1, self._chunk_btree()) +
                          b"".join(struct.pack("<I", c) for c in self.chunks) + struct.pack("<I", esize)))

@@ -172,6 +172,12 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
 size_t ag_wgrad_static_max_bytes(void);
 int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
                     float* d_dw, void* stream);
+/* LZF byte streams on the host (no GPU work): the chunk filter the reference's converter asks h5py for
+ * (compression="lzf", game_converter.py:73-74,81-82).  decompress returns the number of bytes written, or -1 on a
+ * corrupt stream / too small an output buffer; compress returns the stream's length, or 0 when it does not fit
+ * out_cap (the caller then stores the chunk unfiltered, as the HDF5 filter does). */
+long long ag_lzf_decompress(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_cap);
+long long ag_lzf_compress(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_cap);
 /* Minibatch assembly (shuffled_hdf5_batch_generator + BOARD_TRANSFORMATIONS + one_hot_action,
  * supervised_policy_trainer.py:10-40,71-80): for b in [0, batch): sample d_index[b] of the dataset
  * (d_states uint8 [N][planes][size][size], d_actions uint8 [N][2] as (x, y)) under dihedral transform

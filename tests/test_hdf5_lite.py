@@ -87,10 +87,10 @@ def test_chunked_compressed_and_streamed_like_the_reference_converter(tmp_path):
             st[300] = states[0]                           # beyond the current size: resize first
     r = h5.File(path)
     s = r["states"]
-    assert s.shape == (300, 12, 19, 19) and s.chunk == (64, 12, 19, 19) and s.filters == [1] and s.dtype == np.uint8
+    assert s.shape == (300, 12, 19, 19) and s.chunk == (64, 12, 19, 19) and s.filters == [32000] and s.dtype == np.uint8   # real LZF, as the reference
     assert np.array_equal(s[:], states) and np.array_equal(r["actions"][:], acts)
     assert np.array_equal(s[[5, 299, 64]], states[[5, 299, 64]]) and np.array_equal(s[60:70], states[60:70])
-    assert os.path.getsize(path) < states.nbytes // 3    # the chunks really are deflated
+    assert os.path.getsize(path) < states.nbytes // 2    # the chunks really are compressed
 
 
 def test_chunk_tree_with_more_than_one_node_and_nd_chunks(tmp_path):
@@ -103,6 +103,32 @@ def test_chunk_tree_with_more_than_one_node_and_nd_chunks(tmp_path):
     r = h5.File(path)
     assert np.array_equal(r["rows"][:], a) and np.array_equal(r["rows"][997:], a[997:]) and r["rows"].filters == []
     assert np.array_equal(r["grid"][:], grid)
+
+
+def test_lzf_codec_and_chunks_it_cannot_shrink(tmp_path):
+    """the host LZF codec (csrc/lzf.cu) against the pure-Python decoder kept in hdf5_lite as the format's statement, and
+    the optional-filter rule: a chunk LZF cannot shrink is stored raw with its filter-mask bit set"""
+    rng = np.random.RandomState(3)
+    samples = [_planes(8).tobytes(), bytes(70000), b"abcabcabcabcabc", b"the quick brown fox " * 999,
+               bytes(rng.randint(0, 4, 50000).astype(np.uint8)), b"ab" * 5000 + rng.bytes(300) + b"ab" * 5000]
+    for raw in samples:
+        enc = h5.lzf_encode(raw)
+        assert enc is not None and len(enc) < len(raw)
+        assert h5.lzf_decode(enc, len(raw)) == raw and h5.lzf_decompress(enc, len(raw)) == raw
+        with pytest.raises(ValueError):
+            h5.lzf_decode(enc[:-1], len(raw))
+    assert h5.lzf_encode(rng.bytes(4096)) is None        # noise does not compress
+    path = str(tmp_path / "raw.h5")
+    noise = np.frombuffer(rng.bytes(3 * 1024), np.uint8).reshape(3, 1024)
+    mixed = np.concatenate([noise, np.zeros((3, 1024), np.uint8)])
+    with h5.File(path, "w") as f:
+        f.create_dataset("mixed", data=mixed, chunks=(1, 1024), compression="lzf")
+    d = h5.File(path)["mixed"]
+    assert d.filters == [32000] and np.array_equal(d[:], mixed)
+    d._chunk((0, 0))
+    masks = [d._chunks[(i, 0)][2] for i in range(6)]
+    sizes = [d._chunks[(i, 0)][1] for i in range(6)]
+    assert masks == [1, 1, 1, 0, 0, 0] and sizes[:3] == [1024] * 3 and max(sizes[3:]) < 64
 
 
 def _walk_headers(b, addr, seen):
