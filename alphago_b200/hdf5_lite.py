@@ -237,13 +237,25 @@ class Dataset(object):
                 self._walk(child, out)
             p += ksz + 8
 
-    def _chunk(self, offs):
+    def _index(self):
         if self._chunks is None:
             self._chunks = {}
             if self.btree != UNDEF:
                 self._walk(self.btree, self._chunks)
+        return self._chunks
+
+    def _chunk(self, offs):
+        """one decoded chunk, through a small cache (row-by-row readers come back to the same chunk)"""
         if offs in self._cache:
             return self._cache[offs]
+        arr = self._decode(offs)
+        if len(self._cache) > 64:
+            self._cache.clear()
+        self._cache[offs] = arr
+        return arr
+
+    def _decode(self, offs):
+        self._index()
         n = int(np.prod(self.chunk))
         if offs not in self._chunks:
             arr = np.zeros(self.chunk, self.dtype)
@@ -262,9 +274,6 @@ class Dataset(object):
                 else:
                     raise NotImplementedError("HDF5 filter %d" % fid)
             arr = np.frombuffer(raw, self.dtype, count=n).reshape(self.chunk)
-        if len(self._cache) > 64:
-            self._cache.clear()
-        self._cache[offs] = arr
         return arr
 
     def _rows(self, lo, hi):
@@ -278,12 +287,19 @@ class Dataset(object):
         out = np.zeros((hi - lo,) + self.shape[1:], self.dtype)
         c0 = self.chunk[0]
         grid = [range(0, s, c) for s, c in zip(self.shape[1:], self.chunk[1:])]
+        idxs = [()]
+        for g in grid:
+            idxs = [i + (o,) for i in idxs for o in g]
+        keys = [(first,) + rest for first in range(lo // c0 * c0, hi, c0) for rest in idxs]
+        if len(keys) > 8:   # a bulk read (the trainer takes the whole dataset): decode on all cores, past the cache
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as pool:
+                decoded = dict(zip(keys, pool.map(self._decode, keys)))
+        else:
+            decoded = None
         for first in range(lo // c0 * c0, hi, c0):
-            idxs = [()]
-            for g in grid:
-                idxs = [i + (o,) for i in idxs for o in g]
             for rest in idxs:
-                ch = self._chunk((first,) + rest)
+                ch = decoded.pop((first,) + rest) if decoded is not None else self._chunk((first,) + rest)
                 a, z = max(lo, first), min(hi, first + c0, self.shape[0])
                 sl = (slice(a - first, z - first),) + tuple(slice(0, min(c, s - o)) for c, s, o in zip(self.chunk[1:], self.shape[1:], rest))
                 dst = (slice(a - lo, z - lo),) + tuple(slice(o, min(o + c, s)) for c, s, o in zip(self.chunk[1:], self.shape[1:], rest))
