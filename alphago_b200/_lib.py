@@ -56,6 +56,7 @@ def lib():
     L.ag_state_history.argtypes = [vp, i16p]; L.ag_state_history.restype = None
     L.ag_state_groups.argtypes = [vp, i16p, i16p, i16p]; L.ag_state_groups.restype = None
     L.ag_state_pack.argtypes = [vp, i8p, u8p, i8p, i16p]; L.ag_state_pack.restype = None
+    L.ag_state_replay_pack.argtypes = [vp, C.c_int, i16p, i8p, i8p, u8p, i8p, i16p, C.POINTER(C.c_int)]
     L.ag_age_from_history.argtypes = [C.c_int, i8p, i16p, C.c_int, u8p]; L.ag_age_from_history.restype = None
     L.ag_playout_positions.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, i8p, u8p, i8p, i16p]
     L.ag_lzf_decompress.restype = C.c_longlong

@@ -111,7 +111,7 @@ ag_state* ag_state_new(int size) {
 ag_state* ag_state_copy(const ag_state* s) { return s ? new ag_state(*s) : nullptr; }
 void ag_state_free(ag_state* s) { delete s; }
 int ag_state_do_move(ag_state* s, int point, int colour) {
-    if (point >= s->b.n || (colour != 0 && colour != 1 && colour != -1)) { set_error("ag_state_do_move: bad argument"); return AG_EINVAL; }
+    if (point >= s->b.n || point < -1 || (colour != 0 && colour != 1 && colour != -1)) { set_error("ag_state_do_move: bad argument"); return AG_EINVAL; }
     if (!s->b.play(point, colour)) { set_error("illegal move %d", point); return AG_ESTATE; }
     return AG_OK;
 }
@@ -167,6 +167,27 @@ void ag_state_pack(const ag_state* s, int8_t* board, uint8_t* age, int8_t* playe
     ag::age_from_history(b.size, b.stone, b.history.data(), (int)b.history.size(), age);
     *player = (int8_t)b.to_move;
     *ko = (int16_t)b.ko;
+}
+
+int ag_state_replay_pack(ag_state* s, int n_moves, const int16_t* points, const int8_t* colours, int8_t* boards, uint8_t* ages,
+                         int8_t* players, int16_t* kos, int* n_packed) {
+    int k = 0;
+    const int pts = s->b.n;
+    for (int i = 0; i < n_moves; i++) {
+        const int point = points[i], colour = colours[i];
+        if (point < -1 || (colour != 1 && colour != -1)) { *n_packed = k; set_error("ag_state_replay_pack: bad move %d", i); return AG_EINVAL; }
+        if (point >= 0) {   // the position BEFORE a non-pass move is one training pair (game_converter.py:38-40)
+            ag_state_pack(s, boards + (size_t)k * pts, ages + (size_t)k * pts, players + k, kos + k);
+            k++;
+        }
+        if (point >= pts || !s->b.play(point, colour)) {   // off the board counts as illegal, as in GameState.do_move
+            *n_packed = k;
+            set_error("illegal move %d (entry %d)", point, i);
+            return AG_ESTATE;
+        }
+    }
+    *n_packed = k;
+    return AG_OK;
 }
 
 int ag_playout_positions(uint64_t seed, int n, int size, int max_moves, int per_game, int8_t* board, uint8_t* age,

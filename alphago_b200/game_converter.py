@@ -15,7 +15,7 @@ import numpy as np
 
 from . import go
 from .preprocessing import Preprocess, pack_state
-from .util import ParseException, sgf_iter_states
+from .util import ParseException, sgf_iter_states, sgf_move_list
 
 
 class SizeMismatchError(Exception):
@@ -52,13 +52,16 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
         try:
             with open(file_name, "r") as file_object:
                 text = file_object.read()
-            for (state, move, player) in sgf_iter_states(text):
-                if state.size != bd_size:
-                    raise SizeMismatchError()
-                if move != go.PASS_MOVE:
-                    b, a, pl, ko = pack_state(state)
-                    packed.append((b.copy(), a.copy(), pl, ko))
-                    actions.append(move)
+            gs, moves, players = sgf_move_list(text)
+            if moves and gs.size != bd_size:
+                raise SizeMismatchError()
+            # one library call replays the record and packs the position in front of every non-pass move
+            b, a, pl, ko, illegal = gs.replay_pack(moves, players)
+            packed = [(b[i], a[i], int(pl[i]), int(ko[i])) for i in range(len(b))]
+            played = moves if illegal is None else moves[:illegal + 1]
+            actions = [m for m in played if m is not go.PASS_MOVE]
+            if illegal is not None:
+                error = go.IllegalMove(str(moves[illegal]))
         except Exception as e:   # classified by the caller
             error = e
         return packed, actions, error

@@ -219,6 +219,29 @@ class GameState(object):
         return b, a, pl.value, ko.value
 
 
+    def replay_pack(self, moves, players):
+        """Play `moves` ((x, y) or PASS_MOVE) for `players` (BLACK / WHITE) on this state, packing the position in front of
+        every non-pass move: one library call for a whole game record (ag_state_replay_pack).  Returns (boards int8 (k, n),
+        ages uint8 (k, n), players int8 (k,), kos int16 (k,), illegal) with illegal = index into `moves` of the move that
+        was refused (the positions up to and including its own are returned), or None."""
+        m = len(moves)
+        n = self.size * self.size
+        pts = np.asarray([self._idx(mv) for mv in moves], np.int16).reshape(m)
+        col = np.asarray(players, np.int8).reshape(m)
+        b = np.empty((m, n), np.int8); a = np.empty((m, n), np.uint8)
+        pl = np.empty(m, np.int8); ko = np.empty(m, np.int16)
+        k = C.c_int(0)
+        rc = _lib.lib().ag_state_replay_pack(self._h, m, _lib.np_ptr(pts), _lib.np_ptr(col), _lib.np_ptr(b), _lib.np_ptr(a),
+                                             _lib.np_ptr(pl), _lib.np_ptr(ko), C.byref(k))
+        illegal = None
+        if rc != 0:
+            msg = _lib.last_error()
+            if "illegal move" not in msg:
+                raise _lib.AlphaGoB200Error("ag_state_replay_pack failed (%d): %s" % (rc, msg))
+            illegal = int(msg.rsplit("entry ", 1)[1].rstrip(")"))
+        return b[:k.value], a[:k.value], pl[:k.value], ko[:k.value], illegal
+
+
 def playout_positions(seed, n, size=19, max_moves=400, per_game=8):
     """Synthetic random-playout positions (uniform over sensible moves, AlphaGo/ai.py:15) as
     packed encoder inputs: board int8 (n, size*size), age uint8, player int8 (n,), ko int16 (n,)."""

@@ -5,6 +5,7 @@
 game trees, nodes, properties with `\\` escapes inside values; at every branching point the first variation is the
 main line).
 """
+import re
 import string
 
 from . import go
@@ -27,11 +28,13 @@ def unflatten_idx(idx, size):
 
 
 # ------------------------------------------------------------------------------------------ SGF main line
+_WS = re.compile(r"\s*")
+_IDENT = re.compile(r"[^\W\d_]+")                 # letters, as str.isalpha
+_PLAIN_VALUE = re.compile(r"\[([^\]\\]*)\]")     # a value without escapes: the common case, matched in one step
+
+
 def _skip_ws(s, i):
-    n = len(s)
-    while i < n and s[i].isspace():
-        i += 1
-    return i
+    return _WS.match(s, i).end()
 
 
 def _parse_value(s, i):
@@ -66,17 +69,23 @@ def _parse_node(s, i):
     props = {}
     i = _skip_ws(s, i + 1)
     n = len(s)
-    while i < n and s[i].isalpha():
-        j = i
-        while j < n and s[j].isalpha():
-            j += 1
-        ident = "".join(ch for ch in s[i:j] if ch.isupper())   # old files write e.g. "SiZe": only capitals count
-        i = _skip_ws(s, j)
+    while True:
+        m = _IDENT.match(s, i)
+        if m is None:
+            break
+        ident = m.group()
+        if not ident.isupper():
+            ident = "".join(ch for ch in ident if ch.isupper())   # old files write e.g. "SiZe": only capitals count
+        i = _skip_ws(s, m.end())
         if i >= n or s[i] != "[":
             raise ParseException("property %r has no value" % ident)
         values = props.setdefault(ident, [])
         while i < n and s[i] == "[":
-            v, i = _parse_value(s, i)
+            m = _PLAIN_VALUE.match(s, i)
+            if m is not None:
+                v, i = m.group(1), m.end()
+            else:
+                v, i = _parse_value(s, i)   # escapes, or an unterminated value (raises)
             values.append(v)
             i = _skip_ws(s, i)
     return props, i
@@ -150,6 +159,26 @@ def sgf_iter_states(sgf_string):
             raise UnboundLocalError("local variable 'move' referenced before assignment")   # what util.py:81 does
         yield (gs, move, player)
         gs.do_move(move, player)
+
+
+def sgf_move_list(sgf_string):
+    """(GameState after the root node's set-up, moves, players): what sgf_iter_states would play, as lists, for callers
+    that replay a whole record in one library call (GameState.replay_pack).  Same node rules as sgf_iter_states."""
+    nodes = sgf_main_line(sgf_string)
+    gs = _sgf_init_gamestate(nodes[0])
+    moves, players = [], []
+    have = False
+    move = player = None
+    for props in nodes[1:]:
+        if "W" in props:
+            move, player, have = _parse_sgf_move(props["W"][0]), go.WHITE, True
+        elif "B" in props:
+            move, player, have = _parse_sgf_move(props["B"][0]), go.BLACK, True
+        if not have:
+            raise UnboundLocalError("local variable 'move' referenced before assignment")   # what util.py:81 does
+        moves.append(move)
+        players.append(player)
+    return gs, moves, players
 
 
 def sgf_to_gamestate(sgf_string):

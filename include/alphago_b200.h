@@ -85,6 +85,14 @@ void ag_state_history(const ag_state* s, int16_t* h_hist);
 void ag_state_groups(ag_state* s, int16_t* h_gid, int16_t* h_stones, int16_t* h_libs);
 /* encoder inputs of this state */
 void ag_state_pack(const ag_state* s, int8_t* h_board, uint8_t* h_age, int8_t* h_player, int16_t* h_ko);
+/* A whole game record in one call: for i in [0, n_moves) -- if h_points[i] is not a pass (-1), pack the position as
+ * ag_state_pack does into slot k of the outputs (k counts up from 0), then play h_points[i] for h_colours[i] (+1 black,
+ * -1 white).  That is the loop of game_converter.convert_game over util.sgf_iter_states (game_converter.py:35-40,
+ * util.py:64-83) without a Python round trip per move.  Outputs hold up to n_moves positions of size*size points;
+ * *n_packed = positions written.  AG_ESTATE on an illegal move: the pairs up to and including that move's are kept,
+ * as the reference keeps what it had written (game_converter.py:111-112). */
+int ag_state_replay_pack(ag_state* s, int n_moves, const int16_t* h_points, const int8_t* h_colours, int8_t* h_boards,
+                         uint8_t* h_ages, int8_t* h_players, int16_t* h_kos, int* n_packed);
 /* the literal turns_since walk (preprocessing.py:20-43) for any (history, board) pair */
 void ag_age_from_history(int size, const int8_t* h_board, const int16_t* h_hist, int n_hist, uint8_t* h_age);
 /* n positions from seeded random playouts, uniform over get_legal_moves(include_eyes=False)
