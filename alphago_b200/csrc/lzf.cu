@@ -83,9 +83,12 @@ long long ag_lzf_compress(const uint8_t* in, size_t in_len, uint8_t* out, size_t
             if (l < 7) out[op++] = (uint8_t)((l << 5) | (dist >> 8));
             else { out[op++] = (uint8_t)((7u << 5) | (dist >> 8)); out[op++] = (uint8_t)(l - 7); }
             out[op++] = (uint8_t)(dist & 255);
-            // index the positions inside the match too (sparsely: every other one keeps long zero runs cheap)
+            // index the match's second position and its last two: enough for the next match to find its way back, and long
+            // runs (these planes are mostly zeros) cost three table writes instead of hundreds
             const size_t end = ip + len;
-            for (size_t q = ip + 1; q + 2 < in_len && q < end; q += 2) table[hash3(in + q)] = (uint32_t)(q + 1);
+            if (ip + 3 < in_len) table[hash3(in + ip + 1)] = (uint32_t)(ip + 2);
+            for (size_t q = end - 2; q < end; q++)
+                if (q > ip + 1 && q + 2 < in_len) table[hash3(in + q)] = (uint32_t)(q + 1);
             ip = end;
             lit_start = ip;
         } else {
