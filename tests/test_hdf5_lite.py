@@ -262,3 +262,57 @@ def test_converter_writes_the_reference_layout(golden_dir, tmp_path, monkeypatch
     assert f["states"].chunk == (64, 12, 19, 19) and f["actions"].chunk == (1024, 2) and f["states"].dtype == np.uint8
     got = {k: f["file_offsets"][k][:].tolist() for k in f["file_offsets"].keys()}
     assert [got[p.replace("/", ":")] for p in files] == [[int(o[0]), int(o[1])] for o in offsets]
+
+
+def test_round_trip_property(tmp_path):
+    """random shapes, dtypes, chunk shapes and filters: what the writer stores is what the reader returns"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    dtypes = [np.uint8, np.int8, np.int16, np.uint16, np.int32, np.int64, np.float32, np.float64]
+    counter = {"n": 0}
+
+    @settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @given(st.integers(1, 3).flatmap(lambda nd: st.tuples(st.lists(st.integers(0, 13), min_size=nd, max_size=nd),
+                                                         st.lists(st.integers(1, 6), min_size=nd, max_size=nd))),
+           st.sampled_from(dtypes), st.sampled_from([None, "lzf", "gzip"]), st.booleans(), st.integers(0, 2 ** 31 - 1))
+    def check(shape_chunks, dtype, compression, chunked, seed):
+        shape, chunks = tuple(shape_chunks[0]), tuple(shape_chunks[1])
+        rng = np.random.RandomState(seed)
+        data = (rng.randint(0, 3, shape) * rng.randint(0, 2, shape)).astype(dtype)   # sparse: compressible
+        counter["n"] += 1
+        path = str(tmp_path / ("p%d.h5" % counter["n"]))
+        kw = {}
+        if chunked or compression:
+            kw = dict(chunks=chunks, compression=compression, maxshape=(None,) + shape[1:])
+        with h5.File(path, "w") as f:
+            f.create_dataset("grp/d", data=data, **kw)
+            f["grp"].attrs["shape"] = list(shape)
+        r = h5.File(path)
+        d = r["grp/d"]
+        assert d.shape == shape and d.dtype == np.dtype(dtype)
+        assert np.array_equal(d[:], data)
+        if shape[0] > 0:
+            k = seed % shape[0]
+            assert np.array_equal(d[k], data[k]) and np.array_equal(d[k:], data[k:])
+        assert r["grp"].attrs["shape"].tolist() == list(shape)
+
+    check()
+
+
+def test_lzf_round_trip_property():
+    """whatever the compressor emits, both decoders give the input back; streams never exceed the input"""
+    from hypothesis import given, settings, strategies as st
+
+    pieces = st.one_of(st.binary(min_size=0, max_size=40),
+                       st.tuples(st.binary(min_size=1, max_size=5), st.integers(1, 400)).map(lambda t: t[0] * t[1]))
+
+    @settings(max_examples=150, deadline=None)
+    @given(st.lists(pieces, min_size=0, max_size=12).map(b"".join))
+    def check(raw):
+        enc = h5.lzf_encode(raw)
+        if enc is None:
+            return                      # not compressible (or shorter than 4 bytes): stored raw
+        assert len(enc) < len(raw)
+        assert h5.lzf_decode(enc, len(raw)) == raw and h5.lzf_decompress(enc, len(raw)) == raw
+
+    check()
