@@ -75,21 +75,3 @@ def test_leaf_queue_policy_only_and_errors():
     q.submit(go.GameState(9))
     with pytest.raises(ValueError):
         q.flush()
-
-
-def test_parallel_mcts_on_the_networks():
-    """the batched search (alphago_b200/mcts.py, ParallelMCTS) driven by the real networks: every wave's states go through
-    CNNPolicy / CNNValue.batch_eval_state (one encoder launch + one forward pass each)"""
-    from alphago_b200.mcts import ParallelMCTS
-    policy = CNNPolicy(DEFAULT_FEATURES, layers=3, filters_per_layer=32, seed=11, max_batch=16)
-    value = CNNValue(DEFAULT_FEATURES + ["color"], layers=3, filters_per_layer=32, seed=12, max_batch=16)
-    st = _states(1, 4)[0]
-    before = len(st.history)
-    search = ParallelMCTS(st, value.eval_state, policy.eval_state, None, lmbda=0, playout_depth=3, n_search=32, n_parallel=16)
-    move = search.get_move(st)
-    assert st.is_legal(move) and len(st.history) == before
-    visits = {a: n.nVisits for a, n in search.root.children.items() if n.nVisits}
-    assert sum(visits.values()) == 32 and max(visits, key=visits.get) == move
-    assert all(-1.0 <= n.Q_value <= 1.0 for n in search.root.children.values())
-    search.update_with_move(move)
-    assert search.root.parent is None
