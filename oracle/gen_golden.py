@@ -202,12 +202,200 @@ def export_reference_sgf_fixtures():
             print("copied", name)
 
 
+# ----------------------------------------------------------------------------------------------------------------------
+# stage-2 pieces of the reference that ARE runnable here (pure Python around the Keras calls)
+def _load_reference_policy_module():
+    """import AlphaGo/models/policy.py UNMODIFIED.  Its imports of keras (absent here) and of the third-party `sgf`
+    package (pulled in by AlphaGo/util.py:1) are satisfied by empty stand-in modules in sys.modules: none of the code
+    exercised below (policy.py:44-91) touches them."""
+    import types
+    ref_shim.load()
+    for name in ["keras", "keras.models", "keras.layers", "keras.layers.core", "keras.layers.convolutional",
+                 "keras.backend", "sgf"]:
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    km, kl = sys.modules["keras.models"], sys.modules["keras.layers"]
+    km.Sequential = km.model_from_json = None
+    kl.convolutional = sys.modules["keras.layers.convolutional"]
+    sys.modules["keras.layers.core"].Activation = sys.modules["keras.layers.core"].Flatten = None
+    sys.modules["keras"].backend = sys.modules["keras.backend"]
+    sys.modules["keras"].models, sys.modules["keras"].layers = km, kl
+    import AlphaGo.models.policy as pol
+    return pol
+
+
+def export_policy_glue():
+    """tests/golden/ref_policy_glue.npz: what CNNPolicy.eval_state / batch_eval_state / _select_moves_and_normalize
+    (policy.py:44-91) return, run UNMODIFIED on reference GameStates, with `forward` replaced by a table lookup (the
+    network itself needs Keras).  Recorded per case: the move lists that rebuild the states, the fake network output,
+    the moves asked for, and the reference's [(move, prob)] answers."""
+    go, pp = ref_shim.load()
+    pol = _load_reference_policy_module()
+    rng = np.random.RandomState(1444)
+    size = 19
+    policy = object.__new__(pol.CNNPolicy)
+    policy.preprocessor = pp.Preprocess(["board", "ones", "turns_since"])
+    # positions: seeded playouts; record move lists so that the product's GameState can replay them
+    games, states = [], []
+    for g in range(6):
+        gs = go.GameState(size)
+        nm = [0, 30, 120, 250, 330, 400][g]
+        for _ in range(nm):
+            mv = gs.get_legal_moves(include_eyes=False)
+            gs.do_move(mv[rng.randint(len(mv))] if mv else None)
+        games.append(np.asarray([-1 if m is None else m[0] * size + m[1] for m in gs.history], np.int16))
+        states.append(gs)
+    n = len(states)
+    net_out = rng.gamma(0.3, 1.0, size=(n, size * size)).astype(np.float32)
+    net_out /= net_out.sum(axis=1, keepdims=True)
+    seen = []
+
+    def fake_forward(inpt):
+        seen.append(inpt.shape)
+        assert inpt.shape[1:] == (12, size, size)
+        return net_out[:inpt.shape[0]] if inpt.shape[0] > 1 else net_out[fake_forward.row:fake_forward.row + 1]
+    fake_forward.row = 0
+    policy.forward = fake_forward
+    out = {"n_states": np.int32(n), "size": np.int32(size), "net_out": net_out}
+    for i, g in enumerate(games):
+        out["moves_%d" % i] = g
+
+    def flat(res):
+        res = list(res)
+        return (np.asarray([m[0] * size + m[1] for m, _ in res], np.int32), np.asarray([p for _, p in res], np.float64))
+    # batch_eval_state, default (legal) moves
+    res = policy.batch_eval_state(states)
+    for i in range(n):
+        out["batch_default_idx_%d" % i], out["batch_default_p_%d" % i] = flat(res[i])
+    # batch_eval_state with explicit move lists, incl. an empty one and a repeated move
+    asked = []
+    for i, gs in enumerate(states):
+        legal = gs.get_legal_moves()
+        if i == 1:
+            asked.append([])
+        elif i == 2:
+            asked.append([legal[0], legal[0], legal[-1]])
+        else:
+            asked.append([legal[j] for j in rng.permutation(len(legal))[:1 + 7 * i]])
+    res = policy.batch_eval_state(states, asked)
+    for i in range(n):
+        r = list(res[i]) if not isinstance(res[i], list) else res[i]
+        out["asked_%d" % i] = np.asarray([m[0] * size + m[1] for m in asked[i]], np.int32)
+        out["batch_asked_idx_%d" % i], out["batch_asked_p_%d" % i] = flat(r)
+    # eval_state one by one (default and explicit moves)
+    for i, gs in enumerate(states):
+        fake_forward.row = i
+        out["eval_default_idx_%d" % i], out["eval_default_p_%d" % i] = flat(policy.eval_state(gs))
+        out["eval_asked_idx_%d" % i], out["eval_asked_p_%d" % i] = flat(policy.eval_state(gs, asked[i])) \
+            if asked[i] else flat(policy.eval_state(gs, asked[i]))
+    # contracts
+    out["empty_batch_is_empty_list"] = np.int8(policy.batch_eval_state([]) == [])
+    try:
+        policy.batch_eval_state([go.GameState(19), go.GameState(13)])
+        out["mixed_size_error"] = np.asarray("")
+    except ValueError as e:
+        out["mixed_size_error"] = np.asarray(str(e))
+    np.savez_compressed(os.path.join(OUT, "ref_policy_glue.npz"), **out)
+    print("ref_policy_glue.npz written:", n, "states, forward calls", len(seen), "error text:", out["mixed_size_error"])
+
+
+def _exec_reference_lines(path, ranges, namespace):
+    """run line ranges (1-based, inclusive) of a reference source file as they stand.  supervised_policy_trainer.py as a
+    whole is Python 2 (print statement at :115) and imports keras/h5py; the pieces pinned here are valid Python 3."""
+    lines = open(path).read().split("\n")
+    for a, b in ranges:
+        exec(compile("\n" * (a - 1) + "\n".join(lines[a - 1:b]), path, "exec"), namespace)
+    return namespace
+
+
+def export_generator():
+    """tests/golden/ref_generator.npz: shuffled_hdf5_batch_generator + one_hot_action + BOARD_TRANSFORMATIONS
+    (supervised_policy_trainer.py:10-40,71-80) and MetadataWriterCallback (spt.py:43-68), executed from the reference
+    source by line range.  Records, for seeded np.random: the dataset, the index list (its length is NOT a multiple of
+    the batch, so batches straddle the wrap, spt.py:27-40), the data index and transform the generator used for every
+    sample, and the (X, Y) batches it yielded; each of the 8 transforms applied to an asymmetric plane; and the metadata
+    the callback holds after every epoch of two made-up histories."""
+    spt = os.path.join(ref_shim.REFERENCE_ROOT, "AlphaGo", "training", "supervised_policy_trainer.py")
+    ns = _exec_reference_lines(spt, [(10, 40), (71, 80)], {"np": np})
+    T = ns["BOARD_TRANSFORMATIONS"]
+    out = {}
+    rng = np.random.RandomState(99)
+    # each transform alone, on asymmetric arrays (19x19 and 7x7), and on a one-hot action
+    for size in (19, 7):
+        plane = rng.randint(0, 255, (size, size)).astype(np.uint8)
+        out["plane_%d" % size] = plane
+        out["plane_tf_%d" % size] = np.asarray([t(plane) for t in T])
+        acts = np.asarray([(0, 0), (0, size - 1), (2, 5), (size - 1, 3), (size // 2, size // 2)], np.uint8)
+        out["acts_%d" % size] = acts
+        out["acts_tf_%d" % size] = np.asarray([[int(np.argmax(t(ns["one_hot_action"](tuple(a), size)).flatten()))
+                                                 for a in acts] for t in T], np.int32)
+    # the generator
+    n_data, planes, size, batch = 37, 5, 19, 8
+    states = (rng.rand(n_data, planes, size, size) < 0.3).astype(np.uint8)
+    actions = rng.randint(0, size, (n_data, 2)).astype(np.uint8)
+    indices = rng.permutation(n_data)[:21]   # 21 indices, batch 8: the third batch straddles the wrap
+    log_idx, log_tf = [], []
+
+    class LoggedStates(object):
+        shape = states.shape
+
+        def __getitem__(self, i):
+            log_idx.append(int(i))
+            return states[i]
+
+    class LoggedActions(object):
+        def __getitem__(self, i):
+            return tuple(actions[i])   # the HDF5 row indexes the one-hot as (x, y): spt.py:14
+
+    def tagged(k):
+        def f(feature):
+            if feature.shape == (size, size) and (not log_tf or len(log_tf) < len(log_idx)):
+                log_tf.append(k)
+            return T[k](feature)
+        return f
+    np.random.seed(2016)
+    gen = ns["shuffled_hdf5_batch_generator"](LoggedStates(), LoggedActions(), indices, batch, [tagged(k) for k in range(8)])
+    X, Y = [], []
+    for _ in range(7):   # 56 samples = 2 full passes + 14
+        xb, yb = next(gen)
+        assert xb.dtype == np.float64 and yb.dtype == np.float64 and set(np.unique(xb)) <= {0.0, 1.0}
+        X.append(xb.astype(np.uint8).copy()); Y.append(yb.copy())   # the generator reuses its buffers (spt.py:24-25)
+    assert len(log_idx) == len(log_tf) == 7 * batch
+    out.update(gen_states=states, gen_actions=actions, gen_indices=indices.astype(np.int64), gen_batch=np.int32(batch),
+               gen_used_index=np.asarray(log_idx, np.int64), gen_used_transform=np.asarray(log_tf, np.uint8),
+               gen_X=np.asarray(X), gen_Y=np.asarray(Y, np.uint8))
+    # MetadataWriterCallback: best-epoch bookkeeping with and without val_loss
+    import json
+    import tempfile
+    ns2 = _exec_reference_lines(spt, [(43, 68)], {"np": np, "json": json, "Callback": object})
+    hist = {"with_val": [{"loss": 5.0, "acc": .01, "val_loss": 4.0, "val_acc": .02}, {"loss": 4.0, "acc": .02, "val_loss": 4.5, "val_acc": .03},
+                         {"loss": 3.0, "acc": .03, "val_loss": 3.5, "val_acc": .04}, {"loss": 2.5, "acc": .04, "val_loss": 3.5, "val_acc": .05}],
+            "without_val": [{"loss": 5.0, "acc": .01}, {"loss": 5.5, "acc": .02}, {"loss": 4.0, "acc": .03}]}
+    record = {}
+    for name, logs in hist.items():
+        with tempfile.TemporaryDirectory() as d:
+            cb = ns2["MetadataWriterCallback"](os.path.join(d, "metadata.json"))
+            after = []
+            for e, lg in enumerate(logs):
+                cb.on_epoch_end(e, dict(lg))
+                after.append(json.load(open(cb.file)))
+            record[name] = {"logs": logs, "after": after}
+    out["metadata_json"] = np.asarray(json.dumps(record))
+    np.savez_compressed(os.path.join(OUT, "ref_generator.npz"), **out)
+    print("ref_generator.npz written; used index", log_idx[:24], "transforms", log_tf[:16])
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "hdf5":
         export_reference_hdf5_fixture()
     elif len(sys.argv) > 1 and sys.argv[1] == "sgf":
         export_reference_sgf_fixtures()
+    elif len(sys.argv) > 1 and sys.argv[1] == "stage2":
+        export_policy_glue()
+        export_generator()
     else:
         main()
         export_reference_hdf5_fixture()
+        export_policy_glue()
+        export_generator()
 
