@@ -32,6 +32,22 @@ FEATS46 = ["board", "ones", "turns_since", "liberties", "capture_size", "self_at
 ENC_BYTES_PER_POSITION = 48 * 361 + 361 + 361 + 4  # planes out + board + age + player/ko
 
 
+def encode_config(n, feats, planes):
+    return {"workload": "feature-plane encoder, %d synthetic random-playout 19x19 positions/step, %d planes (%s)"
+            % (n, planes, ",".join(feats)),
+            "positions_per_step": n, "planes": planes,
+            "l2": "4 rotating input sets; each step streams %d MB of output planes through the 126 MB L2"
+            % (n * planes * 361 // 2 ** 20)}
+
+
+def train_config(batch, dataset=4096):
+    return {"workload": "AlphaGo SL policy net (13 convs: 5x5 + 11x 3x3 + 1x1, 192 filters, 48 planes) bf16 training step, "
+                        "batch %d per GPU, device-side D4 augmentation, SGD lr decay" % batch,
+            "per_gpu_batch": batch, "planes": 48,
+            "l2": "each step touches ~1 GB of activations/gradients (> 126 MB L2); dataset of %d positions rotates" % dataset,
+            "data": "planes from the CUDA encoder on random-playout positions, labels uniform over legal moves"}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -167,11 +183,7 @@ class EncodeWorkload(object):
                 "algorithmic_bytes_per_launch": self.n * ENC_BYTES_PER_POSITION}
 
     def config(self):
-        return {"workload": "feature-plane encoder, %d synthetic random-playout 19x19 positions/step, %d planes (%s)"
-                % (self.n, self.pp.output_dim, ",".join(self.feats)),
-                "positions_per_step": self.n, "planes": self.pp.output_dim,
-                "l2": "4 rotating input sets; each step streams %d MB of output planes through the 126 MB L2"
-                % (self.n * self.pp.output_dim * 361 // 2 ** 20)}
+        return encode_config(self.n, self.feats, self.pp.output_dim)
 
     def cpu_baseline(self, sample=2048):
         from oracle import go_oracle as og
@@ -294,30 +306,87 @@ class TrainWorkload(object):
                          "frac_of_burst_peak": round(flop / (ms * 1e-3) / 1e12 / pk["tensor_burst"], 4), "flop": flop}
         return out
 
-    def roofline(self, ms_per_step, pk):
+    def in_step_durations(self, steps=10):
+        """per-kernel durations INSIDE the running step (CUPTI through torch.profiler, after the timed region): the
+        same kernels timed alone run at burst clocks with a warm L2, inside the step they follow each other"""
+        t = self.torch
+        try:
+            from torch.profiler import ProfilerActivity, profile
+            for _ in range(3):
+                self.step()
+            t.cuda.synchronize()
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                for _ in range(steps):
+                    self.step()
+                t.cuda.synchronize()
+            acc = {}
+            evs = [e for e in prof.events() if e.time_range is not None and "cuda" in str(e.device_type).lower()]
+            for e in sorted(evs, key=lambda e: e.time_range.start):
+                name = e.name.split("(")[0].split("::")[-1].split("<")[0].strip()
+                if name.startswith("Memcpy") or name.startswith("Memset"):
+                    continue
+                acc.setdefault(name, []).append(e.time_range.end - e.time_range.start)
+            out = {}
+            for k, v in acc.items():
+                lps = len(v) // steps if len(v) % steps == 0 else 0
+                out[k] = {"us_per_step": round(sum(v) / steps, 2), "launches_per_step": round(len(v) / steps, 2)}
+                if 1 <= lps <= 4:   # the i-th launch of this kernel in a step, averaged over the steps
+                    out[k]["us_each"] = [round(sum(v[o::lps]) / steps, 2) for o in range(lps)]
+            return out
+        except Exception as e:  # the profiler is an aid: the bench line does not depend on it
+            return {"unavailable": str(e)[:120]}
+
+    def sustained(self, seconds=2.2, ms_per_step=1.7):
+        """the same step for >= `seconds` back to back with its own clock samples: the power governor settles (the SM clock
+        drops to ~1.65 GHz), which is what the sustained cuBLAS peak was measured under"""
+        t = self.torch
+        steps = int(seconds / (ms_per_step * 1e-3)) + 1
+        sampler = ClockSampler(t.cuda.current_device())
+        sampler.start()
+        e0, e1 = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
+        t.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            self.step()
+        e1.record()
+        t.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        return steps, ms, sampler.stop()
+
+    def roofline(self, ms_per_step, pk, steps=100, world=1, sustained=None):
         ach = self.batch * TRAIN_FLOP_PER_POSITION / (ms_per_step * 1e-3) / 1e12
         k = self.kernel_rooflines(pk)
         name = next(iter(k))   # the forward chain when the net runs chained, else the single-layer forward kernel
         dom = k[name]
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
-        if os.path.exists(tp):  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
-            traffic = json.load(open(tp)).get(name.split("(")[0], {}).get("dram_bytes_per_launch")
-        return {"bound": "tensor", "achieved": dom["tflops"], "peak": pk["tensor_burst"], "unit": "TFLOP/s",
-                "frac": dom["frac_of_burst_peak"], "traffic": traffic,
-                "kernel": "ag::" + name + ", timed alone (20 launches back to back)",
-                "peak_source": pk["source"] + " (cuBLAS bf16 burst, kernel timed alone)",
-                "algorithmic_flops_per_launch": dom["flop"],
-                "whole_step": {"achieved": round(ach, 1), "peak": pk["tensor_sustained"], "frac": round(ach / pk["tensor_sustained"], 4),
-                               "unit": "TFLOP/s", "note": "8.2380 GFLOP/position over the whole step vs sustained peak"},
-                "kernels": k}
+        for tp in ("r2_traffic.json", "r1_traffic.json"):
+            tp = os.path.join(ROOT, "profiles", tp)
+            if os.path.exists(tp):  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
+                traffic = json.load(open(tp)).get(name.split("(")[0], {}).get("dram_bytes_per_launch")
+                break
+        # the whole step against the peak that matches its timed region: a region shorter than a second runs at burst clocks
+        region_s = steps * ms_per_step * 1e-3
+        kind = "tensor_burst" if region_s < 1.0 else "tensor_sustained"
+        out = {"bound": "tensor", "achieved": dom["tflops"], "peak": pk["tensor_burst"], "unit": "TFLOP/s",
+               "frac": dom["frac_of_burst_peak"], "traffic": traffic,
+               "kernel": "ag::" + name + ", timed alone (20 launches back to back)",
+               "peak_source": pk["source"] + " (cuBLAS bf16 burst, kernel timed alone)",
+               "algorithmic_flops_per_launch": dom["flop"],
+               "whole_step": {"achieved": round(ach, 1), "peak": pk[kind], "frac": round(ach / pk[kind], 4), "unit": "TFLOP/s",
+                              "peak_kind": kind, "timed_region_s": round(region_s, 3),
+                              "note": "8.2380 GFLOP/position over the whole step (all %d launches) vs the peak measured under "
+                                      "the same conditions as the timed region" % (self.launches_per_step or 0)},
+               "kernels": k}
+        if sustained is not None:
+            n, ms, clocks = sustained
+            a = self.batch * TRAIN_FLOP_PER_POSITION * n / (ms * 1e-3) / 1e12
+            out["whole_step_sustained"] = {"achieved": round(a, 1), "peak": pk["tensor_sustained"], "unit": "TFLOP/s",
+                                           "frac": round(a / pk["tensor_sustained"], 4), "steps": n, "seconds": round(ms * 1e-3, 3),
+                                           "positions_per_sec_per_gpu": round(self.batch * n / (ms * 1e-3), 1), "clocks": clocks}
+        return out
 
     def config(self):
-        return {"workload": "AlphaGo SL policy net (13 convs: 5x5 + 11x 3x3 + 1x1, 192 filters, 48 planes) bf16 training step, "
-                            "batch %d per GPU, device-side D4 augmentation, SGD lr decay" % self.batch,
-                "per_gpu_batch": self.batch, "planes": 48,
-                "l2": "each step touches ~1 GB of activations/gradients (> 126 MB L2); dataset of %d positions rotates" % self.dataset,
-                "data": "planes from the CUDA encoder on random-playout positions, labels uniform over legal moves"}
+        return train_config(self.batch, self.dataset)
 
     def cpu_baseline(self):
         import torch
@@ -325,10 +394,10 @@ class TrainWorkload(object):
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         params = no.make_params(48, [192] * 12, [5] + [3] * 11, seed=1)
-        bs = 16
+        bs = self.batch   # whole minibatches of the step's own data
         x = self.h_states[:bs]
         y = self.h_actions[:bs, 0].astype("int64") * 19 + self.h_actions[:bs, 1]
-        no.loss_and_grads(params, x[:2], y[:2])
+        no.loss_and_grads(params, x[:8], y[:8])
         t = time.time()
         steps = 0
         while time.time() - t < 10 or steps < 1:
@@ -345,8 +414,8 @@ def reference_arm(args, rank, workload):
     """The reference arm: the reference's own CPU algorithm for the path on the host cores, same metric/config as our
     arm.  The reference's Python (8 ms/position encoder) cannot travel to the GPU box and its Keras 1.0/Theano 0.8
     stack is not installable, so this is the oracle port: oracle/go_oracle.c (OpenMP over all cores) for `encode`,
-    the fp32 torch-CPU restatement of the network (oracle/nn_oracle.py, all cores) for `train`.  Each step is a
-    bounded sample of the workload."""
+    the fp32 torch-CPU restatement of the network (oracle/nn_oracle.py, all cores) for `train`.  Each step is the
+    whole step of the repo arm (256 positions of training, 16384 of encoding: about 1-2 s of host time each)."""
     if rank != 0:
         return
     import numpy as np
@@ -354,38 +423,38 @@ def reference_arm(args, rank, workload):
     cores = os.cpu_count() or 1
     if workload == "encode":
         feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
-        sample = 1024
+        sample = args.positions   # the whole step: same configuration as the repo arm
         b, a, pl, ko = og.playout_positions(1000, sample, size=19, max_moves=400, per_game=16)
         for _ in range(args.warmup):
-            og.encode_batch(b[:128], a[:128], pl[:128], ko[:128], 19, feats, threads=cores)
+            og.encode_batch(b[:256], a[:256], pl[:256], ko[:256], 19, feats, threads=cores)
         t = time.time()
         for _ in range(args.steps):
             og.encode_batch(b, a, pl, ko, 19, feats, threads=cores)
         dt = time.time() - t
         metric, dtype = EncodeWorkload.metric, "u8"
-        cfg = {"workload": "feature-plane encoder on host cores, %d of the 16384 positions per step, %d planes" % (sample, og.output_dim(feats))}
-        how = "%d positions per step, C oracle (oracle/go_oracle.c) with OpenMP over all host cores" % sample
+        cfg = encode_config(sample, feats, og.output_dim(feats))
+        how = "all %d positions of the step, C oracle (oracle/go_oracle.c) with OpenMP over all host cores" % sample
     else:
         import torch
         from oracle import nn_oracle as no
         torch.set_num_threads(cores)
-        sample = 16
+        sample = args.batch       # the whole minibatch: same configuration as the repo arm
         params = no.make_params(48, [192] * 12, [5] + [3] * 11, seed=1)
         rng = np.random.RandomState(0)
         b, a, pl, ko = og.playout_positions(500, sample, size=19, max_moves=400, per_game=16)
         x = og.encode_batch(b, a, pl, ko, 19, og.DEFAULT_FEATURES, threads=cores)
         y = rng.randint(0, 361, sample)
-        for _ in range(args.warmup):
-            no.loss_and_grads(params, x[:2], y[:2])
+        for _ in range(min(args.warmup, 2)):
+            no.loss_and_grads(params, x[:8], y[:8])
         t = time.time()
         for _ in range(args.steps):
             _, _, grads, _ = no.loss_and_grads(params, x, y)
             params, _ = no.sgd_update(params, grads, 0.003)
         dt = time.time() - t
         metric, dtype = TrainWorkload.metric, "f32"
-        cfg = {"workload": "AlphaGo SL policy net (13 convs, 192 filters, 48 planes) training step on host cores, "
-                           "%d of the 256 positions per step" % sample}
-        how = "%d positions per step, fp32 torch-CPU restatement of the same net and SGD step, all host cores" % sample
+        cfg = train_config(sample)
+        how = ("all %d positions of the step, fp32 torch-CPU restatement of the same net and SGD step (oracle/nn_oracle.py), "
+               "all host cores; the reference's Keras 1.0 / Theano 0.8 stack is not installable here" % sample)
     v = round(args.steps * sample / dt, 2)
     line = {"impl": "reference", "metric": metric, "value": v, "unit": "positions/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True,
@@ -407,6 +476,7 @@ def main():
     ap.add_argument("--planes", type=int, default=48, choices=[46, 48])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-encoder", action="store_true")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the 2 s sustained run and the in-step kernel timeline")
     args = ap.parse_args()
     rank, world, local = dist_env()
     workload = args.workload or "train"
@@ -434,9 +504,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from alphago_b200 import _lib
-    from oracle import go_oracle as og
 
-    feats = FEATS46 if args.planes == 46 else og.DEFAULT_FEATURES
+    feats = FEATS46 if args.planes == 46 else TRAIN_FEATS
     if workload == "train":
         wl = TrainWorkload(args.batch, rank)
     else:
@@ -492,11 +561,40 @@ def main():
     e2e = {"value": round(world * wl.units_per_step * ke / te, 1), "unit": wl.unit, "h2d_bytes_per_step": wl.h2d,
            "d2h_bytes_per_step": wl.d2h, "steps": ke}
 
+    sustained = in_step = None
+    if workload == "train" and not args.no_sustained:
+        # every rank runs these (the step holds a collective when world > 1); only rank 0 reports them
+        wl.launches_per_step = int(launches) // max(1, args.steps)
+        sustained = wl.sustained(2.2, ms_per_step)
+        barrier()
+        in_step = wl.in_step_durations()
+        barrier()
+
     if rank == 0:
+        if workload == "train":
+            roof = wl.roofline(ms_per_step, pk, steps=args.steps, world=world, sustained=sustained)
+            if in_step is not None:
+                roof["in_step"] = in_step
+                for kname, kv in roof["kernels"].items():   # the in-step figure beside the timed-alone one
+                    base = kname.split("(")[0].split("+")[0]
+                    each = in_step.get(base, {}).get("us_each") if isinstance(in_step.get(base), dict) else None
+                    if not each or "one layer" in kname:
+                        continue
+                    which = 1 if ("data gradients" in kname and len(each) > 1) else 0
+                    kv["in_step_ms"] = round(each[which] / 1e3, 4)
+                dom = next(iter(roof["kernels"].values()))
+                if "in_step_ms" in dom:
+                    a = dom["flop"] / (dom["in_step_ms"] * 1e-3) / 1e12
+                    roof["in_step_frac"] = {"achieved": round(a, 1), "ms": dom["in_step_ms"],
+                                            "frac_of_burst_peak": round(a / pk["tensor_burst"], 4),
+                                            "frac_of_sustained_peak": round(a / pk["tensor_sustained"], 4),
+                                            "note": "the dominant kernel's duration inside the running step (CUPTI)"}
+        else:
+            roof = wl.roofline(ms_per_step, pk)
         line = {"metric": wl.metric, "value": round(value, 1), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic", "config": wl.config(),
-                "roofline": wl.roofline(ms_per_step, pk), "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+                "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = wl.cpu_baseline()
         if workload == "train" and not args.no_encoder:
