@@ -23,6 +23,7 @@ def bind(L):
     L.ag_net_train_step.argtypes = [vp, vp, vp, i, C.c_float, C.c_float, vp, vp]
     L.ag_net_debug_read.argtypes = [vp, i, i, i, vp]
     L.ag_net_run_layer.argtypes = [vp, i, i, i, vp]
+    L.ag_debug_hold_sms.argtypes = [i, C.c_longlong, vp]
     L.ag_wgrad_scratch_bytes.restype = C.c_size_t
     L.ag_wgrad_scratch_bytes.argtypes = [i, i, i, C.c_longlong]
     L.ag_wgrad_partial_bytes.restype = C.c_size_t

@@ -35,12 +35,23 @@ bool pdl_enabled() {
     return v == 1;
 }
 
+bool chain_coop_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("AG_CHAIN_COOP"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
+
+int current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+    return dev < kMaxDevices ? dev : kMaxDevices - 1;
+}
+
 int sm_count() {
-    static int n = 0;
+    static PerDevice<int> cache;
+    int& n = cache.cur();
     if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, current_device()) != cudaSuccess || n <= 0) n = 148;
     }
     return n;
 }

@@ -30,7 +30,17 @@ void count_launch(int n = 1);
         if (_e != cudaSuccess) return ::ag::cuda_fail(_e, name);     \
     } while (0)
 
-int sm_count();
+int sm_count();   // of the CURRENT device
+
+// One process may drive several GPUs (one thread or one net per device): everything the launchers cache about a device
+// (shared-memory opt-ins, occupancy answers, symbol addresses) is kept per device ordinal, never process-wide.
+constexpr int kMaxDevices = 64;
+int current_device();   // cudaGetDevice(), clamped to [0, kMaxDevices)
+template <typename T>
+struct PerDevice {
+    T v[kMaxDevices] = {};
+    T& cur() { return v[current_device()]; }
+};
 
 // Programmatic dependent launch: every kernel of the training step is launched with the stream-serialization
 // attribute, raises `launch_dependents` on entry and does its set-up (barrier init, TMEM allocation, descriptor
@@ -58,13 +68,23 @@ template <typename... P, typename... A>
 inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
     return launch_k_opt(true, kernel, grid, block, smem, stream, args...);
 }
-// for kernels whose CTAs wait for each other (the layer chains): launched only once everything before them in the stream has
-// finished and left the SMs, so the whole grid becomes resident at once
+// For kernels whose CTAs wait for each other (the layer chains): a COOPERATIVE launch.  The runtime refuses a grid that
+// cannot be co-resident on the device (cudaErrorCooperativeLaunchTooLarge: the caller falls back to per-layer kernels) and
+// the hardware starts the grid only as a whole, so CTAs never spin on CTAs that have no SM yet -- whatever else runs on
+// the device (another net on a second stream, NCCL's CTAs, the encoder).  Never a programmatic-dependent-launch secondary:
+// starting early behind the kernel in front is exactly the piecemeal residency this rules out.  AG_CHAIN_COOP=0 falls back to
+// a plain launch (for A/B measurements only).
+bool chain_coop_enabled();
 template <typename... P, typename... A>
 inline cudaError_t launch_k_whole(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
-    static int early = -1;
-    if (early < 0) { const char* e = getenv("AG_CHAIN_PDL"); early = (e && e[0] == '1') ? 1 : 0; }
-    return launch_k_opt(early == 1, kernel, grid, block, smem, stream, args...);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = chain_coop_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, P(args)...);
 }
 #endif
 

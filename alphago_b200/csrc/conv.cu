@@ -785,7 +785,8 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         const int win_rows = tmap_a_win && conv_window_enabled() ? conv_window_rows(args.off, args.taps) : 0;
         if (win_rows) {
             // one activation window per channel slice, taps as row-shifted descriptor starts
-            static size_t configured3 = 0;
+            static PerDevice<size_t> configured3_dev;
+            size_t& configured3 = configured3_dev.cur();
             int bstages = kMaxBStages;
             while (bstages > 2 && conv_win_smem_bytes(args.n, win_rows, bstages) > 227 * 1024) bstages--;
             size_t smem = conv_win_smem_bytes(args.n, win_rows, bstages);
@@ -804,7 +805,8 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
                 return AG_OK;
             }
         }
-        static size_t configured2 = 0;
+        static PerDevice<size_t> configured2_dev;
+        size_t& configured2 = configured2_dev.cur();
         int stages = kMaxStages;
         while (stages > 2 && conv_pair_smem_bytes(args.n, stages) > 227 * 1024) stages--;
         size_t smem = conv_pair_smem_bytes(args.n, stages);
@@ -819,7 +821,8 @@ int conv_gemm_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const
         AG_LAUNCH_CHECK("conv_gemm_pair_kernel");
         return AG_OK;
     }
-    static size_t configured = 0;
+    static PerDevice<size_t> configured_dev;
+    size_t& configured = configured_dev.cur();
     const int stages = conv_stages(args.n);
     size_t smem = conv_smem_bytes(args.n, stages);
     if (smem > 227 * 1024) { set_error("conv: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
@@ -854,8 +857,10 @@ int conv_chain_launch(const ChainParams& P, unsigned int* d_flags, unsigned int 
     // the first waits for tiles of the second's pair), so ask for more than half of the SM's shared memory
     if (smem < 120 * 1024) smem = 120 * 1024;
     if (smem > 227 * 1024) { set_error("conv chain: %zu bytes of shared memory needed", smem); return AG_EINVAL; }
-    static size_t configured = 0;
-    static int max_clusters = 0;
+    static PerDevice<size_t> configured_dev;
+    static PerDevice<int> max_clusters_dev;
+    size_t& configured = configured_dev.cur();
+    int& max_clusters = max_clusters_dev.cur();
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(conv_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
@@ -869,8 +874,13 @@ int conv_chain_launch(const ChainParams& P, unsigned int* d_flags, unsigned int 
     int clusters = sm_count() / 2;
     if (clusters > max_clusters) clusters = max_clusters;
     if (clusters > P.total_tiles) clusters = P.total_tiles;
-    if (clusters < 1) { set_error("conv chain: no CTA pair fits on this device"); return AG_ECUDA; }
-    launch_k_whole(conv_chain_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, P, d_flags, epoch, win_bytes, b_bytes, bstages);
+    if (clusters < 1) { set_error("conv chain: no CTA pair fits on this device"); return AG_ESTATE; }
+    cudaError_t e = launch_k_whole(conv_chain_kernel, dim3(2 * clusters), dim3(kThreads), smem, stream, P, d_flags, epoch, win_bytes, b_bytes, bstages);
+    if (e == cudaErrorCooperativeLaunchTooLarge || e == cudaErrorNotSupported) {   // the grid cannot be co-resident here: not an error of the stream
+        (void)cudaGetLastError();
+        set_error("conv chain: %d CTA pairs cannot be co-resident on this device (%s)", clusters, cudaGetErrorString(e));
+        return AG_ESTATE;
+    }
     AG_LAUNCH_CHECK("conv_chain_kernel");
     return AG_OK;
 }

@@ -21,6 +21,8 @@
 // the integer work in steps 2-5 is what the kernel spends its time on.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "encode.cuh"
 #include "ladder.cuh"
@@ -413,7 +415,8 @@ size_t encode_smem_bytes() { return sizeof(enc::WarpMem) * enc::WARPS; }
 
 int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player, const int16_t* ko, int npos, int size,
                   const enc::PlaneTable& tab, uint8_t* out, cudaStream_t stream) {
-    static bool configured = false;
+    static PerDevice<bool> configured_dev;
+    bool& configured = configured_dev.cur();
     size_t smem = encode_smem_bytes();
     if (!configured) {
         AG_CUDA(cudaFuncSetAttribute(enc::encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -431,10 +434,12 @@ int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player,
         if (tab.arr[j] == enc::C_LADCAP && cap_plane < 0) cap_plane = j;
         if (tab.arr[j] == enc::C_LADESC && esc_plane < 0) esc_plane = j;
     }
-    static unsigned int* counters = nullptr;
-    static unsigned next_counter = 0;
+    // the symbol's address differs per device; the ring position is shared by host threads
+    static PerDevice<unsigned int*> counters_dev;
+    static std::atomic<unsigned> next_counter{0};
+    unsigned int*& counters = counters_dev.cur();
     if (!counters) AG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_ladder_counters));
-    unsigned int* ctr = counters + (next_counter++ & 15);
+    unsigned int* ctr = counters + (next_counter.fetch_add(1) & 15);
     AG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned int), stream));
     // enough work units to fill the machine even for a handful of positions; and never whole positions: the launch ends with
     // the slowest unit, and one position can hold several deep read-outs

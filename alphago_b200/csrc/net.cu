@@ -25,6 +25,17 @@ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // uint8 planes [n][C][S][S] (the encoder's / HDF5 layout) -> bf16 padded-pixel rows [n*img_stride][64k]
 // for the first conv layer; channels >= C and pad slots stay zero (buffer zero-filled once).
+__global__ void hold_sm_kernel(long long ns) {
+    extern __shared__ uint8_t hold_smem[];
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    do {
+        __nanosleep(1000);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    } while ((long long)(t - t0) < ns);
+    if (ns < 0) hold_smem[threadIdx.x] = 0;
+}
+
 __global__ void pack_input_kernel(const uint8_t* __restrict__ planes, int n, int C, int S, PixelLayout L, int ld,
                                   bf16* __restrict__ out) {
     pdl_trigger();
@@ -504,6 +515,8 @@ struct ag_net {
     unsigned int chain_epoch_fwd = 0, chain_epoch_bwd = 0;
     int chain_win_rows = 0, chain_nmax_fwd = 0, chain_nmax_bwd = 0;
     bool dgrad_chain_done = false;  // the data-gradient chain of the current forward_loss has been queued
+    bool wgrad_chain_refused = false;   // a chained weight-gradient launch was refused (grid not co-resident): stay on per-layer kernels
+    int chain_fallbacks = 0;        // chained launches the device refused, each answered by the per-layer kernels
     // head
     float *hw = nullptr, *hb = nullptr, *hpos = nullptr;       // 1x1 conv w[ld], b[1], position bias[pts] (optional)
     float *vhw = nullptr, *vhb = nullptr, *vhpos = nullptr;    // velocities
@@ -682,7 +695,7 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
         w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
         const int wg_tiles = (c.taps * (c.ldout / 64) + 3) / 4;   // the chained kernel keeps whole-accumulator partials: 256 rows x kin per tile
-        c.wgrad_chain = wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && wg_tiles <= kWgradCounterStride &&
+        c.wgrad_chain = !net->wgrad_chain_refused && wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && wg_tiles <= kWgradCounterStride &&
                         (size_t)c.wgrad_splits * wg_tiles * 256 * c.kin <= net->wgrad_scratch_floats;
     }
     // the arrival counters count in units of this batch's split factors: start over.  (Batch-size changes are rare; the device
@@ -865,7 +878,14 @@ void ag_net_destroy(ag_net* net) {
 int ag_net_layer_info(const ag_net* net, int layer, int field) {
     if (layer < 0 || layer >= net->n_conv) return -1;
     const ConvLayer& c = net->L[layer];
-    switch (field) { case 0: return c.cin; case 1: return c.cout; case 2: return c.width; case 3: return c.kin; case 4: return c.ldout; }
+    switch (field) {
+        case 0: return c.cin; case 1: return c.cout; case 2: return c.width; case 3: return c.kin; case 4: return c.ldout;
+        case 5: return net->chain_fwd ? 1 : 0;                       // forward runs inside the chained launch
+        case 6: return (net->chain_bwd && layer > 0) ? 1 : 0;        // its data gradient does
+        case 7: return (c.wgrad_chain && net->wgrad_n > 0) ? 1 : 0;  // its weight gradient does (known after a forward_loss)
+        case 8: return net->chain_fallbacks;                         // chained launches refused so far (whole net)
+        case 9: return c.wgrad_splits;                               // split-K factor planned for its weight gradient
+    }
     return -1;
 }
 
@@ -977,9 +997,12 @@ static int net_conv_stack(ag_net* net, const uint8_t* d_planes, int n, cudaStrea
         ++net->chain_epoch_fwd;
         for (const ChainParams& P : net->chain_fwd_p) {
             rc = conv_chain_launch(P, net->chain_flags_fwd, net->chain_epoch_fwd, net->chain_win_rows, net->chain_nmax_fwd, st);
+            if (rc == AG_ESTATE) break;   // the device cannot hold the whole grid at once: per-layer kernels from here on
             if (rc) return rc;
         }
-        return AG_OK;
+        if (rc == AG_OK) return AG_OK;
+        net->chain_fwd = false;
+        net->chain_fallbacks++;
     }
     for (int l = 0; l < net->n_conv; l++) {
         ConvLayer& c = net->L[l];
@@ -1098,6 +1121,16 @@ static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) 
         w.ldout = first.ldout; w.kin = first.kin; w.splits = first.wgrad_splits;
         w.kb_img = wgrad_kb_img(first.lin, first.tm_wg.krows); w.img_stride = first.lin.img_stride;
         int rc = wgrad_chain_launch(w, e, cnt, st);
+        if (rc == AG_ESTATE) {   // refused (grid not co-resident): these and all later layers use their own kernel + reduce
+            net->wgrad_chain_refused = true;
+            net->chain_fallbacks++;
+            for (auto& c : net->L) c.wgrad_chain = false;
+            for (int k = l + cnt; k > l; k--) {
+                rc = net_wgrad_one(net, k, n, st);
+                if (rc) return rc;
+            }
+            continue;
+        }
         if (rc) return rc;
     }
     return AG_OK;
@@ -1122,11 +1155,19 @@ int ag_net_backward_range(ag_net* net, int hi, int lo, int n, void* stream) {
             ++net->chain_epoch_bwd;
             for (const ChainParams& P : net->chain_bwd_p) {
                 rc = conv_chain_launch(P, net->chain_flags_bwd, net->chain_epoch_bwd, net->chain_win_rows, net->chain_nmax_bwd, st);
+                if (rc == AG_ESTATE) break;
                 if (rc) return rc;
             }
-            net->dgrad_chain_done = true;
+            if (rc == AG_ESTATE) {   // refused: the data gradients go layer by layer, this range now and the others as they come
+                if (hi != net->n_conv - 1) { set_error("data-gradient chain refused after part of the backward pass was queued"); return AG_ESTATE; }
+                net->chain_bwd = false;
+                net->chain_fallbacks++;
+            } else {
+                net->dgrad_chain_done = true;
+            }
         }
-    } else {
+    }
+    if (!net->chain_bwd) {
         for (int l = hi; l >= lo && l > 0; l--) {  // data gradient of layer l into the layer below (needs only G of layer l)
             ConvLayer& c = net->L[l];
             ConvArgs a;
@@ -1243,6 +1284,22 @@ int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream) {
     }
     set_error("ag_net_run_layer: mode %d not available for layer %d", mode, layer);
     return AG_EINVAL;
+}
+
+// Test hook: `ctas` CTAs that each take an SM's worth of shared memory and sit there for `microseconds` (globaltimer), on
+// `stream`.  Lets a test put the chained launches next to a kernel that holds SMs (what another net, NCCL or a torch op on
+// a second stream does in production).  Bounded: at most 5 s.
+int ag_debug_hold_sms(int ctas, long long microseconds, void* stream) {
+    if (ctas < 1 || ctas > 1024 || microseconds < 0 || microseconds > 5000000) { set_error("ag_debug_hold_sms: bad argument"); return AG_EINVAL; }
+    static PerDevice<bool> configured;
+    const int smem = 160 * 1024;   // more than half an SM: one holder per SM
+    if (!configured.cur()) {
+        AG_CUDA(cudaFuncSetAttribute(hold_sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured.cur() = true;
+    }
+    hold_sm_kernel<<<ctas, 32, smem, (cudaStream_t)stream>>>(microseconds * 1000);
+    AG_LAUNCH_CHECK("hold_sm_kernel");
+    return AG_OK;
 }
 
 // Test/debug readback (synchronous): output activations of conv layer `layer` (kind 0) or the

@@ -699,7 +699,8 @@ int wgrad_launch(const WgradMaps& maps, WgradArgs args, float* dw, float* db, cu
     args.tiles = wgrad_tiling(args.taps, args.ldout, args.kin, &args.tpg, &args.groups);
     if (args.splits < 1) args.splits = 1;
     if (args.kb_img && (args.img_stride < 1 || args.m_total % args.img_stride != 0 || args.kb_img * maps.krows > args.img_stride)) args.kb_img = 0;
-    static size_t configured = 0;
+    static PerDevice<size_t> configured_dev;
+    size_t& configured = configured_dev.cur();
     if (!db || args.kin + 16 > 256) args.bias_scratch = nullptr;
     if (db && !args.bias_scratch) { set_error("wgrad: bias gradient needs bias_scratch and kin <= 240"); return AG_EINVAL; }
     args.krows = maps.krows;
@@ -761,12 +762,18 @@ int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_lay
     const int stages = wgrad_stages(args.taps, args.kin, with_bias, args.krows, args.win_rows);
     size_t smem = wgrad_smem_bytes(args.taps, args.kin, with_bias, args.krows, args.win_rows);
     if (smem < 120 * 1024) smem = 120 * 1024;  // one CTA per SM (see wgrad_chain_ok)
-    static size_t configured = 0;
+    static PerDevice<size_t> configured_dev;
+    size_t& configured = configured_dev.cur();
     if (smem > configured) {
         AG_CUDA(cudaFuncSetAttribute(wgrad_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    launch_k_whole(wgrad_chain_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, P, stages);
+    cudaError_t e = launch_k_whole(wgrad_chain_kernel, dim3(args.tiles * args.splits), dim3(kThreads), smem, stream, P, stages);
+    if (e == cudaErrorCooperativeLaunchTooLarge || e == cudaErrorNotSupported) {   // the grid cannot be co-resident here: not an error of the stream
+        (void)cudaGetLastError();
+        set_error("wgrad chain: %d CTAs cannot be co-resident on this device (%s)", args.tiles * args.splits, cudaGetErrorString(e));
+        return AG_ESTATE;
+    }
     AG_LAUNCH_CHECK("wgrad_chain_kernel");
     return AG_OK;
 }

@@ -131,6 +131,16 @@ class ConvNet(object):
         """backward of layers hi .. lo in one call (descending ranges after forward_loss): equal layers share chained launches"""
         _lib.check(_lib.lib().ag_net_backward_range(self._h, hi, lo, n, _lib.current_stream()), "ag_net_backward_range")
 
+    def launch_plan(self):
+        """how the layers are launched: {"fwd": [...], "dgrad": [...], "wgrad": [...]} = layers inside the chained launches,
+        "refused": chained launches the device refused so far, "splits": split-K factor per layer (after a forward_loss)"""
+        L, h = _lib.lib(), self._h
+        rng = range(self.n_conv)
+        return {"fwd": [l for l in rng if L.ag_net_layer_info(h, l, 5) == 1],
+                "dgrad": [l for l in rng if L.ag_net_layer_info(h, l, 6) == 1],
+                "wgrad": [l for l in rng if L.ag_net_layer_info(h, l, 7) == 1],
+                "refused": L.ag_net_layer_info(h, 0, 8), "splits": [L.ag_net_layer_info(h, l, 9) for l in rng]}
+
     def run_layer(self, layer, mode, n):
         _lib.check(_lib.lib().ag_net_run_layer(self._h, layer, mode, n, _lib.current_stream()), "ag_net_run_layer")
 

@@ -112,7 +112,11 @@ typedef struct ag_net ag_net;
 ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters, const int* h_widths,
                       int head_kind, int max_batch);                /* policy.py:93-156 create_network */
 void ag_net_destroy(ag_net* net);
-int ag_net_layer_info(const ag_net* net, int layer, int field);    /* 0 cin, 1 cout, 2 width, 3 padded cin, 4 padded cout */
+/* 0 cin, 1 cout, 2 width, 3 padded cin, 4 padded cout; how the layer is launched (no counterpart in the reference):
+ * 5 = its forward runs inside the one chained launch, 6 = its data gradient does, 7 = its weight gradient does (known
+ * after a forward_loss), 8 = chained launches the device refused so far (whole net; each was answered by the per-layer
+ * kernels), 9 = split-K factor of its weight gradient */
+int ag_net_layer_info(const ag_net* net, int layer, int field);
 /* conv weights, cross-correlation filters in Keras 'th' order w[co][ci][kx][ky], b[co] (host, synchronous);
  * Keras model.get_weights / set_weights (tests/test_policy.py:42-51, policy.py:165-167,188-190) */
 int ag_net_set_conv(ag_net* net, int layer, const float* h_w, const float* h_b);
@@ -198,6 +202,9 @@ int ag_augment(const uint8_t* d_states, const uint8_t* d_actions, const int64_t*
  * one chained launch, 4 = the whole data-gradient chain, 5 = the weight gradients of every hidden layer as one chained
  * launch (3, 4 and 5 ignore `layer`; AG_ESTATE when the net runs unchained) */
 int ag_net_run_layer(ag_net* net, int layer, int mode, int n, void* stream);
+/* test hook (no counterpart in the reference): `ctas` CTAs that each occupy one SM for `microseconds` (<= 5 s) on `stream`,
+ * to put the network's launches next to a kernel that holds SMs */
+int ag_debug_hold_sms(int ctas, long long microseconds, void* stream);
 /* test/debug readback (synchronous, allocates): kind 0 = activations of conv layer, 1 = its pre-activation
  * gradient, as fp32 [n][cout][board][board] on the host */
 int ag_net_debug_read(ag_net* net, int layer, int kind, int n, float* h_out);

@@ -83,21 +83,24 @@ def test_feature_subsets_orders_and_repeats():
 
 
 def test_full_size_batch_properties_and_oracle():
-    """BASELINE config 2 upper size: 16384 positions, all reference planes; one-hot invariants
+    """BASELINE configs[1] upper size: 16384 positions, ALL 48 planes (ladder planes included); one-hot invariants
     plus the oracle on the whole batch (the C oracle does this in seconds with all host cores)."""
     n = 16384
     b, a, pl, ko = go.playout_positions(99, n, size=19, per_game=16)
-    got = gpu_encode(FEATS46, b, a, pl, ko, 19)
+    got = gpu_encode(DEFAULT_FEATURES, b, a, pl, ko, 19)
+    assert got.shape == (n, 48, 19, 19)
     stones = (b != 0).reshape(n, 19, 19)
     assert np.array_equal(got[:, 0:3].sum(1), np.ones((n, 19, 19), np.uint8))          # board is a partition
-    assert (got[:, 3] == 1).all() and (got[:, 45] == 0).all()                          # ones / zeros
+    assert (got[:, 3] == 1).all() and (got[:, 47] == 0).all()                          # ones / zeros
     assert np.array_equal(got[:, 4:12].sum(1), stones.astype(np.uint8))                # one age per stone
     assert np.array_equal(got[:, 12:20].sum(1), stones.astype(np.uint8))               # one liberty class per stone
     legal = got[:, 20:28].sum(1)
     assert legal.max() <= 1 and np.array_equal(got[:, 36:44].sum(1), legal)            # capture/libs_after on legal moves
-    assert (got[:, 28:36].sum(1) <= legal).all() and (got[:, 44] <= legal).all()       # self-atari, sensible subset of legal
-    want = og.encode_batch(b, a, pl, ko, 19, FEATS46, threads=os.cpu_count() or 1)
-    assert_same(got, want, FEATS46)
+    assert (got[:, 28:36].sum(1) <= legal).all() and (got[:, 46] <= legal).all()       # self-atari, sensible subset of legal
+    assert (got[:, 44] <= legal).all() and (got[:, 45] <= legal).all()                 # ladder moves are legal moves
+    want = og.encode_batch(b, a, pl, ko, 19, DEFAULT_FEATURES, threads=os.cpu_count() or 1)
+    assert_same(got, want, DEFAULT_FEATURES)
+    assert want[:, 44].sum() > 1000 and want[:, 45].sum() > 1000
 
 
 def test_edge_cases():
