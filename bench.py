@@ -322,7 +322,7 @@ class TrainWorkload(object):
             acc = {}
             evs = [e for e in prof.events() if e.time_range is not None and "cuda" in str(e.device_type).lower()]
             for e in sorted(evs, key=lambda e: e.time_range.start):
-                name = e.name.split("(")[0].split("::")[-1].split("<")[0].strip()
+                name = e.name.replace("(anonymous namespace)::", "").split("(")[0].split("::")[-1].split("<")[0].strip()
                 if name.startswith("Memcpy") or name.startswith("Memset"):
                     continue
                 acc.setdefault(name, []).append(e.time_range.end - e.time_range.start)
@@ -588,7 +588,9 @@ def main():
                     roof["in_step_frac"] = {"achieved": round(a, 1), "ms": dom["in_step_ms"],
                                             "frac_of_burst_peak": round(a / pk["tensor_burst"], 4),
                                             "frac_of_sustained_peak": round(a / pk["tensor_sustained"], 4),
-                                            "note": "the dominant kernel's duration inside the running step (CUPTI)"}
+                                            "note": "the dominant kernel's duration inside the running step (CUPTI); small kernels "
+                                                    "launched with programmatic dependent launch start early and their in-step "
+                                                    "durations include the wait for the kernel in front"}
         else:
             roof = wl.roofline(ms_per_step, pk)
         line = {"metric": wl.metric, "value": round(value, 1), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
