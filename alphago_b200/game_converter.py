@@ -52,7 +52,7 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
         try:
             with open(file_name, "r") as file_object:
                 text = file_object.read()
-            gs, moves, players = sgf_move_list(text)
+            gs, moves, players, parse_error = sgf_move_list(text)
             if moves and gs.size != bd_size:
                 raise SizeMismatchError()
             # one library call replays the record and packs the position in front of every non-pass move
@@ -62,6 +62,8 @@ class game_converter(object):   # the reference's own (lower-case) class name, g
             actions = [m for m in played if m is not go.PASS_MOVE]
             if illegal is not None:
                 error = go.IllegalMove(str(moves[illegal]))
+            elif parse_error is not None:   # a bad node part-way through: the pairs in front of it stand
+                error = parse_error
         except Exception as e:   # classified by the caller
             error = e
         return packed, actions, error

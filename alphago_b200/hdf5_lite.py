@@ -276,7 +276,37 @@ class Dataset(object):
             arr = np.frombuffer(raw, self.dtype, count=n).reshape(self.chunk)
         return arr
 
-    def _rows(self, lo, hi):
+    def take_rows(self, index, out=None, pool=None):
+        """rows `index` (any order, repeats allowed) along the first axis, the way a shuffled minibatch reads a dataset
+        (supervised_policy_trainer.py:27-36 reads them one `state_dataset[data_idx]` at a time): every chunk that holds
+        one of the rows is decoded once per call, the chunks in parallel when a thread pool is given (the LZF / deflate
+        decoders release the GIL).  Nothing but those chunks is read from the file."""
+        index = np.asarray(index, np.int64)
+        if out is None:
+            out = np.empty((len(index),) + self.shape[1:], self.dtype)
+        if len(index) and (index.min() < 0 or index.max() >= self.shape[0]):
+            raise IndexError("row index out of range")
+        if self.layout != 2:
+            np.take(self._rows(0, self.shape[0]), index, axis=0, out=out)
+            return out
+        c0 = self.chunk[0]
+        order = np.argsort(index // c0, kind="stable")
+        firsts, starts = np.unique(index[order] // c0, return_index=True)
+        bounds = list(starts) + [len(index)]
+
+        def one(k):
+            first = int(firsts[k]) * c0
+            rows = self._rows(first, min(first + c0, self.shape[0]), cached=False)
+            sel = order[bounds[k]:bounds[k + 1]]
+            out[sel] = rows[index[sel] - first]
+        if pool is not None and len(firsts) > 1:
+            list(pool.map(one, range(len(firsts))))
+        else:
+            for k in range(len(firsts)):
+                one(k)
+        return out
+
+    def _rows(self, lo, hi, cached=True):
         """rows [lo, hi) along the first axis"""
         if self.layout != 2:
             count = int(np.prod(self.shape)) if self.shape else 1
@@ -299,7 +329,7 @@ class Dataset(object):
             decoded = None
         for first in range(lo // c0 * c0, hi, c0):
             for rest in idxs:
-                ch = decoded.pop((first,) + rest) if decoded is not None else self._chunk((first,) + rest)
+                ch = decoded.pop((first,) + rest) if decoded is not None else (self._chunk((first,) + rest) if cached else self._decode((first,) + rest))
                 a, z = max(lo, first), min(hi, first + c0, self.shape[0])
                 sl = (slice(a - first, z - first),) + tuple(slice(0, min(c, s - o)) for c, s, o in zip(self.chunk[1:], self.shape[1:], rest))
                 dst = (slice(a - lo, z - lo),) + tuple(slice(o, min(o + c, s)) for c, s, o in zip(self.chunk[1:], self.shape[1:], rest))
@@ -386,8 +416,12 @@ class Group(object):
 
 class _ReadFile(Group):
     def __init__(self, path):
+        # mapped, not read: a KGS-scale dataset is hundreds of GB and only the chunks a reader asks for are touched
+        import mmap
         with open(path, "rb") as fh:
-            buf = memoryview(fh.read())
+            size = os.fstat(fh.fileno()).st_size
+            self._map = mmap.mmap(fh.fileno(), 0, access=mmap.ACCESS_READ) if size > 0 else None
+        buf = memoryview(self._map) if self._map is not None else memoryview(b"")
         if bytes(buf[:8]) != MAGIC:
             raise ValueError("%s is not an HDF5 file" % path)
         ver = buf[8]
@@ -542,7 +576,9 @@ class WDataset(_WNode):
             raise NotImplementedError("rows must be written in ascending order without gaps (next row: %d, got %d)" % (self._next, lo))
         rows = np.broadcast_to(np.asarray(value, self.dtype).reshape((-1,) + self.shape[1:]) if np.ndim(value) else np.asarray(value, self.dtype),
                                (hi - lo,) + self.shape[1:])
-        self._pending.append(rows)
+        # a copy: the rows wait here until a chunk is full, and the caller may reuse its buffer meanwhile (the reference's
+        # converter and generator both reuse theirs)
+        self._pending.append(np.array(rows, dtype=self.dtype, copy=True))
         self._npending += hi - lo
         self._next = hi
         if self._npending >= self.chunks[0]:

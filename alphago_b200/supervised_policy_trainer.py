@@ -5,8 +5,13 @@ Same command line (positional `model train_data out_directory`; --minibatch/-B, 
 (`metadata.json` with {"epochs": [{loss, acc, val_loss, val_acc}...], "best_epoch", "training_data",
 "model_file"}, `shuffle.npz`, `weights.NNNNN.hdf5`), same data order semantics: one shuffled index list split into
 train/val/test, an endless generator over the train indices that picks one of the 8 board symmetries per sample
-(spt.py:18-40).  What changes is where the work happens: the dataset sits in device memory, minibatch assembly is
-a gather kernel, and the step is the CUDA network (`SLTrainer`).  Added flags (non-breaking): --momentum, --seed.
+(spt.py:18-40).  What changes is where the work happens: minibatch assembly is a gather kernel and the step is the
+CUDA network (`SLTrainer`).  A dataset that fits the device budget (--device-dataset-mb, default 16 GiB) is copied to
+device memory once; a larger one STREAMS, as the reference's generator does (it reads `state_dataset[data_idx]` sample
+by sample and never holds the file, spt.py:27-36): the HDF5 file stays mapped, a worker thread reads and decodes only the
+chunks that hold the next minibatch while the GPU runs the current one, and the rows travel through pinned staging
+buffers (`training.HostFeeder`).  Both paths see the same minibatches and symmetries and give bitwise the same weights.
+Added flags (non-breaking): --momentum, --seed, --device-dataset-mb, --io-threads.
 Launched under torchrun, every rank trains on its share of each minibatch and rank 0 writes the files.
 """
 import argparse
@@ -80,6 +85,8 @@ def run_training(cmd_line_args=None):
     parser.add_argument("--train-val-test", help="Fraction of data to use for training/val/test. Must sum to 1. Invalid if restarting training", nargs=3, type=float, default=[0.93, .05, .02])
     parser.add_argument("--momentum", help="SGD momentum. Default: 0 (as the reference)", type=float, default=0.0)
     parser.add_argument("--seed", help="seed for the shuffle and the symmetry choice", type=int, default=None)
+    parser.add_argument("--device-dataset-mb", help="Keep the dataset in device memory when it is at most this many MB, else stream it from the file. Default: 16384", type=float, default=16384.0)
+    parser.add_argument("--io-threads", help="Threads decoding dataset chunks when streaming. Default: 4", type=int, default=4)
     args = parser.parse_args(cmd_line_args)
 
     import torch
@@ -151,55 +158,80 @@ def run_training(cmd_line_args=None):
     train_indices = shuffle_indices[0:n_train_data]
     val_indices = shuffle_indices[n_train_data:n_train_data + n_val_data]
 
-    # dataset resident in device memory (uint8: 17 KB per 48-plane position)
-    d_states = torch.from_numpy(np.ascontiguousarray(states[:], dtype=np.uint8)).cuda()
-    d_actions = torch.from_numpy(np.ascontiguousarray(actions[:], dtype=np.uint8)).cuda()
-    if d_states.shape[1] != model.in_planes or d_states.shape[-1] != model.board:
+    shape = tuple(int(v) for v in states.shape)
+    if shape[1] != model.in_planes or shape[-1] != model.board:
         raise ValueError("dataset has %d planes on %dx%d boards, the model expects %d on %dx%d" % (
-            d_states.shape[1], d_states.shape[-1], d_states.shape[-1], model.in_planes, model.board, model.board))
-
+            shape[1], shape[-1], shape[-1], model.in_planes, model.board, model.board))
     if args.minibatch % world != 0:
         raise ValueError("--minibatch %d must be a multiple of the %d ranks" % (args.minibatch, world))
     share = args.minibatch // world  # this rank's part of every minibatch
     model.ensure_batch(share)
     trainer = SLTrainer(model.net, lr=args.learning_rate, decay=args.decay, momentum=args.momentum)
+    mine = slice(rank * share, (rank + 1) * share)
+    dataset_mb = float(np.prod(shape)) / 2 ** 20
+    streaming = dataset_mb > args.device_dataset_mb
+    if streaming:
+        # the dataset stays where it is (a mapped file or host arrays); rows reach the device minibatch by minibatch
+        from concurrent.futures import ThreadPoolExecutor
+        from .training import HostFeeder
+        say("streaming the dataset (%.0f MB > --device-dataset-mb %.0f)" % (dataset_mb, args.device_dataset_mb))
+        feeder = HostFeeder(trainer, states, actions, share, io_threads=max(0, args.io_threads))
+        reader = ThreadPoolExecutor(max_workers=1)
+    else:
+        # dataset resident in device memory (uint8: 17 KB per 48-plane position)
+        d_states = torch.from_numpy(np.ascontiguousarray(states[:], dtype=np.uint8)).cuda()
+        d_actions = torch.from_numpy(np.ascontiguousarray(actions[:], dtype=np.uint8)).cuda()
+
+    def batches(stream, total):
+        """(index, transform) of this rank for minibatch after minibatch until `total` samples have been seen"""
+        seen = 0
+        while seen < total:
+            idx = next(stream)
+            tf = rng.randint(0, 8, len(idx))  # np.random.choice(transforms) per sample, spt.py:30
+            seen += len(idx)
+            yield idx[mine], tf[mine]
+
+    def run(stream, total, train):
+        """one pass: returns the number of local samples"""
+        local = 0
+        if not streaming:
+            for idx_r, tf_r in batches(stream, total):
+                x, y = trainer.assemble(d_states, d_actions, idx_r, tf_r)
+                (trainer.step if train else trainer.evaluate)(x, y)
+                local += len(idx_r)
+            return local
+        it = batches(stream, total)
+        nxt = next(it, None)
+        pending = reader.submit(feeder.stage, nxt[0]) if nxt is not None else None
+        while nxt is not None:
+            cur, nxt = nxt, next(it, None)
+            pending.result()                       # minibatch `cur` is in its staging buffers
+            feeder.step(cur[0], cur[1], train=train)   # queue copy + step ...
+            if nxt is not None:                    # ... and read the next one meanwhile
+                pending = reader.submit(feeder.stage, nxt[0])
+            local += len(cur[0])
+        return local
+
     train_stream = _index_stream(train_indices, args.minibatch)
     val_stream = _index_stream(val_indices, args.minibatch) if n_val_data > 0 else None
     samples_per_epoch = args.epoch_length or n_train_data
-    mine = slice(rank * share, (rank + 1) * share)
     say("STARTING TRAINING")
 
     for epoch in range(args.epochs):
-        seen = 0
-        local_seen = 0
-        while seen < samples_per_epoch:  # Keras 1.0 fit_generator: batches until samples_per_epoch is reached
-            idx = next(train_stream)
-            tf = rng.randint(0, 8, len(idx))  # np.random.choice(transforms) per sample, spt.py:30
-            idx_r, tf_r = idx[mine], tf[mine]
-            if len(idx_r):
-                x, y = trainer.assemble(d_states, d_actions, idx_r, tf_r)
-                trainer.step(x, y)
-                local_seen += len(idx_r)
-            seen += len(idx)
+        # Keras 1.0 fit_generator: batches until samples_per_epoch is reached
+        local_seen = run(train_stream, samples_per_epoch, True)
         loss, acc = trainer.pop_metrics(local_seen)
         logs = {"loss": loss, "acc": acc}
         if val_stream is not None:
-            vseen, vlocal = 0, 0
-            while vseen < n_val_data:
-                idx = next(val_stream)
-                tf = rng.randint(0, 8, len(idx))
-                idx_r, tf_r = idx[mine], tf[mine]
-                if len(idx_r):
-                    x, y = trainer.assemble(d_states, d_actions, idx_r, tf_r)
-                    trainer.evaluate(x, y)
-                    vlocal += len(idx_r)
-                vseen += len(idx)
+            vlocal = run(val_stream, n_val_data, False)
             logs["val_loss"], logs["val_acc"] = trainer.pop_metrics(vlocal)
         if chief:
             # ModelCheckpoint numbers files from 0 in every run (spt.py:161-162)
             model.save_weights(os.path.join(args.out_directory, "weights.%05d.hdf5" % epoch))
             meta_writer.on_epoch_end(logs)
         say("epoch %d: %s" % (epoch, json.dumps(logs)))
+    if streaming:
+        reader.shutdown()
     if world > 1:
         dist.barrier()
     return meta_writer.metadata

@@ -158,9 +158,14 @@ class HostFeeder(object):
     augment + train on the compute stream, and copy the running (loss sum, correct count) back.  Nothing waits for the
     step just queued: the copy of batch k overlaps the kernels of step k-1, and `step()` returns the metrics of the
     PREVIOUS step (None on the first call); `flush()` returns the last ones.
+
+    `h_states` / `h_actions` are numpy arrays, or datasets that read rows from a file on demand (anything with
+    `take_rows(index, out)`, e.g. hdf5_lite.Dataset: only the chunks holding the minibatch are decoded).  `stage(index)`
+    does the gather of the NEXT step ahead of time -- host work only, safe on a worker thread while this thread queues
+    the current step -- which is how `run_training` hides file reads behind the GPU.
     """
 
-    def __init__(self, trainer, h_states, h_actions, batch):
+    def __init__(self, trainer, h_states, h_actions, batch, io_threads=0):
         import torch
         self.torch, self.trainer = torch, trainer
         self.h_states, self.h_actions, self.batch = h_states, h_actions, int(batch)
@@ -176,6 +181,11 @@ class HostFeeder(object):
         self.ev_metrics = [torch.cuda.Event() for _ in range(2)]
         self.ident = np.arange(self.batch)
         self.k = 0
+        self.staged = 0      # minibatches gathered so far (at most one ahead of self.k)
+        self.pool = None
+        if io_threads > 0:
+            from concurrent.futures import ThreadPoolExecutor
+            self.pool = ThreadPoolExecutor(max_workers=io_threads)
         self.h2d_bytes = self.pin_x[0].numel() + self.pin_a[0].numel()
         self.d2h_bytes = 8
 
@@ -183,15 +193,36 @@ class HostFeeder(object):
         self.ev_metrics[slot].synchronize()
         return float(self.pin_m[slot][0]), float(self.pin_m[slot][1])
 
-    def step(self, index, transform):
+    def _gather(self, src, index, out):
+        if hasattr(src, "take_rows"):
+            src.take_rows(index, out, self.pool)
+        elif isinstance(src, np.ndarray):
+            np.take(src, index, axis=0, out=out)
+        else:   # an h5py dataset: fancy indexing wants increasing, unique rows
+            uniq, inverse = np.unique(np.asarray(index), return_inverse=True)
+            out[...] = np.asarray(src[uniq.tolist()])[inverse]
+
+    def stage(self, index):
+        """gather minibatch number `self.staged` into its pinned staging buffers (host work only)"""
+        if len(index) != self.batch:
+            raise ValueError("HostFeeder was built for minibatches of %d, got %d" % (self.batch, len(index)))
+        if self.staged > self.k + 1:
+            raise RuntimeError("HostFeeder.stage: at most one minibatch ahead of step()")
+        slot = self.staged & 1
+        if self.staged >= 2:
+            self.ev_copied[slot].synchronize()      # the staging buffer's previous copy has left the host
+        self._gather(self.h_states, index, self.pin_x[slot].numpy())
+        self._gather(self.h_actions, index, self.pin_a[slot].numpy())
+        self.staged += 1
+
+    def step(self, index, transform, train=True):
+        """queue one step on minibatch `index` (already staged, or gathered now); train=False only evaluates it"""
         torch = self.torch
         slot = self.k & 1
         if len(index) != self.batch:
             raise ValueError("HostFeeder was built for minibatches of %d, got %d" % (self.batch, len(index)))
-        if self.k >= 2:
-            self.ev_copied[slot].synchronize()      # the staging buffer's previous copy has left the host
-        np.take(self.h_states, index, axis=0, out=self.pin_x[slot].numpy())
-        np.take(self.h_actions, index, axis=0, out=self.pin_a[slot].numpy())
+        if self.staged == self.k:
+            self.stage(index)
         main = torch.cuda.current_stream()
         with torch.cuda.stream(self.copy_stream):
             if self.k >= 2:
@@ -202,7 +233,10 @@ class HostFeeder(object):
         main.wait_event(self.ev_copied[slot])
         x, y = self.trainer.assemble(self.dx[slot], self.da[slot], self.ident, transform)
         self.ev_consumed[slot].record(main)
-        self.trainer.step(x, y)
+        if train:
+            self.trainer.step(x, y)
+        else:
+            self.trainer.evaluate(x, y)
         self.pin_m[slot].copy_(self.trainer.loss_acc, non_blocking=True)
         self.ev_metrics[slot].record(main)
         self.k += 1

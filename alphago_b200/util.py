@@ -162,23 +162,29 @@ def sgf_iter_states(sgf_string):
 
 
 def sgf_move_list(sgf_string):
-    """(GameState after the root node's set-up, moves, players): what sgf_iter_states would play, as lists, for callers
-    that replay a whole record in one library call (GameState.replay_pack).  Same node rules as sgf_iter_states."""
+    """(GameState after the root node's set-up, moves, players, error): what sgf_iter_states would play, as lists, for
+    callers that replay a whole record in one library call (GameState.replay_pack).  Same node rules as sgf_iter_states.
+    `error` is the exception a node raised part-way through the record (a malformed move value, a first node with no
+    move), or None: the moves in front of it are returned, because the reference's generator has already yielded -- and
+    its converter already written -- those pairs when the exception surfaces (game_converter.py:103-123)."""
     nodes = sgf_main_line(sgf_string)
     gs = _sgf_init_gamestate(nodes[0])
     moves, players = [], []
     have = False
     move = player = None
-    for props in nodes[1:]:
-        if "W" in props:
-            move, player, have = _parse_sgf_move(props["W"][0]), go.WHITE, True
-        elif "B" in props:
-            move, player, have = _parse_sgf_move(props["B"][0]), go.BLACK, True
-        if not have:
-            raise UnboundLocalError("local variable 'move' referenced before assignment")   # what util.py:81 does
-        moves.append(move)
-        players.append(player)
-    return gs, moves, players
+    try:
+        for props in nodes[1:]:
+            if "W" in props:
+                move, player, have = _parse_sgf_move(props["W"][0]), go.WHITE, True
+            elif "B" in props:
+                move, player, have = _parse_sgf_move(props["B"][0]), go.BLACK, True
+            if not have:
+                raise UnboundLocalError("local variable 'move' referenced before assignment")   # what util.py:81 does
+            moves.append(move)
+            players.append(player)
+    except Exception as e:
+        return gs, moves, players, e
+    return gs, moves, players, None
 
 
 def sgf_to_gamestate(sgf_string):

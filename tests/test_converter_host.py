@@ -109,3 +109,14 @@ def test_pack_game_error_handling(golden_dir, tmp_path):
     q.write_text("hello")
     packed, acts, error = conv.pack_game(str(q), 19)
     assert packed == [] and isinstance(error, util.ParseException)
+    # a malformed move value part-way through the record: the pairs in front of it stand, the error is reported (the
+    # reference's generator has yielded them before the exception surfaces, game_converter.py:103-123)
+    m = tmp_path / "malformed.sgf"
+    m.write_text("(;SZ[19];B[aa];W[bb];B[c];W[dd])")
+    packed, acts, error = conv.pack_game(str(m), 19)
+    assert acts == [(0, 0), (1, 1)] and len(packed) == 2 and isinstance(error, (IndexError, ValueError))
+    # a first node that carries no move: nothing to repeat yet (util.py:81 fails the same way)
+    n = tmp_path / "nomove.sgf"
+    n.write_text("(;SZ[19];C[hello];B[aa])")
+    packed, acts, error = conv.pack_game(str(n), 19)
+    assert packed == [] and acts == [] and isinstance(error, UnboundLocalError)

@@ -316,3 +316,30 @@ def test_lzf_round_trip_property():
         assert h5.lzf_decode(enc, len(raw)) == raw and h5.lzf_decompress(enc, len(raw)) == raw
 
     check()
+
+
+def test_take_rows_reads_only_what_a_shuffled_minibatch_needs(tmp_path):
+    """Dataset.take_rows: rows in any order, with repeats, from LZF chunks (the converter's layout), equal to plain
+    indexing; with and without a thread pool; on a mapped file (the reader never loads the whole file)"""
+    from concurrent.futures import ThreadPoolExecutor
+    rng = np.random.RandomState(3)
+    data = (rng.rand(300, 5, 7, 7) < 0.3).astype(np.uint8)
+    acts = rng.randint(0, 7, (300, 2)).astype(np.uint8)
+    path = os.path.join(str(tmp_path), "d.h5")
+    with h5.File(path, "w") as f:
+        f.create_dataset("states", data=data, chunks=(64, 5, 7, 7), compression="lzf")
+        f.create_dataset("actions", data=acts, chunks=(128, 2), compression="lzf")
+        f.create_dataset("plain", data=acts)
+    f = h5.File(path, "r")
+    assert f._map is not None
+    idx = rng.randint(0, 300, 97)
+    idx[:3] = [299, 0, 299]
+    with ThreadPoolExecutor(4) as pool:
+        for name, ref in (("states", data), ("actions", acts), ("plain", acts)):
+            ds = f[name]
+            assert np.array_equal(ds.take_rows(idx), ref[idx])
+            out = np.empty((len(idx),) + ref.shape[1:], ref.dtype)
+            assert ds.take_rows(idx, out, pool) is out and np.array_equal(out, ref[idx])
+    assert f["states"].take_rows([]).shape == (0, 5, 7, 7)
+    with pytest.raises(IndexError):
+        f["states"].take_rows([300])

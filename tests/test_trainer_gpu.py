@@ -89,3 +89,30 @@ def test_host_feeder_matches_device_resident_training(golden_dir):
         assert np.array_equal(wa, wb) and np.array_equal(ba, bb)
     with pytest.raises(ValueError):
         feeder.step(plan[0][0][:5], plan[0][1][:5])
+
+
+def test_run_training_streams_a_dataset_larger_than_the_device_budget(tmp_path, golden_dir):
+    """A dataset above --device-dataset-mb is never copied to the device as a whole: run_training reads minibatches from
+    the mapped HDF5 file on a worker thread (the reference's generator reads sample by sample, spt.py:27-36).  Same seed,
+    same minibatches, same symmetries -> bitwise the same weights as the device-resident run."""
+    from test_oracle import load_hdf5_fixture
+    from alphago_b200 import hdf5_lite
+    states, actions, _, feats = load_hdf5_fixture(golden_dir)
+    d = str(tmp_path)
+    data = os.path.join(d, "features.hdf5")
+    with hdf5_lite.File(data, "w") as f:   # the converter's layout: LZF chunks of 64 / 1024 rows (game_converter.py:71-88)
+        f.create_dataset("states", data=states, chunks=(64,) + states.shape[1:], compression="lzf")
+        f.create_dataset("actions", data=actions, chunks=(1024, 2), compression="lzf")
+    model = os.path.join(d, "model.json")
+    CNNPolicy(feats, layers=3, filters_per_layer=32, seed=5).save_model(model)
+    common = ["--epochs", "2", "--minibatch", "32", "--epoch-length", "320", "--learning-rate", "0.05", "--seed", "4"]
+    meta_a = run_training([model, data, os.path.join(d, "resident")] + common)
+    meta_b = run_training([model, data, os.path.join(d, "streamed")] + common + ["--device-dataset-mb", "1", "--io-threads", "3"])
+    assert states.nbytes > 2 ** 20
+    for ea, eb in zip(meta_a["epochs"], meta_b["epochs"]):
+        for k in ("loss", "acc", "val_loss", "val_acc"):
+            assert abs(ea[k] - eb[k]) <= 1e-5 * max(1.0, abs(ea[k])), (k, ea, eb)   # loss sums use float atomics
+    for name in ("weights.00000.hdf5", "weights.00001.hdf5"):
+        a = CNNPolicy.load_model(model); a.model.load_weights(os.path.join(d, "resident", name))
+        b = CNNPolicy.load_model(model); b.model.load_weights(os.path.join(d, "streamed", name))
+        assert all(np.array_equal(x, y) for x, y in zip(a.model.get_weights(), b.model.get_weights())), name
