@@ -40,6 +40,34 @@ def test_static_scratch_matches_ag_wgrad_twice_in_a_row():
         assert rel(first, oracle_dw(x, g, width)) < 1e-3
 
 
+def test_static_entry_point_leaves_device_memory_alone():
+    """the property the entry point exists for: across its calls the device's free memory (cudaMemGetInfo, which sees every
+    allocation of every allocator in the process) does not move, and neither does torch's own pool.  Inputs and outputs are
+    allocated first; the library and its 16 MiB array are on the device already (an earlier launch loaded the module)."""
+    import torch
+    from test_wgrad_gpu import padded_rows
+    S, n, cin, cout, width = 19, 6, 192, 192, 3
+    x, g = make_inputs(S, n, cin, cout, 7)
+    run_wgrad(via_ag_wgrad(), x, g, width, S)            # loads the module / warms both entry points' kernels
+    run_wgrad(via_static(), x, g, width, S)
+    rs, ist = S + 1, (S + 1) * (S + 1)
+    dx, dg = padded_rows(x, rs, ist, 192), padded_rows(g, rs, ist, 192)
+    dw = torch.empty((9, 192, 192), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    reserved0, allocated0 = torch.cuda.memory_reserved(), torch.cuda.memory_allocated()
+    for _ in range(3):
+        rc = _lib.lib().ag_wgrad_static(C.c_void_p(dg.data_ptr()), C.c_void_p(dx.data_ptr()), n * ist, 192, 192, width, rs,
+                                        C.c_void_p(dw.data_ptr()), _lib.current_stream())
+        assert rc == 0, _lib.last_error()
+        free_mid, _ = torch.cuda.mem_get_info()          # while the kernels may still be running
+        assert free_mid == free0
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free0
+    assert torch.cuda.memory_reserved() == reserved0 and torch.cuda.memory_allocated() == allocated0
+    assert torch.isfinite(dw).all()
+
+
 def test_static_scratch_refuses_oversized_problems():
     import torch
     z = torch.zeros(1 << 16, dtype=torch.float32, device="cuda")
