@@ -15,6 +15,7 @@ LIB = os.path.join(HERE, "libalphago_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--expt-relaxed-constexpr"]
+FLAGS += os.environ.get("AG_NVCC_EXTRA", "").split()   # e.g. AG_NVCC_EXTRA=-DAG_ENC_PROFILE for the per-phase cycle counters
 
 
 def sources():

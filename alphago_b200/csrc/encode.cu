@@ -6,19 +6,24 @@
 // is rebuilt per position by a warp-wide union-find instead of porting the reference's
 // incremental Python sets (go.py:104-157).
 //
-// Per position (flat point index p = x*size+y, planes [f][x][y], AlphaGo/util.py:6-8):
-//   1. board/age -> shared memory                      (coalesced byte loads)
-//   2. union-find over same-colour edges               (atomicMin hooking + path walk)
-//   3. per-group size / liberty count / first 8 liberties (shared-memory atomics)
-//   4. per-point feature codes: liberties, legality (go.py:181-216), capture_size, the
-//      liberty union for self_atari_size / liberties_after (preprocessing.py:91-144, incl. the
-//      negative-index wrap of :143 and the "captures ignored" quirk), sensibleness via an
-//      iterative restatement of the path-dependent is_eye recursion (go.py:230-259)
-//   5. ladder planes (see ladder.cuh)
-//   6. codes -> one-hot uint8 planes, 16-byte coalesced stores
+// Per position (flat point p = x*size+y, planes [f][x][y], AlphaGo/util.py:6-8); lane l owns points l, l+32, ...:
+//   1. board / age -> shared memory; colour and turns_since codes           (coalesced byte loads)
+//   2. groups: horizontal runs by pointer jumping (5 rounds), then ONE pass of lock-free unions (atomicMin hooking)
+//      over the vertical edges that join two runs for the first time, then a flatten to the root point
+//   3. per group: stones and liberties (shared-memory atomics); the liberties of the side to move's groups, up to 8
+//      each, in one pool laid out by a warp prefix sum (sum of min(libs, 8) <= 964 on any 19x19 board)
+//   4. per point: liberties plane; for empty points legality (go.py:181-216), capture_size, and |L| for
+//      self_atari_size / liberties_after (preprocessing.py:91-144, incl. the negative-index wrap of :143 and the
+//      "captures ignored" quirk) counted WITHOUT a set: the first own neighbour group gives libs-1, every further
+//      liberty counts if none of ITS neighbours belongs to a group taken before (labels compared, no bit sets);
+//      sensibleness via an iterative restatement of the path-dependent is_eye recursion (go.py:230-259)
+//   5. ladder candidates (moves touching an opponent group with two liberties / an own group in atari) go to a work
+//      list in global memory; ladder_resolve_kernel reads them out one query per warp, dynamically balanced
+//   6. nibble codes -> one-hot uint8 planes, 16-byte coalesced stores
 //
-// HBM-bound by construction (18,054 algorithmic bytes per position); in practice
-// the integer work in steps 2-5 is what the kernel spends its time on.
+// HBM-bound by construction (18,054 algorithmic bytes per position); in practice the integer work of
+// steps 2-5 is what the kernel spends its time on, so the design goals are warps per SM (7.3 KB of shared memory per
+// warp: 30 warps/SM) and short dependent chains.
 #include <stdlib.h>
 
 #include <atomic>
@@ -44,7 +49,7 @@ __device__ __forceinline__ bool eyeish(const int8_t* col, int size, int p, int o
 // go.py:230-259 as an explicit-stack DFS.  The reference's result for inner calls depends on the
 // current recursion path (`d not in stack`) and on the early exit once bad > allowable, so the
 // visit order (go.py:102) and both of those are reproduced literally.  Frame = pos | next<<9 | bad<<12.
-__device__ bool is_eye(const int8_t* col, int size, int p0, int owner) {
+__device__ __noinline__ bool is_eye(const int8_t* col, int size, int p0, int owner) {
     if (!eyeish(col, size, p0, owner)) return false;
     uint16_t stk[184];  // path nodes are distinct same-parity points: <= 181 on 19x19
     int sp = 0;
@@ -90,309 +95,449 @@ __device__ bool is_eye(const int8_t* col, int size, int p0, int owner) {
     }
 }
 
+#ifdef AG_ENC_PROFILE
+__device__ unsigned long long g_enc_phase_cycles[8];
+#define ENC_T(i) do { long long _t = clock64(); if (lane == 0) atomicAdd(&g_enc_phase_cycles[i], (unsigned long long)(_t - t_phase)); t_phase = _t; } while (0)
+#else
+#define ENC_T(i) do {} while (0)
+#endif
+
+constexpr int COLPAD = 384;   // 12 x 32 points; col[] is zero beyond the board, so p + size may be read unguarded
+constexpr int POOL = 968;     // >= max over boards of sum over one colour's groups of min(liberties, 8)  (= 964 on 19x19)
+constexpr int NCODE = 4;      // nibble-packed code arrays: BOARD|TURNS, LIBS|CAPTURE, SELFATARI|LIBSAFTER, SENSIBLE|ladder marks
+
 struct WarpMem {
-    uint32_t label[NPAD];         // union-find parent, then root per point
-    uint32_t cnt[NPAD];           // by root: group size << 16 | liberty count
-    uint16_t liblist[MAXN][8];    // by root: first 8 liberties
-    uint32_t lanebits[LW][32];    // lane-private 361-bit scratch set, [word][lane] (conflict-free)
-    uint32_t codes[N_CODE][CODE_STRIDE / 4];  // per-point plane index per feature family, 0xFF = none
-    int8_t col[NPAD];
-    uint32_t ncand;               // ladder candidates queued in liblist (reused once the codes are final)
+    int8_t col[COLPAD];           // colour of the point
+    uint16_t lab[NPAD];           // root point of the stone's group; 0xFFFF where empty
+    uint32_t cnt[NPAD];           // by root: stones << 16 | liberties
+    uint32_t off[NPAD];           // union-find parents (step 2); then, by root of an own group: filled << 16 | pool offset
+    uint16_t pool[POOL];          // liberty lists (<= 8 each) of the side to move's groups
+    uint8_t codes[NCODE][NPAD];   // low / high nibble = plane index within a family, 0xF = none
 };
 
-__device__ __forceinline__ uint32_t find_root(volatile uint32_t* label, uint32_t p) {
-    uint32_t r = label[p];
-    while (true) {
-        uint32_t n = label[r];
-        if (n == r) return r;
-        r = n;
+// plane descriptor in shared memory: bits 0-11 byte offset of the code array, 12-15 nibble shift, 16-19 value,
+// 24-25 kind (0 compare, 1 all zeros, 2 all ones, 3 ones when black is to move)
+__device__ __forceinline__ uint32_t plane_desc(int arr, int val) {
+    switch (arr) {
+        case C_BOARD: return 0u * NPAD | 0u << 12 | (uint32_t)val << 16;
+        case C_TURNS: return 0u * NPAD | 4u << 12 | (uint32_t)val << 16;
+        case C_LIBS: return 1u * NPAD | 0u << 12 | (uint32_t)val << 16;
+        case C_CAPTURE: return 1u * NPAD | 4u << 12 | (uint32_t)val << 16;
+        case C_SELFATARI: return 2u * NPAD | 0u << 12 | (uint32_t)val << 16;
+        case C_LIBSAFTER: return 2u * NPAD | 4u << 12 | (uint32_t)val << 16;
+        case C_SENSIBLE: return 3u * NPAD | 0u << 12 | (uint32_t)val << 16;
+        case C_CONST: return (val == 0 ? 2u : 1u) << 24;
+        case C_COLOR: return 3u << 24;
+        default: return 1u << 24;   // ladder planes: zeros here, ladder_resolve_kernel writes the ones
     }
 }
 
-__global__ void __launch_bounds__(WARPS * 32) encode_kernel(
+// work list of ladder queries: header {appended, taken} then entries position << 10 | kind << 9 | point
+struct LadderWork {
+    unsigned int* head;      // [0] entries appended by encode_kernel, [1] next entry to take (ladder_resolve_kernel)
+    uint32_t* entries;
+    uint32_t* bits;          // per position: 12 words of black stones, 12 words of white stones
+};
+
+__device__ __forceinline__ uint32_t uf_find(volatile uint32_t* parent, uint32_t a) {
+    while (true) {
+        const uint32_t b = parent[a];
+        if (b == a) return a;
+        a = b;
+    }
+}
+// lock-free union: hook the larger root under the smaller one; a lost race continues from what the winner left
+__device__ __forceinline__ void uf_unite(volatile uint32_t* parent, uint32_t a, uint32_t b) {
+    while (true) {
+        a = uf_find(parent, a);
+        b = uf_find(parent, b);
+        if (a == b) return;
+        if (a < b) { const uint32_t t = a; a = b; b = t; }
+        const uint32_t old = atomicMin((uint32_t*)&parent[a], b);
+        if (old == a) return;
+        a = old;
+    }
+}
+// does point e touch (4-neighbourhood) a stone whose group root is one of the first m roots packed in r01 / r23
+// (16 bits each)?  Not inlined: the kernel must stay small enough for the instruction cache (see the header of the kernel).
+__device__ __noinline__ bool touches(const uint16_t* lab, const uint16_t* s_xy, int size, int e, uint32_t r01, uint32_t r23, int m) {
+    const int x = s_xy[e] & 255, y = s_xy[e] >> 8;
+    const uint32_t l0 = x > 0 ? lab[e - size] : 0xFFFFu, l1 = x < size - 1 ? lab[e + size] : 0xFFFFu;
+    const uint32_t l2 = y > 0 ? lab[e - 1] : 0xFFFFu, l3 = y < size - 1 ? lab[e + 1] : 0xFFFFu;
+    bool hit = false;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t r = ((i < 2 ? r01 : r23) >> (16 * (i & 1))) & 0xFFFFu;
+        if (i < m) hit |= (l0 == r) | (l1 == r) | (l2 == r) | (l3 == r);
+    }
+    return hit;
+}
+// one output byte: plane descriptor d at point p
+__device__ __forceinline__ uint32_t point_value(const uint8_t* codes, uint32_t d, int p, uint32_t black) {
+    const uint32_t kind = d >> 24;
+    if (kind) return kind == 2 ? 1u : (kind == 3 ? (black & 1u) : 0u);
+    return (((uint32_t)codes[(d & 0xFFFu) + p] >> ((d >> 12) & 0xFu)) & 0xFu) == ((d >> 16) & 0xFu) ? 1u : 0u;
+}
+// four consecutive output bytes of a plane starting at point p (bytes past the plane's end are garbage: the caller masks)
+__device__ __forceinline__ uint32_t plane_word(const uint8_t* codes, uint32_t d, int p, uint32_t black) {
+    const uint32_t kind = d >> 24;
+    if (kind) return kind == 2 ? 0x01010101u : (kind == 3 ? black : 0u);
+    const uint32_t* ca = reinterpret_cast<const uint32_t*>(codes + (d & 0xFFFu) + (p & ~3));
+    const uint32_t cv = __funnelshift_r(ca[0], ca[1], (p & 3) * 8);
+    const uint32_t nib = (cv >> ((d >> 12) & 0xFu)) & 0x0F0F0F0Fu;
+    return __vcmpeq4(nib, ((d >> 16) & 0xFu) * 0x01010101u) & 0x01010101u;
+}
+
+__global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
     const int8_t* __restrict__ g_board, const uint8_t* __restrict__ g_age, const int8_t* __restrict__ g_player,
-    const int16_t* __restrict__ g_ko, int npos, int size, PlaneTable tab, uint8_t* __restrict__ g_out) {
+    const int16_t* __restrict__ g_ko, int npos, int size, PlaneTable tab, uint8_t* __restrict__ g_out, LadderWork work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ uint8_t s_arr[MAX_PLANES], s_val[MAX_PLANES];
-    __shared__ uint16_t s_xy[NPAD];  // x | y << 8 of every point: replaces p / size in the hot loops
+    __shared__ uint32_t s_tab[MAX_PLANES];
+    __shared__ uint16_t s_xy[COLPAD];  // x | y << 8 of every point: replaces p / size in the hot loops
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpMem& W = reinterpret_cast<WarpMem*>(smem_raw)[warp];
     const int n = size * size;
     const int F = tab.n_planes;
-    for (int i = threadIdx.x; i < F; i += blockDim.x) { s_arr[i] = tab.arr[i]; s_val[i] = tab.val[i]; }
-    for (int i = threadIdx.x; i < NPAD; i += blockDim.x) { int x = i / size; s_xy[i] = (uint16_t)(x | ((i - x * size) << 8)); }
+    for (int i = threadIdx.x; i < F; i += blockDim.x) s_tab[i] = plane_desc(tab.arr[i], tab.val[i]);
+    for (int i = threadIdx.x; i < COLPAD; i += blockDim.x) { int x = i / size; s_xy[i] = (uint16_t)(x | ((i - x * size) << 8)); }
     __syncthreads();
-    uint8_t* const codes = reinterpret_cast<uint8_t*>(W.codes);  // [N_CODE][CODE_STRIDE]
-#define CODE(a, p) codes[(a) * CODE_STRIDE + (p)]
-    volatile uint32_t* label = W.label;
+    volatile uint32_t* parent = W.off;
+    const float inv_n = 1.0f / (float)n;
+    const int nwarps = blockDim.x >> 5;
 
-    for (int pos = blockIdx.x * WARPS + warp; pos < npos; pos += gridDim.x * WARPS) {
+    for (int pos = blockIdx.x * nwarps + warp; pos < npos; pos += gridDim.x * nwarps) {
         const int8_t* board = g_board + (size_t)pos * n;
         const uint8_t* age = g_age + (size_t)pos * n;
         const int me = g_player[pos];
         const int ko = g_ko[pos];
-
-        // ---- 1. load; board / turns_since / constant codes
-        for (int p = lane; p < NPAD; p += 32) {
+#ifdef AG_ENC_PROFILE
+        long long t_phase = clock64();
+#endif
+        // ---- 1. load; board / turns_since codes; the position's bit boards for the ladder read-out
+        uint32_t my_blk = 0, my_wht = 0;
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
             int c = 0, a = 255;
             if (p < n) { c = board[p]; a = age[p]; }
             W.col[p] = (int8_t)c;
-            label[p] = p;
-            W.cnt[p] = 0;
-            CODE(C_BOARD, p) = c == 0 ? 2 : (c == me ? 0 : 1);          // preprocessing.py:9-17
-            CODE(C_TURNS, p) = (c != 0 && a < 8) ? (uint8_t)a : 0xFF;    // preprocessing.py:20-43
-            CODE(C_CONST, p) = 0;
-            CODE(C_COLOR, p) = me == 1 ? 0 : 0xFF;
-            CODE(C_LADCAP, p) = 0xFF;
-            CODE(C_LADESC, p) = 0xFF;
-        }
-        for (int w = 0; w < LW; w++) W.lanebits[w][lane] = 0;
-        if (lane == 0) W.ncand = 0;
-        __syncwarp();
-
-        // ---- 2. union-find over same-colour edges (+x and +y direction of every stone)
-        while (true) {
-            bool changed = false;
-            for (int p = lane; p < n; p += 32) {
-                int c = W.col[p];
-                if (c == 0) continue;
-                const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
-#pragma unroll
-                for (int e = 0; e < 2; e++) {
-                    int q = e == 0 ? p + 1 : p + size;
-                    bool ok = e == 0 ? (y < size - 1) : (x < size - 1);
-                    if (!ok || W.col[q] != c) continue;
-                    uint32_t rp = find_root(label, p), rq = find_root(label, q);
-                    if (rp != rq) {
-                        uint32_t hi = max(rp, rq), lo = min(rp, rq);
-                        atomicMin((uint32_t*)&label[hi], lo);
-                        changed = true;
-                    }
-                }
+            const uint32_t bb = __ballot_sync(0xffffffffu, c > 0), bw = __ballot_sync(0xffffffffu, c < 0);
+            if (lane == k) { my_blk = bb; my_wht = bw; }
+            if (p < NPAD) {
+                W.cnt[p] = 0;
+                const int cb = c == 0 ? 2 : (c == me ? 0 : 1);           // preprocessing.py:9-17
+                const int ct = (c != 0 && a < 8) ? a : 0xF;              // preprocessing.py:20-43
+                W.codes[0][p] = (uint8_t)(cb | ct << 4);
             }
+        }
+        if (work.bits && lane < 12) { work.bits[(size_t)pos * 24 + lane] = my_blk; work.bits[(size_t)pos * 24 + 12 + lane] = my_wht; }
+        __syncwarp();
+        ENC_T(0);
+
+        // ---- 2. groups.  2a: every stone points at the left end of its horizontal run (pointer jumping)
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p < NPAD) {
+                const int c = W.col[p];
+                const int y = s_xy[p] >> 8;
+                W.off[p] = (p < n && c != 0 && y > 0 && W.col[p - 1] == c) ? p - 1 : p;
+            }
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int r = 0; r < 5; r++) {   // runs are at most 19 long: 2^5 >= 19.  In place: a racing read sees an ancestor either way
+#pragma unroll 4
+            for (int k = 0; k < 12; k++) { const int p = k * 32 + lane; if (p < NPAD) W.off[p] = W.off[W.off[p]]; }
             __syncwarp();
-            if (!__any_sync(0xffffffffu, changed)) break;
         }
-        // flatten: concurrent walks stay correct, a store only ever shortens a path to the same root
-        for (int p = lane; p < n; p += 32) label[p] = find_root(label, p);
+        // 2b: one union per pair of vertically touching runs (the edge whose left neighbour does not already join them)
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p >= n) continue;
+            const int c = W.col[p];
+            if (c == 0 || W.col[p + size] != c || p + size >= n) continue;
+            const int y = s_xy[p] >> 8;
+            if (y > 0 && W.col[p - 1] == c && W.col[p + size - 1] == c) continue;
+            uf_unite(parent, (uint32_t)p, (uint32_t)(p + size));
+        }
         __syncwarp();
+        // 2c: flatten to the root point
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p < NPAD) W.lab[p] = (p < n && W.col[p] != 0) ? (uint16_t)uf_find(parent, (uint32_t)p) : (uint16_t)0xFFFF;
+        }
+        __syncwarp();
+        ENC_T(1);
 
-        // ---- 3. group sizes, liberty counts, first 8 liberties
-        for (int p = lane; p < n; p += 32) {
-            int c = W.col[p];
-            if (c != 0) { atomicAdd(&W.cnt[label[p]], 1u << 16); continue; }
+        // ---- 3. group sizes and liberty counts; then the liberty lists of the side to move's groups
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p >= n) continue;
+            if (W.col[p] != 0) { atomicAdd(&W.cnt[W.lab[p]], 1u << 16); continue; }
             const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
-            uint32_t r[4]; int k = 0;
-            if (x > 0 && W.col[p - size] != 0) r[k++] = label[p - size];
-            if (x < size - 1 && W.col[p + size] != 0) r[k++] = label[p + size];
-            if (y > 0 && W.col[p - 1] != 0) r[k++] = label[p - 1];
-            if (y < size - 1 && W.col[p + 1] != 0) r[k++] = label[p + 1];
-            for (int j = 0; j < k; j++) {
-                bool dup = false;
-                for (int t = 0; t < j; t++) dup |= (r[t] == r[j]);
-                if (dup) continue;
-                uint32_t idx = atomicAdd(&W.cnt[r[j]], 1u) & 0xFFFFu;
-                if (idx < 8) W.liblist[r[j]][idx] = (uint16_t)p;
+            const uint32_t r0 = x > 0 ? W.lab[p - size] : 0xFFFFu, r1 = x < size - 1 ? W.lab[p + size] : 0xFFFFu;
+            const uint32_t r2 = y > 0 ? W.lab[p - 1] : 0xFFFFu, r3 = y < size - 1 ? W.lab[p + 1] : 0xFFFFu;
+            if (r0 != 0xFFFFu) atomicAdd(&W.cnt[r0], 1u);
+            if (r1 != 0xFFFFu && r1 != r0) atomicAdd(&W.cnt[r1], 1u);
+            if (r2 != 0xFFFFu && r2 != r0 && r2 != r1) atomicAdd(&W.cnt[r2], 1u);
+            if (r3 != 0xFFFFu && r3 != r0 && r3 != r1 && r3 != r2) atomicAdd(&W.cnt[r3], 1u);
+        }
+        __syncwarp();
+        {   // pool offsets: exclusive prefix sum of min(liberties, 8) over the root points of own groups
+            uint32_t base = 0;
+#pragma unroll 1
+            for (int k = 0; k < 12; k++) {
+                const int p = k * 32 + lane;
+                uint32_t m = 0;
+                if (p < n && W.col[p] == me && W.lab[p] == p) m = min(W.cnt[p] & 0xFFFFu, 8u);
+                uint32_t incl = m;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+                if (p < NPAD) W.off[p] = base + incl - m;
+                base += __shfl_sync(0xffffffffu, incl, 31);
             }
         }
         __syncwarp();
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p >= n || W.col[p] != 0) continue;
+            const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
+            uint32_t r[4];
+            r[0] = (x > 0 && W.col[p - size] == me) ? W.lab[p - size] : 0xFFFFu;
+            r[1] = (x < size - 1 && W.col[p + size] == me) ? W.lab[p + size] : 0xFFFFu;
+            r[2] = (y > 0 && W.col[p - 1] == me) ? W.lab[p - 1] : 0xFFFFu;
+            r[3] = (y < size - 1 && W.col[p + 1] == me) ? W.lab[p + 1] : 0xFFFFu;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                bool dup = r[j] == 0xFFFFu;
+#pragma unroll
+                for (int t = 0; t < j; t++) dup |= r[t] == r[j];
+                if (dup) continue;
+                const uint32_t o = atomicAdd(&W.off[r[j]], 1u << 16);
+                const uint32_t idx = o >> 16, at = (o & 0xFFFFu) + idx;
+                if (idx < 8 && at < POOL) W.pool[at] = (uint16_t)p;
+            }
+        }
+        __syncwarp();
+        ENC_T(2);
 
         // ---- 4. per-point codes
-        for (int p = lane; p < NPAD; p += 32) {
-            uint8_t c_libs = 0xFF, c_cap = 0xFF, c_sa = 0xFF, c_la = 0xFF, c_sens = 0xFF;
-            int c = p < n ? W.col[p] : 1;
+#pragma unroll 1
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            if (p >= NPAD) continue;
+            uint32_t c_libs = 0xF, c_cap = 0xF, c_sa = 0xF, c_la = 0xF, c_sens = 0xF, lad = 0;
+            const int c = p < n ? W.col[p] : 1;
             if (p < n && c != 0) {
-                int l = W.cnt[label[p]] & 0xFFFF;                         // preprocessing.py:46-61
-                if (l >= 1) c_libs = (uint8_t)(l >= 8 ? 7 : l - 1);
+                const int l = W.cnt[W.lab[p]] & 0xFFFF;                       // preprocessing.py:46-61
+                if (l >= 1) c_libs = (uint32_t)(l >= 8 ? 7 : l - 1);
             } else if (p < n) {
                 const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
-                int nb[4], k = 0;                                        // go.py:96 order
-                if (x > 0) nb[k++] = p - size;
-                if (x < size - 1) nb[k++] = p + size;
-                if (y > 0) nb[k++] = p - 1;
-                if (y < size - 1) nb[k++] = p + 1;
-                uint32_t roots[4];
-                bool has_empty = false, ok = false, all_mine = true;
-                int cap = 0;
-                for (int j = 0; j < k; j++) {
-                    int q = nb[j], cq = W.col[q];
-                    roots[j] = 0xFFFFFFFFu;
-                    if (cq != me) all_mine = false;
-                    if (cq == 0) { has_empty = true; continue; }
-                    uint32_t r = label[q], cn = W.cnt[r];
-                    int libs = cn & 0xFFFF;
-                    roots[j] = r;
-                    bool dup = false;
-                    for (int t = 0; t < j; t++) dup |= (roots[t] == r);
-                    if (cq == me) { if (libs > 1) ok = true; }             // go.py:192-195
-                    else if (libs == 1) { ok = true; if (!dup) cap += cn >> 16; }  // go.py:197-199, pp:79-86
+                int nb[4];                                                    // go.py:96 order; -1 = off the board
+                nb[0] = x > 0 ? p - size : -1; nb[1] = x < size - 1 ? p + size : -1;
+                nb[2] = y > 0 ? p - 1 : -1;    nb[3] = y < size - 1 ? p + 1 : -1;
+                int cq[4];
+                uint32_t rt[4], cn[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {                                 // all loads first: they are independent
+                    const int q = nb[j] < 0 ? p : nb[j];
+                    cq[j] = W.col[q];
+                    rt[j] = W.lab[q];
                 }
-                bool legal = (p != ko) && (has_empty || ok);              // go.py:204-216
+#pragma unroll
+                for (int j = 0; j < 4; j++) cn[j] = (nb[j] >= 0 && cq[j] != 0) ? W.cnt[rt[j]] : 0;
+                bool has_empty = false, ok = false, all_mine = true, lcap = false, lesc = false;
+                int cap = 0, gsz = 1, ko_n = 0;
+                uint32_t ro[4] = {0xFFFEu, 0xFFFEu, 0xFFFEu, 0xFFFEu}, lo[4] = {0, 0, 0, 0};
+                bool big = false;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (nb[j] < 0) continue;
+                    if (cq[j] != me) all_mine = false;
+                    if (cq[j] == 0) { has_empty = true; continue; }
+                    const int libs = cn[j] & 0xFFFF;
+                    bool dup = false;
+#pragma unroll
+                    for (int t = 0; t < j; t++) dup |= (nb[t] >= 0 && cq[t] != 0 && rt[t] == rt[j]);
+                    if (cq[j] == me) {
+                        if (libs > 1) ok = true;                              // go.py:192-195
+                        if (libs == 1) lesc = true;
+                        if (!dup) {
+                            gsz += cn[j] >> 16;
+                            if (libs > 8) big = true;                         // >= 9 liberties: |L| >= 8 for certain
+#pragma unroll
+                            for (int t = 0; t < 4; t++) if (t == ko_n) { ro[t] = rt[j]; lo[t] = (uint32_t)libs; }
+                            ko_n++;
+                        }
+                    } else {
+                        if (libs == 1) { ok = true; if (!dup) cap += cn[j] >> 16; }   // go.py:197-199, pp:79-86
+                        if (libs == 2) lcap = true;
+                    }
+                }
+                const bool legal = (p != ko) && (has_empty || ok);            // go.py:204-216
                 if (legal) {
-                    c_cap = (uint8_t)min(cap, 7);                         // preprocessing.py:87
-                    // L = empty neighbours U liberties of adjacent own groups, minus p (pp:98-109, 131-142)
-                    int gsz = 1, cntL = 0;
-                    bool big = false, any_own = false;
-                    for (int j = 0; j < k; j++) {
-                        int q = nb[j], cq = W.col[q];
-                        if (cq == 0) { W.lanebits[q >> 5][lane] |= 1u << (q & 31); continue; }
-                        if (cq != me) continue;
-                        bool dup = false;
-                        for (int t = 0; t < j; t++) dup |= (roots[t] == roots[j]);
-                        if (dup) continue;
-                        any_own = true;
-                        uint32_t cn = W.cnt[roots[j]];
-                        int libs = cn & 0xFFFF;
-                        gsz += cn >> 16;
-                        if (libs > 8) { big = true; continue; }          // >= 9 liberties: |L| >= 8 for certain
-                        for (int t = 0; t < libs; t++) {
-                            int e = W.liblist[roots[j]][t];
-                            W.lanebits[e >> 5][lane] |= 1u << (e & 31);
+                    c_cap = (uint32_t)min(cap, 7);                            // preprocessing.py:87
+                    // |L|, L = empty neighbours U liberties of adjacent own groups, minus p (pp:98-109, 131-142)
+                    int cntL = 8;
+                    if (!big) {
+                        const uint32_t r01 = ro[0] | ro[1] << 16, r23 = ro[2] | ro[3] << 16;
+                        const uint32_t l123 = lo[1] | lo[2] << 8 | lo[3] << 16;
+                        cntL = ko_n > 0 ? (int)lo[0] - 1 : 0;
+                        if (ko_n == 0) {
+#pragma unroll
+                            for (int j = 0; j < 4; j++) cntL += (nb[j] >= 0 && cq[j] == 0) ? 1 : 0;
+                        } else {
+                            uint32_t emp = 0;   // the (<= 3) empty neighbours, 9 bits each, 0x1FF = none
+#pragma unroll
+                            for (int j = 3; j >= 0; j--) if (nb[j] >= 0 && cq[j] == 0) emp = emp << 9 | (uint32_t)nb[j];
+                            int nemp = 0;
+#pragma unroll
+                            for (int j = 0; j < 4; j++) nemp += (nb[j] >= 0 && cq[j] == 0) ? 1 : 0;
+#pragma unroll 1
+                            for (int t = 0; t < nemp; t++, emp >>= 9)
+                                if (!touches(W.lab, s_xy, size, (int)(emp & 0x1FFu), r01, r23, 4)) cntL++;
+#pragma unroll 1
+                            for (int j = 1; j < ko_n; j++) {
+                                const uint32_t rj = ((j < 2 ? r01 : r23) >> (16 * (j & 1))) & 0xFFFFu, lj = (l123 >> (8 * (j - 1))) & 0xFFu;
+                                const uint32_t o = W.off[rj] & 0xFFFFu;
+#pragma unroll 1
+                                for (uint32_t t = 0; t < lj; t++) {
+                                    const int e = W.pool[o + t];
+                                    if (e != p && !touches(W.lab, s_xy, size, e, r01, r23, j)) cntL++;
+                                }
+                            }
                         }
                     }
-                    (void)any_own;
-                    W.lanebits[p >> 5][lane] &= ~(1u << (p & 31));
-#pragma unroll
-                    for (int w = 0; w < LW; w++) { cntL += __popc(W.lanebits[w][lane]); W.lanebits[w][lane] = 0; }
-                    if (big) cntL = max(cntL, 8);
-                    if (cntL == 1) c_sa = (uint8_t)min(gsz - 1, 7);        // preprocessing.py:111-114
-                    c_la = cntL == 0 ? 7 : (uint8_t)min(7, cntL - 1);     // preprocessing.py:143 (-1 wraps to plane 7)
+                    if (cntL == 1) c_sa = (uint32_t)min(gsz - 1, 7);          // preprocessing.py:111-114
+                    c_la = cntL == 0 ? 7u : (uint32_t)min(7, cntL - 1);       // preprocessing.py:143 (-1 wraps to plane 7)
                     // go.py:261-267: legal and not is_eye(p, current_player)
                     c_sens = 0;
-                    if (tab.need_eye && all_mine && is_eye(W.col, size, p, me)) c_sens = 0xFF;
+                    if (tab.need_eye && all_mine && is_eye(W.col, size, p, me)) c_sens = 0xF;
+                    if (tab.need_ladder) lad = (lcap ? 1u : 0u) | (lesc ? 2u : 0u);
                 }
             }
-            CODE(C_LIBS, p) = c_libs;
-            CODE(C_CAPTURE, p) = c_cap;
-            CODE(C_SELFATARI, p) = c_sa;
-            CODE(C_LIBSAFTER, p) = c_la;
-            CODE(C_SENSIBLE, p) = c_sens;
+            W.codes[1][p] = (uint8_t)(c_libs | c_cap << 4);
+            W.codes[2][p] = (uint8_t)(c_sa | c_la << 4);
+            W.codes[3][p] = (uint8_t)(c_sens | lad << 4);
         }
         __syncwarp();
+        ENC_T(3);
 
-        // ---- 5. ladder planes, first half: mark the moves that touch a prey group (an adjacent opponent group with
-        // two liberties / an adjacent own group in atari).  Everything else is 0 for certain; the marked moves are
-        // resolved by ladder_resolve_kernel, which runs at full occupancy with dynamic work distribution.
-        if (tab.need_ladder) {
-            for (int p = lane; p < n; p += 32) {
-                if (CODE(C_CAPTURE, p) == 0xFF) continue;  // not a legal move
-                const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
-                bool cap = false, esc = false;
-                int nb[4], k = 0;
-                if (x > 0) nb[k++] = p - size;
-                if (x < size - 1) nb[k++] = p + size;
-                if (y > 0) nb[k++] = p - 1;
-                if (y < size - 1) nb[k++] = p + 1;
-                for (int j = 0; j < k; j++) {
-                    int cq = W.col[nb[j]];
-                    if (cq == 0) continue;
-                    int libs = W.cnt[label[nb[j]]] & 0xFFFF;
-                    if (cq == -me && libs == 2) cap = true;
-                    if (cq == me && libs == 1) esc = true;
-                }
-                if (cap) CODE(C_LADCAP, p) = 0;
-                if (esc) CODE(C_LADESC, p) = 0;
+        // ---- 5. ladder candidates -> work list (everything else on the two planes is 0 for certain)
+        if (tab.need_ladder && work.entries) {
+            int total = 0;
+#pragma unroll 1
+            for (int k = 0; k < 12; k++) {
+                const int p = k * 32 + lane;
+                const uint32_t f = p < n ? (uint32_t)(W.codes[3][p] >> 4) : 0u;
+                total += __popc(__ballot_sync(0xffffffffu, f & 1u)) + __popc(__ballot_sync(0xffffffffu, f & 2u));
             }
-            __syncwarp();
+            if (total > 0) {
+                unsigned int base = 0;
+                if (lane == 0) base = atomicAdd(work.head, (unsigned int)total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll 1
+                for (int k = 0; k < 12; k++) {
+                    const int p = k * 32 + lane;
+                    const uint32_t f = p < n ? (uint32_t)(W.codes[3][p] >> 4) : 0u;
+                    const uint32_t bc = __ballot_sync(0xffffffffu, f & 1u), be = __ballot_sync(0xffffffffu, f & 2u);
+                    const uint32_t e = (uint32_t)pos << 10 | (uint32_t)p;
+                    if (f & 1u) work.entries[base + __popc(bc & lt)] = e;
+                    if (f & 2u) work.entries[base + __popc(bc) + __popc(be & lt)] = e | 512u;
+                    base += __popc(bc) + __popc(be);
+                }
+            }
         }
+        ENC_T(4);
 
-        // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (code[arr][p] == val).
+        // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (nibble code of the plane's family == its value).
         // A position's planes are one contiguous run of F*n bytes: a few head bytes up to the next
         // 16-byte boundary, 16-byte vectors, a few tail bytes.
+        const uint8_t* codes = &W.codes[0][0];
         const int total = F * n;
         uint8_t* out = g_out + (size_t)pos * total;
         int lead = (int)((16 - (reinterpret_cast<uintptr_t>(out) & 15)) & 15);
         if (lead > total) lead = total;
         const int nvec = (total - lead) >> 4;
         const int tail0 = lead + (nvec << 4);
+        const uint32_t black = me == 1 ? 0x01010101u : 0u;
         for (int i = lane; i < lead + (total - tail0); i += 32) {
-            int b = i < lead ? i : tail0 + (i - lead);
-            int plane = b / n, p = b - plane * n;
-            out[b] = CODE(s_arr[plane], p) == s_val[plane];
+            const int b = i < lead ? i : tail0 + (i - lead);
+            const int plane = b / n, p = b - plane * n;
+            out[b] = (uint8_t)point_value(codes, s_tab[plane], p, black);
         }
         for (int v = lane; v < nvec; v += 32) {
-            int i0 = lead + (v << 4);
-            int plane = i0 / n, p = i0 - plane * n;
+            const int i0 = lead + (v << 4);
+            int plane = (int)((float)i0 * inv_n);
+            int p = i0 - plane * n;
+            if (p < 0) { plane--; p += n; }
+            if (p >= n) { plane++; p -= n; }
             uint32_t wds[4];
 #pragma unroll
             for (int w = 0; w < 4; w++) {
-                uint32_t word;
-                if (p + 3 < n) {
-                    const uint32_t* ca = W.codes[s_arr[plane]];
-                    uint32_t lo = ca[p >> 2], hi = ca[(p >> 2) + 1];
-                    uint32_t cv = __funnelshift_r(lo, hi, (p & 3) * 8);
-                    word = __vcmpeq4(cv, s_val[plane] * 0x01010101u) & 0x01010101u;
+                // four points of this plane from p on; where the plane ends inside the word, the rest comes from the next
+                // plane's first points (n >= 4: a word never spans more than two planes)
+                uint32_t word = plane_word(codes, s_tab[plane], p, black);
+                const int left = n - p;
+                if (left < 4) {
+                    const uint32_t nxt = plane + 1 < F ? plane_word(codes, s_tab[plane + 1], 0, black) : 0u;
+                    word = (word & (0xFFFFFFFFu >> (8 * (4 - left)))) | nxt << (8 * left);
+                    p = 4 - left; plane++;
+                } else {
                     p += 4;
                     if (p == n) { p = 0; plane++; }
-                } else {
-                    word = 0;
-#pragma unroll
-                    for (int b = 0; b < 4; b++) {
-                        uint32_t bit = (plane < F) && (CODE(s_arr[plane], p) == s_val[plane]);
-                        word |= bit << (8 * b);
-                        if (++p == n) { p = 0; plane++; }
-                    }
                 }
                 wds[w] = word;
             }
             *reinterpret_cast<uint4*>(out + i0) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
         }
         __syncwarp();
+        ENC_T(5);
     }
 }
 
-#undef CODE
-
-// Ladder planes, second half.  Input: the planes encode_kernel wrote, whose ladder planes hold 1 on every candidate
-// move.  Each warp claims positions one at a time from a global counter, lists the position's candidates (ascending, by
-// ballot) in shared memory and reads them out one after the other with the whole warp (ladder_warp.cuh: the board's bit
-// sets are spread over the lanes, so the search has one control path); each 0/1 answer overwrites the candidate mark.
+// Ladder planes, second half.  encode_kernel has queued every candidate move (position, kind, point) and stored each
+// position's stones as bit boards.  Warps take queries from the list one at a time (a global counter: the launch ends at
+// most one query after the list runs dry, whatever the spread of query costs) and read each out with the whole warp
+// (ladder_warp.cuh: the board's bit sets are spread over the lanes, so the search has one control path).  Only "yes"
+// answers are written: encode_kernel has already written zeros on both planes.
 constexpr int kResolveWarps = 8;
 
 __global__ void __launch_bounds__(kResolveWarps * 32)
-ladder_resolve_kernel(const int8_t* __restrict__ g_board, const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko,
-                      int npos, int size, int n_planes, int cap_plane, int esc_plane, uint8_t* __restrict__ g_out,
-                      unsigned int* __restrict__ counter, int slices) {
+ladder_resolve_kernel(const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko, int size, int n_planes,
+                      int cap_plane, int esc_plane, uint8_t* __restrict__ g_out, LadderWork work) {
     __shared__ LadderFrame s_frames[kResolveWarps][kLadderDepth + 2];
-    __shared__ uint16_t s_list[kResolveWarps][2 * MAXN];  // kind << 9 | point
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = size * size;
     WBoard B;
     B.m = wmasks_make(size, lane);
     B.size = size; B.lane = lane;
+    const unsigned int total = work.head[0];
+    unsigned int cur = 0xFFFFFFFFu;
     while (true) {
-        // work unit = (position, slice): a small batch is cut into `slices` shares of each position's candidates (by point),
-        // so that one position with many deep read-outs does not become the whole launch's critical path
-        unsigned int unit = 0;
-        if (lane == 0) unit = atomicAdd(counter, 1u);
-        unit = __shfl_sync(0xffffffffu, unit, 0);
-        if (unit >= (unsigned)npos * (unsigned)slices) break;
-        const unsigned int pos = unit / (unsigned)slices;
-        const int slice = (int)(unit - pos * (unsigned)slices);
-        uint8_t* planes = g_out + (size_t)pos * n_planes * n;
-        int count = 0;
-        for (int kind = 0; kind < 2; kind++) {
-            const int pl = kind ? esc_plane : cap_plane;
-            if (pl < 0) continue;
-            for (int p0 = 0; p0 < n; p0 += 32) {
-                const int p = p0 + lane;
-                // a share = the candidates at points p with p % slices == slice: other warps are overwriting the marks of their
-                // own shares with answers at the same time, so membership must not depend on the other marks
-                const bool mark = p < n && (p % slices) == slice && planes[(size_t)pl * n + p] != 0;
-                const unsigned bal = __ballot_sync(0xffffffffu, mark);
-                if (mark) s_list[warp][count + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)(kind << 9 | p);
-                count += __popc(bal);
-            }
+        unsigned int idx = 0;
+        if (lane == 0) idx = atomicAdd(&work.head[1], 1u);
+        idx = __shfl_sync(0xffffffffu, idx, 0);
+        if (idx >= total) break;
+        const uint32_t e = work.entries[idx];
+        const unsigned int pos = e >> 10;
+        const int kind = (e >> 9) & 1, a = e & 511;
+        const int pl = kind ? esc_plane : cap_plane;
+        if (pl < 0) continue;
+        if (pos != cur) {   // wl_query leaves the board as it found it: consecutive queries of one position share the load
+            B.blk = lane < 12 ? work.bits[(size_t)pos * 24 + lane] : 0u;
+            B.wht = lane < 12 ? work.bits[(size_t)pos * 24 + 12 + lane] : 0u;
+            cur = pos;
         }
-        __syncwarp();
-        if (count == 0) continue;
-        wl_load(B, g_board + (size_t)pos * n, size, g_player[pos], g_ko[pos], lane);
-        for (int i = 0; i < count; i++) {
-            const int c = s_list[warp][i];
-            const int kind = c >> 9, a = c & 0x1FF;
-            const bool yes = wl_query(B, s_frames[warp], kind, a);
-            if (lane == 0) planes[(size_t)(kind ? esc_plane : cap_plane) * n + a] = yes ? 1 : 0;
-        }
+        B.player = g_player[pos]; B.ko = g_ko[pos]; B.undo_top = 0;
+        const bool yes = wl_query(B, s_frames[warp], kind, a);
+        if (yes && lane == 0) g_out[((size_t)pos * n_planes + pl) * n + a] = 1;
         __syncwarp();
     }
 }
@@ -408,55 +553,91 @@ __global__ void ladder_copy_plane_kernel(uint8_t* out, int npos, int n, int n_pl
 
 }  // namespace enc
 
-// work counters of ladder_resolve_kernel: a small ring so that encodes in flight on different streams do not share one
-static __device__ unsigned int g_ladder_counters[16];
-
 size_t encode_smem_bytes() { return sizeof(enc::WarpMem) * enc::WARPS; }
+
+#ifdef AG_ENC_PROFILE
+extern "C" int ag_debug_enc_phases(unsigned long long* h_out, int reset) {
+    cudaMemcpyFromSymbol(h_out, enc::g_enc_phase_cycles, sizeof(unsigned long long) * 8);
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(enc::g_enc_phase_cycles, z, sizeof(z)); }
+    return 0;
+}
+#endif
+
+// Work-list memory of the ladder read-out: worst case 2 queries per point, so 722 entries + 24 bit-board words per position.
+// It belongs to the library, per device, allocated on the first encode that asks for ladder planes and grown (never
+// shrunk) when a call brings more positions than any before it; calls in between allocate nothing.  Four slots are
+// handed out in turn, so up to four encodes may be in flight on different streams of one device.
+namespace {
+constexpr int kWorkSlots = 4;
+constexpr int kWorkChunk = 65536;          // positions per launch pair (190 MB of work list at most)
+constexpr int kWorkEntriesPerPos = 722;
+struct WorkSlot { unsigned char* mem; size_t cap_pos; };
+struct WorkSlots { WorkSlot s[kWorkSlots]; };
+PerDevice<WorkSlots> g_work;
+std::atomic<unsigned> g_next_slot{0};
+
+int work_get(int npos, enc::LadderWork* w) {
+    WorkSlot& s = g_work.cur().s[g_next_slot.fetch_add(1) % kWorkSlots];
+    if ((size_t)npos > s.cap_pos) {
+        size_t cap = 1024;
+        while (cap < (size_t)npos) cap <<= 1;
+        if (s.mem) AG_CUDA(cudaFree(s.mem));   // waits for the kernels that may still read it
+        s.mem = nullptr; s.cap_pos = 0;
+        AG_CUDA(cudaMalloc(&s.mem, 256 + cap * (24 + kWorkEntriesPerPos) * sizeof(uint32_t)));
+        s.cap_pos = cap;
+    }
+    w->head = reinterpret_cast<unsigned int*>(s.mem);
+    w->bits = reinterpret_cast<uint32_t*>(s.mem + 256);
+    w->entries = w->bits + s.cap_pos * 24;
+    return AG_OK;
+}
+}  // namespace
 
 int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player, const int16_t* ko, int npos, int size,
                   const enc::PlaneTable& tab, uint8_t* out, cudaStream_t stream) {
     static PerDevice<bool> configured_dev;
     bool& configured = configured_dev.cur();
-    size_t smem = encode_smem_bytes();
+    const size_t smem = encode_smem_bytes();
     if (!configured) {
         AG_CUDA(cudaFuncSetAttribute(enc::encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
-    int blocks_needed = (npos + enc::WARPS - 1) / enc::WARPS;
-    int max_blocks = sm_count() * 16;  // grid-stride beyond that
-    int grid = blocks_needed < max_blocks ? blocks_needed : max_blocks;
-    if (grid < 1) grid = 1;
-    enc::encode_kernel<<<grid, enc::WARPS * 32, smem, stream>>>(board, age, player, ko, npos, size, tab, out);
-    AG_LAUNCH_CHECK("encode_kernel");
-    if (!tab.need_ladder) return AG_OK;
     int cap_plane = -1, esc_plane = -1;
     for (int j = 0; j < tab.n_planes; j++) {
         if (tab.arr[j] == enc::C_LADCAP && cap_plane < 0) cap_plane = j;
         if (tab.arr[j] == enc::C_LADESC && esc_plane < 0) esc_plane = j;
     }
-    // the symbol's address differs per device; the ring position is shared by host threads
-    static PerDevice<unsigned int*> counters_dev;
-    static std::atomic<unsigned> next_counter{0};
-    unsigned int*& counters = counters_dev.cur();
-    if (!counters) AG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_ladder_counters));
-    unsigned int* ctr = counters + (next_counter.fetch_add(1) & 15);
-    AG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned int), stream));
-    // enough work units to fill the machine even for a handful of positions; and never whole positions: the launch ends with
-    // the slowest unit, and one position can hold several deep read-outs
-    int slices = 65536 / (npos > 0 ? npos : 1);
-    slices = slices < 8 ? 8 : (slices > 16 ? 16 : slices);   // measured at 16384 positions: 4 -> 4.37 ms, 8 -> 4.19 ms, 16 -> 4.23 ms
-    { static int forced = -1; if (forced < 0) { const char* e = getenv("AG_LADDER_SLICES"); forced = e ? atoi(e) : 0; } if (forced > 0) slices = forced; }
-    int rgrid = sm_count() * 8;
-    int need = (npos * slices + enc::kResolveWarps - 1) / enc::kResolveWarps;
-    if (rgrid > need) rgrid = need;
-    enc::ladder_resolve_kernel<<<rgrid, enc::kResolveWarps * 32, 0, stream>>>(board, player, ko, npos, size, tab.n_planes, cap_plane, esc_plane, out, ctr,
-                                                                              slices);
-    AG_LAUNCH_CHECK("ladder_resolve_kernel");
-    for (int j = 0; j < tab.n_planes; j++) {  // repeated ladder features
-        int src = tab.arr[j] == enc::C_LADCAP ? cap_plane : (tab.arr[j] == enc::C_LADESC ? esc_plane : -1);
-        if (src < 0 || src == j) continue;
-        enc::ladder_copy_plane_kernel<<<sm_count() * 4, 256, 0, stream>>>(out, npos, size * size, tab.n_planes, src, j);
-        AG_LAUNCH_CHECK("ladder_copy_plane_kernel");
+    const int n = size * size;
+    for (int start = 0; start < npos; start += kWorkChunk) {
+        const int cnt = npos - start < kWorkChunk ? npos - start : kWorkChunk;
+        enc::LadderWork work = {nullptr, nullptr, nullptr};
+        if (tab.need_ladder) {
+            int rc = work_get(cnt, &work);
+            if (rc) return rc;
+            AG_CUDA(cudaMemsetAsync(work.head, 0, 2 * sizeof(unsigned int), stream));
+        }
+        // small batches: fewer warps per CTA so that every SM gets positions
+        int warps = cnt / (sm_count() * 3);
+        warps = warps < 1 ? 1 : (warps > enc::WARPS ? enc::WARPS : warps);
+        const int blocks_needed = (cnt + warps - 1) / warps;
+        const int max_blocks = sm_count() * 24;  // grid-stride beyond that
+        const int grid = blocks_needed < max_blocks ? blocks_needed : max_blocks;
+        uint8_t* o = out + (size_t)start * tab.n_planes * n;
+        enc::encode_kernel<<<grid, warps * 32, sizeof(enc::WarpMem) * warps, stream>>>(
+            board + (size_t)start * n, age + (size_t)start * n, player + start, ko + start, cnt, size, tab, o, work);
+        AG_LAUNCH_CHECK("encode_kernel");
+        if (!tab.need_ladder) continue;
+        enc::ladder_resolve_kernel<<<sm_count() * 6, enc::kResolveWarps * 32, 0, stream>>>(player + start, ko + start, size, tab.n_planes,
+                                                                                          cap_plane, esc_plane, o, work);
+        AG_LAUNCH_CHECK("ladder_resolve_kernel");
+    }
+    if (tab.need_ladder) {
+        for (int j = 0; j < tab.n_planes; j++) {  // repeated ladder features
+            int src = tab.arr[j] == enc::C_LADCAP ? cap_plane : (tab.arr[j] == enc::C_LADESC ? esc_plane : -1);
+            if (src < 0 || src == j) continue;
+            enc::ladder_copy_plane_kernel<<<sm_count() * 4, 256, 0, stream>>>(out, npos, n, tab.n_planes, src, j);
+            AG_LAUNCH_CHECK("ladder_copy_plane_kernel");
+        }
     }
     return AG_OK;
 }

@@ -9,7 +9,7 @@ namespace enc {
 constexpr int MAXN = 361;        // 19x19
 constexpr int NPAD = 368;        // points padded to a multiple of 16
 constexpr int LW = 12;           // 361-bit sets as 12 words
-constexpr int WARPS = 5;         // positions per CTA (one warp each): 3 CTAs x 5 warps fill the 227 KB of an SM (4 gave 12 warps)
+constexpr int WARPS = 10;        // positions per CTA (one warp each): 3 CTAs x 10 warps fill the 227 KB of an SM
 constexpr int MAX_PLANES = 64;   // longest feature list the kernel accepts, in planes
 
 // feature ids of the C ABI (order of DEFAULT_FEATURES, preprocessing.py:211-214, + value-net colour)
