@@ -132,7 +132,8 @@ __device__ __forceinline__ uint32_t plane_desc(int arr, int val) {
     }
 }
 
-// work list of ladder queries: header {appended, taken} then entries position << 10 | kind << 9 | point
+// work list of ladder queries: header {appended, taken} then entries position << 16 | point << 5 | kind << 4 | prey mask
+// (bit j of the mask: neighbour j of the point, in go.py:96 order, is the first to touch a prey group)
 struct LadderWork {
     unsigned int* head;      // [0] entries appended by encode_kernel, [1] next entry to take (ladder_resolve_kernel)
     uint32_t* entries;
@@ -330,7 +331,6 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
 #pragma unroll 1
         for (int k = 0; k < 12; k++) {
             const int p = k * 32 + lane;
-            if (p >= NPAD) continue;
             uint32_t c_libs = 0xF, c_cap = 0xF, c_sa = 0xF, c_la = 0xF, c_sens = 0xF, lad = 0;
             const int c = p < n ? W.col[p] : 1;
             if (p < n && c != 0) {
@@ -351,7 +351,8 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                 }
 #pragma unroll
                 for (int j = 0; j < 4; j++) cn[j] = (nb[j] >= 0 && cq[j] != 0) ? W.cnt[rt[j]] : 0;
-                bool has_empty = false, ok = false, all_mine = true, lcap = false, lesc = false;
+                bool has_empty = false, ok = false, all_mine = true;
+                uint32_t mcap = 0, mesc = 0;   // neighbours (go.py:96 order) that name a ladder prey group for the first time
                 int cap = 0, gsz = 1, ko_n = 0;
                 uint32_t ro[4] = {0xFFFEu, 0xFFFEu, 0xFFFEu, 0xFFFEu}, lo[4] = {0, 0, 0, 0};
                 bool big = false;
@@ -366,7 +367,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                     for (int t = 0; t < j; t++) dup |= (nb[t] >= 0 && cq[t] != 0 && rt[t] == rt[j]);
                     if (cq[j] == me) {
                         if (libs > 1) ok = true;                              // go.py:192-195
-                        if (libs == 1) lesc = true;
+                        if (libs == 1 && !dup) mesc |= 1u << j;
                         if (!dup) {
                             gsz += cn[j] >> 16;
                             if (libs > 8) big = true;                         // >= 9 liberties: |L| >= 8 for certain
@@ -376,7 +377,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                         }
                     } else {
                         if (libs == 1) { ok = true; if (!dup) cap += cn[j] >> 16; }   // go.py:197-199, pp:79-86
-                        if (libs == 2) lcap = true;
+                        if (libs == 2 && !dup) mcap |= 1u << j;
                     }
                 }
                 const bool legal = (p != ko) && (has_empty || ok);            // go.py:204-216
@@ -418,42 +419,33 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                     // go.py:261-267: legal and not is_eye(p, current_player)
                     c_sens = 0;
                     if (tab.need_eye && all_mine && is_eye(W.col, size, p, me)) c_sens = 0xF;
-                    if (tab.need_ladder) lad = (lcap ? 1u : 0u) | (lesc ? 2u : 0u);
+                    if (tab.need_ladder) lad = mcap | mesc << 4;
                 }
             }
-            W.codes[1][p] = (uint8_t)(c_libs | c_cap << 4);
-            W.codes[2][p] = (uint8_t)(c_sa | c_la << 4);
-            W.codes[3][p] = (uint8_t)(c_sens | lad << 4);
+            if (p < NPAD) {
+                W.codes[1][p] = (uint8_t)(c_libs | c_cap << 4);
+                W.codes[2][p] = (uint8_t)(c_sa | c_la << 4);
+                W.codes[3][p] = (uint8_t)c_sens;
+            }
+            // ---- 5. ladder candidates (moves touching an opponent group with two liberties / an own group in atari) -> work
+            // list, with the prey neighbours the read-out starts from; everything else on the two planes is 0 for certain
+            if (tab.need_ladder && work.entries) {
+                __syncwarp();
+                const uint32_t bc = __ballot_sync(0xffffffffu, (lad & 0xFu) != 0), be = __ballot_sync(0xffffffffu, (lad >> 4) != 0);
+                if (bc | be) {
+                    unsigned int base = 0;
+                    if (lane == 0) base = atomicAdd(work.head, (unsigned int)(__popc(bc) + __popc(be)));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    const uint32_t lt = (1u << lane) - 1u;
+                    const uint32_t e = (uint32_t)pos << 16 | (uint32_t)p << 5;
+                    if (lad & 0xFu) work.entries[base + __popc(bc & lt)] = e | (lad & 0xFu);
+                    if (lad >> 4) work.entries[base + __popc(bc) + __popc(be & lt)] = e | 16u | (lad >> 4);
+                }
+            }
         }
         __syncwarp();
         ENC_T(3);
 
-        // ---- 5. ladder candidates -> work list (everything else on the two planes is 0 for certain)
-        if (tab.need_ladder && work.entries) {
-            int total = 0;
-#pragma unroll 1
-            for (int k = 0; k < 12; k++) {
-                const int p = k * 32 + lane;
-                const uint32_t f = p < n ? (uint32_t)(W.codes[3][p] >> 4) : 0u;
-                total += __popc(__ballot_sync(0xffffffffu, f & 1u)) + __popc(__ballot_sync(0xffffffffu, f & 2u));
-            }
-            if (total > 0) {
-                unsigned int base = 0;
-                if (lane == 0) base = atomicAdd(work.head, (unsigned int)total);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll 1
-                for (int k = 0; k < 12; k++) {
-                    const int p = k * 32 + lane;
-                    const uint32_t f = p < n ? (uint32_t)(W.codes[3][p] >> 4) : 0u;
-                    const uint32_t bc = __ballot_sync(0xffffffffu, f & 1u), be = __ballot_sync(0xffffffffu, f & 2u);
-                    const uint32_t e = (uint32_t)pos << 10 | (uint32_t)p;
-                    if (f & 1u) work.entries[base + __popc(bc & lt)] = e;
-                    if (f & 2u) work.entries[base + __popc(bc) + __popc(be & lt)] = e | 512u;
-                    base += __popc(bc) + __popc(be);
-                }
-            }
-        }
         ENC_T(4);
 
         // ---- 6. one-hot expansion, coalesced stores.  out[pos][plane][p] = (nibble code of the plane's family == its value).
@@ -526,8 +518,8 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_player, const int16_t* __rest
         idx = __shfl_sync(0xffffffffu, idx, 0);
         if (idx >= total) break;
         const uint32_t e = work.entries[idx];
-        const unsigned int pos = e >> 10;
-        const int kind = (e >> 9) & 1, a = e & 511;
+        const unsigned int pos = e >> 16;           // position << 16 | point << 5 | kind << 4 | prey-neighbour mask
+        const int kind = (e >> 4) & 1, a = (e >> 5) & 511;
         const int pl = kind ? esc_plane : cap_plane;
         if (pl < 0) continue;
         if (pos != cur) {   // wl_query leaves the board as it found it: consecutive queries of one position share the load
@@ -536,7 +528,7 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_player, const int16_t* __rest
             cur = pos;
         }
         B.player = g_player[pos]; B.ko = g_ko[pos]; B.undo_top = 0;
-        const bool yes = wl_query(B, s_frames[warp], kind, a);
+        const bool yes = wl_query(B, s_frames[warp], kind, a, (int)(e & 15u));
         if (yes && lane == 0) g_out[((size_t)pos * n_planes + pl) * n + a] = 1;
         __syncwarp();
     }

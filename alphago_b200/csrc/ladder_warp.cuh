@@ -72,6 +72,8 @@ struct WBoard {
     uint32_t undo_cap[kLadderDepth + 2];   // per move on the path: this lane's word of the captured stones
     int16_t undo_pt[kLadderDepth + 2], undo_ko[kLadderDepth + 2];
     uint32_t replies[kLadderDepth + 2];    // per frame: this lane's word of the current prey's reply set
+    uint32_t pgrp[kLadderDepth + 2];       // per frame: this lane's word of the prey group after the frame's move
+    uint32_t plib[kLadderDepth + 2];       // per frame: ... and of that group's liberties
     int undo_top;
 };
 
@@ -84,6 +86,15 @@ __device__ __forceinline__ uint32_t wl_dilate(const WBoard& B, uint32_t g) {
     const uint32_t left = __funnelshift_r(g & ~B.m.col_first, next & ~B.m.col_first_next, 1);               // y - 1 (not from column 0)
     const uint32_t right = __funnelshift_l(prev & ~B.m.col_last_prev, g & ~B.m.col_last, 1);                // y + 1 (not from the last column)
     return (up | down | left | right) & B.m.all;
+}
+// stones / points with at least two members of `e` among their four neighbours (bit-sliced count of the four shifted copies)
+__device__ __forceinline__ uint32_t wl_two_neighbours_in(const WBoard& B, uint32_t e) {
+    const uint32_t prev = __shfl_sync(kFullWarp, e, (B.lane + 31) & 31), next = __shfl_sync(kFullWarp, e, (B.lane + 1) & 31);
+    const uint32_t up = __funnelshift_r(e, next, B.size);
+    const uint32_t down = __funnelshift_l(prev, e, B.size);
+    const uint32_t left = __funnelshift_r(e & ~B.m.col_first, next & ~B.m.col_first_next, 1);
+    const uint32_t right = __funnelshift_l(prev & ~B.m.col_last_prev, e & ~B.m.col_last, 1);
+    return ((up & down) | (left & right) | ((up | down) & (left | right))) & B.m.all;
 }
 __device__ __forceinline__ int wl_colour(const WBoard& B, int p) {
     const uint32_t bw = __shfl_sync(kFullWarp, B.blk, p >> 5), ww = __shfl_sync(kFullWarp, B.wht, p >> 5);
@@ -171,10 +182,21 @@ __device__ __forceinline__ void wl_undo(WBoard& B) {
 
 // is (kind ? ladder_escape : ladder_capture)(a) true on board B for the side to move?  B is left unchanged.
 // fr: kLadderDepth + 2 frames in shared memory, private to this warp (every lane writes the same values).
-__device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, int a) {
+// prey_mask != 0: the caller (the encoder) knows that a is legal and which of its neighbours (go.py:96 order: x-1, x+1, y-1, y+1)
+// name the prey groups -- exactly what LP_ENTER would find -- so the root frame starts past it, with its node already counted.
+__device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, int a, int prey_mask = 0) {
     int nodes = kLadderNodes, sp = 0;
     bool ret = false;
     fr[0].a = (uint16_t)a; fr[0].prey = kNoPoint; fr[0].kind = (uint8_t)kind; fr[0].phase = LP_ENTER;
+    if (prey_mask) {
+        const int nbr[4] = {a - B.size, a + B.size, a - 1, a + 1};
+        int np = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) if (prey_mask & (1 << j)) fr[0].preys[np++] = (uint16_t)nbr[j];
+        fr[0].nprey = (uint8_t)np; fr[0].iprey = 0;
+        fr[0].phase = LP_NEXT_PREY;
+        nodes--;
+    }
     sp = 1;
     while (sp > 0) {
         LadderFrame& f = fr[sp - 1];
@@ -211,13 +233,30 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
         } else if (phase == LP_NEXT_PREY) {
             if (f.iprey >= f.nprey) { done = true; value = false; }
             else {
+                const int pr = f.preys[f.iprey];
                 wl_play(B, fa);
                 f.last = kNoPoint;
+                // The prey group after the move and its liberties.  Below the root the parent frame holds the group as it was
+                // before this move (the board between a frame's move and its children's moves does not change): a hunter's move
+                // leaves it as it is, the prey's own move adds the stone -- if it touches the group; a reply may also capture
+                // hunter stones elsewhere -- and whatever it connects to: one or two dilations instead of a flood fill along the
+                // whole ladder.
+                const int prey_col = fkind == 0 ? B.player : -B.player;   // wl_play has passed the turn
+                const uint32_t own = prey_col > 0 ? B.blk : B.wht;
+                uint32_t g = sp >= 2 ? B.pgrp[sp - 2] : wb_point(pr, B.lane);
+                uint32_t d;
+                while (true) {
+                    d = wl_dilate(B, g);
+                    const uint32_t nn = g | (d & own);
+                    if (!__any_sync(kFullWarp, nn != g)) break;
+                    g = nn;
+                }
+                const uint32_t libset = d & ~B.blk & ~B.wht;
+                B.pgrp[sp - 1] = g;
+                B.plib[sp - 1] = libset;
                 bool go_on = true;
                 if (fkind == 1) {
-                    const int pr = f.preys[f.iprey];
-                    uint32_t g, l;
-                    const int libs = wl_group_libs(B, pr, wl_colour(B, pr), 2, &g, &l);
+                    const int libs = wb_count(libset);
                     if (libs >= 3) { wl_undo(B); done = true; value = true; go_on = false; }
                     else if (libs <= 1) { wl_undo(B); f.iprey++; go_on = false; }
                 }
@@ -228,12 +267,13 @@ __device__ __forceinline__ bool wl_query(WBoard& B, LadderFrame* fr, int kind, i
             const int after = f.last == kNoPoint ? -1 : (int)f.last;
             uint32_t replies;
             if (f.last == kNoPoint) {  // first child of this prey: work the reply set out once, keep it for the siblings
-                const int prey_col = wl_colour(B, pr);
-                uint32_t prey;
-                wl_group_libs(B, pr, prey_col, 0x7fff, &prey, &replies);
+                replies = B.plib[sp - 1];
                 if (fkind == 0) {
-                    // + the single liberty of every hunter group that touches the prey and is in atari
-                    uint32_t touching = wl_dilate(B, prey) & (prey_col > 0 ? B.wht : B.blk);
+                    // + the single liberty of every hunter group that touches the prey and is in atari.  A group in atari has no
+                    // stone with two empty neighbours: those are dropped before the per-group check
+                    const int prey_col = wl_colour(B, pr);
+                    const uint32_t empty = ~B.blk & ~B.wht & B.m.all;
+                    uint32_t touching = wl_dilate(B, B.pgrp[sp - 1]) & (prey_col > 0 ? B.wht : B.blk) & ~wl_two_neighbours_in(B, empty);
                     for (int s = wb_next(touching, -1, B.lane); s >= 0; s = wb_next(touching, -1, B.lane)) {
                         uint32_t h, hl;
                         const int nl = wl_group_libs(B, s, -prey_col, 1, &h, &hl);  // h is partial when given up early: it still holds s
