@@ -491,6 +491,7 @@ struct ConvLayer {
     int wgrad_splits;
     bool wgrad_chain;                           // can take part in a chained weight-gradient launch
     unsigned int wgrad_chain_count;             // chained launches since its counters were zeroed
+    unsigned int wgrad_done_target;             // value of its "done" counter once the latest chained launch has finished it
 };
 
 }  // namespace ag
@@ -695,14 +696,14 @@ static int net_build_wgrad_maps(ag_net* net, int n) {
         w.m_total = (int)rows; w.taps = c.taps; w.ldout = c.ldout; w.kin = c.kin; w.splits = c.wgrad_splits;
         w.kb_img = wgrad_kb_img(c.lin, c.tm_wg.krows); w.img_stride = c.lin.img_stride;
         const int wg_tiles = (c.taps * (c.ldout / 64) + 3) / 4;   // the chained kernel keeps whole-accumulator partials: 256 rows x kin per tile
-        c.wgrad_chain = !net->wgrad_chain_refused && wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && wg_tiles <= kWgradCounterStride &&
+        c.wgrad_chain = !net->wgrad_chain_refused && wgrad_chain_ok(w, c.tm_wg, c.kin + 16 <= 256) && wg_tiles < kWgradCounterStride &&
                         (size_t)c.wgrad_splits * wg_tiles * 256 * c.kin <= net->wgrad_scratch_floats;
     }
     // the arrival counters count in units of this batch's split factors: start over.  (Batch-size changes are rare; the device
     // is drained first so that no weight-gradient launch of the old batch size, on whatever stream, still uses them.)
     AG_CUDA(cudaDeviceSynchronize());
     AG_CUDA(cudaMemset(net->wgrad_counters, 0, sizeof(unsigned int) * net->n_conv * kWgradCounterStride));
-    for (auto& c : net->L) c.wgrad_chain_count = 0;
+    for (auto& c : net->L) { c.wgrad_chain_count = 0; c.wgrad_done_target = 0; }
     net->wgrad_n = n;
     return AG_OK;
 }
@@ -1112,6 +1113,7 @@ static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) 
             e[cnt].dw = c.gw; e[cnt].db = c.gb;
             e[cnt].counters = net->wgrad_counters + (size_t)l * kWgradCounterStride;
             e[cnt].target = ++c.wgrad_chain_count * (unsigned int)c.wgrad_splits;
+            e[cnt].done = e[cnt].counters + (kWgradCounterStride - 1);   // the layer's last counter slot (tiles < stride)
             cnt++;
             l--;
         }
@@ -1120,6 +1122,8 @@ static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) 
         w.m_total = n * first.lin.img_stride; w.taps = first.taps; memcpy(w.off, first.off_fwd, sizeof(int) * first.taps);
         w.ldout = first.ldout; w.kin = first.kin; w.splits = first.wgrad_splits;
         w.kb_img = wgrad_kb_img(first.lin, first.tm_wg.krows); w.img_stride = first.lin.img_stride;
+        const unsigned int ctas = (unsigned int)wgrad_chain_ctas(w);
+        for (int k = l + cnt; k > l; k--) net->L[k].wgrad_done_target = net->L[k].wgrad_chain_count * ctas;
         int rc = wgrad_chain_launch(w, e, cnt, st);
         if (rc == AG_ESTATE) {   // refused (grid not co-resident): these and all later layers use their own kernel + reduce
             net->wgrad_chain_refused = true;
@@ -1208,6 +1212,35 @@ int ag_net_sgd(ag_net* net, float lr, float momentum, float grad_scale, void* st
              net->sgd_tiles, flats, lr, momentum, grad_scale);
     AG_LAUNCH_CHECK("sgd_all_kernel");
     net->iterations++;
+    return AG_OK;
+}
+
+// Where a chained layer's gradient becomes final while the launch is still running: the device address of a counter and the
+// value it reaches when dw / db of `layer` from the latest ag_net_backward_range are complete.  AG_ESTATE when the layer's
+// weight gradient did not run chained (its gradient is final when the backward call's kernels are: wait for the stream).
+int ag_net_wgrad_done(ag_net* net, int layer, unsigned int** d_counter, unsigned int* target) {
+    if (layer < 0 || layer >= net->n_conv) { set_error("ag_net_wgrad_done: bad layer %d", layer); return AG_EINVAL; }
+    ConvLayer& c = net->L[layer];
+    if (!c.wgrad_chain || c.wgrad_chain_count == 0) { set_error("ag_net_wgrad_done: layer %d does not run chained", layer); return AG_ESTATE; }
+    *d_counter = net->wgrad_counters + (size_t)layer * kWgradCounterStride + (kWgradCounterStride - 1);
+    *target = c.wgrad_done_target;
+    return AG_OK;
+}
+
+// Makes `stream` wait until the 32-bit word at d_addr has reached `value` (cuStreamWaitValue32, >= in wrap-around
+// arithmetic): everything queued on the stream afterwards starts only then.
+int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int value) {
+    typedef CUresult (*wait_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+    static wait_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q);
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) { set_error("cuStreamWaitValue32 is not available"); return AG_ECUDA; }
+        fn = (wait_fn)p;
+    }
+    CUresult r = fn((CUstream)stream, (CUdeviceptr)(uintptr_t)d_addr, value, CU_STREAM_WAIT_VALUE_GEQ);
+    if (r != CUDA_SUCCESS) { set_error("cuStreamWaitValue32 failed (%d)", (int)r); return AG_ECUDA; }
     return AG_OK;
 }
 

@@ -360,6 +360,7 @@ struct WgradChainLayer {
     float* db;             // [ldout]
     unsigned int* counters;  // [tiles], running totals over launches
     unsigned int target;     // counter value that means "all splits of this launch have arrived"
+    unsigned int* done;      // running total of CTAs that have finished their share of this layer's dW / db (may be null)
 };
 struct WgradChainParams {
     WgradArgs a;           // shared geometry (scratch pointers unused)
@@ -585,6 +586,15 @@ wgrad_chain_kernel(const __grid_constant__ WgradChainParams P, const int kStages
                     L.db[c] = t;
                 }
             }
+            // ---- this CTA's part of the layer's gradient is final: count it.  A stream that waits for the count to reach
+            // (launches so far) x (CTAs per launch) may start exchanging this layer while the layers below are still running.
+            if (L.done) {
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (et == 0) {
+                    asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(L.done) : "memory");
+                }
+            }
         }
     }
     pdl_trigger();  // not earlier: every CTA of this grid must be resident before anything queued behind it may take SMs
@@ -737,6 +747,11 @@ bool wgrad_chain_ok(const WgradArgs& a_in, const WgradMaps& maps, bool with_bias
     return a.tiles * a.splits <= sm_count() && wgrad_stages(a.taps, a.kin, with_bias, maps.krows, maps.win_rows) >= 2;
 }
 
+int wgrad_chain_ctas(const WgradArgs& a_in) {
+    WgradArgs a = a_in;
+    return wgrad_tiling(a.taps, a.ldout, a.kin, &a.tpg, &a.groups) * (a.splits < 1 ? 1 : a.splits);
+}
+
 int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_layers, cudaStream_t stream) {
     if (n_layers < 1) return AG_OK;
     if (n_layers > kWgradChainMax) { set_error("wgrad chain: %d layers in one launch (max %d)", n_layers, kWgradChainMax); return AG_EINVAL; }
@@ -752,7 +767,7 @@ int wgrad_chain_launch(WgradArgs args, const WgradChainEntry* entries, int n_lay
         WgradChainLayer& L = P.layers[i];
         L.g = entries[i].maps->g; L.gw = entries[i].maps->gw; L.x = entries[i].maps->x;
         L.scratch = entries[i].scratch; L.bias_scratch = entries[i].bias_scratch;
-        L.dw = entries[i].dw; L.db = entries[i].db; L.counters = entries[i].counters; L.target = entries[i].target;
+        L.dw = entries[i].dw; L.db = entries[i].db; L.counters = entries[i].counters; L.target = entries[i].target; L.done = entries[i].done;
         if ((entries[i].bias_scratch != nullptr) != with_bias || entries[i].maps->win_rows != args.win_rows) {
             set_error("wgrad chain: layers of one launch must share their geometry");
             return AG_EINVAL;

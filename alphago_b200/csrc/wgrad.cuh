@@ -56,7 +56,11 @@ struct WgradChainEntry {
     float* db;
     unsigned int* counters;    // [tiles] arrival counters (running totals over launches)
     unsigned int target;       // their value once this launch's partials are all in: (launches so far, this one included) * splits
+    unsigned int* done;        // nullptr, or a running count of CTAs whose share of this layer's gradient is final: it reaches
+                               // (launches so far) * tiles * splits when dw / db of the layer are complete
 };
+// CTAs of one chained launch for this geometry (tiles * splits)
+int wgrad_chain_ctas(const WgradArgs& args);
 // can this problem run chained (taps not folded into N, all CTAs resident at once, ...)?
 bool wgrad_chain_ok(const WgradArgs& args, const WgradMaps& maps, bool with_bias);
 // weight (+bias) gradients of n_layers layers in one launch, split reduction included; args: m_total, taps, off, ldout, kin, splits

@@ -141,6 +141,13 @@ class ConvNet(object):
                 "wgrad": [l for l in rng if L.ag_net_layer_info(h, l, 7) == 1],
                 "refused": L.ag_net_layer_info(h, 0, 8), "splits": [L.ag_net_layer_info(h, l, 9) for l in rng]}
 
+    def wgrad_done(self, layer):
+        """(device address of a counter, value it reaches when this layer's gradient of the latest backward_range is
+        final) for a layer whose weight gradient runs inside the chained launch, else None"""
+        ptr, target = C.c_void_p(), C.c_uint()
+        rc = _lib.lib().ag_net_wgrad_done(self._h, int(layer), C.byref(ptr), C.byref(target))
+        return (ptr.value, target.value) if rc == 0 else None
+
     def run_layer(self, layer, mode, n):
         _lib.check(_lib.lib().ag_net_run_layer(self._h, layer, mode, n, _lib.current_stream()), "ag_net_run_layer")
 

@@ -47,7 +47,7 @@ def allreduce_in_buckets(dist, flat, plan, group=None, after_bucket=None):
 
 
 class SLTrainer(object):
-    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=2, process_group=None):
+    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=6, process_group=None):
         import torch
         self.torch = torch
         self.net, self.lr0, self.decay, self.momentum = net, float(lr), float(decay), float(momentum)
@@ -66,10 +66,15 @@ class SLTrainer(object):
             import os
             import torch as _t
             sms = _t.cuda.get_device_properties(_t.cuda.current_device()).multi_processor_count
-            net.set_sm_budget(max(1, sms - int(os.environ.get("AG_DP_RESERVE_SMS", "8"))))
+            net.set_sm_budget(max(1, sms - int(os.environ.get("AG_DP_RESERVE_SMS", "4"))))
         # gradient buckets: contiguous runs of layers, last layers first (they finish first in backward)
         import os as _os
         self.plan = plan_buckets(net.n_conv, net.grad_offsets, int(_os.environ.get("AG_DP_BUCKETS", buckets)))
+        # 1: each bucket's all-reduce is gated by the weight-gradient kernel's own per-layer "gradient final" counters
+        # (cuStreamWaitValue32 on a side stream), so the exchange starts inside the one chained launch; 0: buckets are cut
+        # at launch boundaries and gated by stream order
+        self.flag_gated = _os.environ.get("AG_DP_FLAGS", "1") != "0"
+        self._side = None
         self._out = None
         self._labels = None
 
@@ -119,7 +124,7 @@ class SLTrainer(object):
         lr = self.current_lr()
         if self.dist is None:
             net.train_step(planes, labels, lr, self.momentum, self.loss_acc)
-        else:
+        elif not self.flag_gated:
             net.forward_loss(planes, labels, self.loss_acc)
 
             def backward_bucket(i, lo, hi):
@@ -127,6 +132,31 @@ class SLTrainer(object):
             # each bucket is reduced as soon as its layers' gradients are enqueued: NCCL's stream picks up after the
             # kernels issued so far, so the exchange overlaps the backward of the layers below
             works = allreduce_in_buckets(self.dist, net.grad_tensor(), self.plan, self.group, backward_bucket)
+            for w in works:
+                w.wait()
+            net.sgd(lr, self.momentum, 1.0 / self.world)
+        else:
+            # The whole backward pass is queued at once (one data-gradient launch, one weight-gradient launch for the equal
+            # layers, the first layer's own kernels).  The weight-gradient kernel counts, per layer, the CTAs that have
+            # finished their share: a side stream waits for the count of a bucket's LOWEST layer (layers finish top down)
+            # and NCCL's stream waits for the side stream, so bucket k is on the wire while the same launch is still
+            # computing the layers below it.
+            torch = self.torch
+            net.forward_loss(planes, labels, self.loss_acc)
+            net.backward_range(net.n_conv - 1, 0, n)
+            flat = net.grad_tensor()
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            works = []
+            for lo, hi, start, end in self.plan:
+                gate = net.wgrad_done(lo)
+                if gate is None:   # not a chained layer (the first layer, a refused launch): final when the stream gets there
+                    works.append(self.dist.all_reduce(flat[start:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
+                    continue
+                with torch.cuda.stream(self._side):
+                    _lib.check(_lib.lib().ag_stream_wait_value(C.c_void_p(self._side.cuda_stream), C.c_void_p(gate[0]), gate[1]),
+                               "ag_stream_wait_value")
+                    works.append(self.dist.all_reduce(flat[start:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
             for w in works:
                 w.wait()
             net.sgd(lr, self.momentum, 1.0 / self.world)

@@ -143,6 +143,14 @@ int ag_net_backward_range(ag_net* net, int hi, int lo, int n, void* stream);
 /* SMs the weight-gradient launches may fill (0 = all).  No counterpart in the reference (Keras/Theano schedule their own
  * kernels); data-parallel training leaves a few SMs to the gradient all-reduce that runs beside the backward pass. */
 int ag_net_set_sm_budget(ag_net* net, int sms);
+/* Overlap of the gradient exchange with the backward pass (no counterpart in the reference, which trains on one device).
+ * After ag_net_backward_range: *d_counter is a device word that reaches *target (wrap-around >=) once the weight and bias
+ * gradients of `layer` are final -- inside the chained launch, while the layers below are still being computed.
+ * AG_ESTATE if the layer does not run chained (then its gradient is final when the stream reaches the end of the call).
+ * ag_stream_wait_value() makes a stream wait for such a word (cuStreamWaitValue32): what SLTrainer puts in front of each
+ * bucket's all-reduce. */
+int ag_net_wgrad_done(ag_net* net, int layer, unsigned int** d_counter, unsigned int* target);
+int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int value);
 /* loss differentiated by ag_net_forward_loss: 0 = categorical cross-entropy (compile(loss='categorical_crossentropy'),
  * supervised_policy_trainer.py:200), 1 = Keras binary_crossentropy on the softmax outputs
  * (compile(loss='binary_crossentropy'), reinforcement_policy_trainer.py:109) */

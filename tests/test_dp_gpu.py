@@ -10,10 +10,13 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _setup_net(max_batch):
+SHAPES = {"small": ([64, 64, 64], [5, 3, 3]), "bench": ([192] * 12, [5] + [3] * 11)}   # "bench": BASELINE configs[2]/[3]
+
+
+def _setup_net(max_batch, shape="small"):
     from alphago_b200 import nn
     from oracle import nn_oracle as no
-    filters, widths = [64, 64, 64], [5, 3, 3]
+    filters, widths = SHAPES[shape]
     params = no.make_params(48, filters, widths, seed=21)
     params["head_w"] = (params["head_w"] * 20).astype(np.float32)
     net = nn.ConvNet(19, 48, filters, widths, max_batch=max_batch)
@@ -28,7 +31,7 @@ def _data(n):
     return (rng.rand(n, 48, 19, 19) < 0.3).astype(np.uint8), rng.randint(0, 361, n).astype(np.int32)
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, shape):
     import torch
     import torch.distributed as dist
     from alphago_b200.training import SLTrainer
@@ -39,21 +42,25 @@ def _worker(rank, world, port, out):
     n = 32
     x, y = _data(n)
     share = n // world
-    net, _ = _setup_net(share)
+    net, _ = _setup_net(share, shape)
     tr = SLTrainer(net, lr=0.05, decay=0.0, momentum=0.9)
-    assert tr.world == world
+    assert tr.world == world and tr.flag_gated
     sl = slice(rank * share, (rank + 1) * share)
     for _ in range(2):
         tr.step(torch.from_numpy(x[sl]).cuda(), torch.from_numpy(y[sl]).cuda())
     loss, acc = tr.pop_metrics(2 * share)
     torch.cuda.synchronize()
     if rank == 0:
-        np.savez(out, loss=loss, **{"w%d" % l: net.get_conv(l)[0] for l in range(3)}, hw=net.get_head(0)[0])
+        # the exchange of the chained layers was gated by their "gradient final" counters, not by launch boundaries
+        gated = [net.wgrad_done(l) is not None for l in range(net.n_conv)]
+        np.savez(out, loss=loss, gated=np.asarray(gated), **{"w%d" % l: net.get_conv(l)[0] for l in range(net.n_conv)},
+                 hw=net.get_head(0)[0])
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_two_rank_step_equals_single_rank_step(tmp_path):
+@pytest.mark.parametrize("shape", ["small", "bench"])
+def test_two_rank_step_equals_single_rank_step(tmp_path, shape):
     import torch
     import torch.multiprocessing as mp
     if torch.cuda.device_count() < 2:
@@ -61,20 +68,24 @@ def test_two_rank_step_equals_single_rank_step(tmp_path):
     from alphago_b200.training import SLTrainer
     out = os.path.join(str(tmp_path), "dp.npz")
     port = 29700 + os.getpid() % 200
-    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, port, out, shape), nprocs=2, join=True)
     dp = np.load(out)
     n = 32
     x, y = _data(n)
-    net, params = _setup_net(n)
+    net, params = _setup_net(n, shape)
     tr = SLTrainer(net, lr=0.05, decay=0.0, momentum=0.9)
     for _ in range(2):
         tr.step(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
     loss, _ = tr.pop_metrics(2 * n)
     assert abs(loss - float(dp["loss"])) < 2e-3 * max(1.0, abs(loss))
-    for l in range(3):
+    if shape == "bench":   # every hidden layer ran chained and gave a counter to wait for
+        assert dp["gated"][1:].all() and not dp["gated"][0], dp["gated"]
+    for l in range(net.n_conv):
         w = net.get_conv(l)[0]
         w0 = params["convs"][l][0]
         err = np.linalg.norm((w - w0) - (dp["w%d" % l] - w0)) / np.linalg.norm(w - w0)
-        assert err < 2e-2, (l, err)
+        # the 12-layer net's gradient is ill-conditioned on a random init (tests/test_bench_shape_gpu.py): the second step
+        # starts from weights that differ in the last bits and its gradient moves by a few per cent
+        assert err < (5e-2 if shape == "bench" else 2e-2), (l, err)
     hw = net.get_head(0)[0]
     assert np.linalg.norm(hw - dp["hw"]) / np.linalg.norm(hw - params["head_w"]) < 2e-2
