@@ -238,10 +238,11 @@ class Dataset(object):
             p += ksz + 8
 
     def _index(self):
-        if self._chunks is None:
-            self._chunks = {}
+        if self._chunks is None:   # built aside and published whole: take_rows decodes chunks on several threads
+            chunks = {}
             if self.btree != UNDEF:
-                self._walk(self.btree, self._chunks)
+                self._walk(self.btree, chunks)
+            self._chunks = chunks
         return self._chunks
 
     def _chunk(self, offs):
