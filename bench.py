@@ -30,6 +30,7 @@ sys.path.insert(0, ROOT)
 FEATS46 = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
            "liberties_after", "sensibleness", "zeros"]
 ENC_BYTES_PER_POSITION = 48 * 361 + 361 + 361 + 4  # planes out + board + age + player/ko
+ENC_WARP_INST_PER_POSITION_48 = (434935893 + 935732771) / 16384.0   # profiles/r2_encode_ncu_summary.json
 
 
 def encode_config(n, feats, planes):
@@ -177,10 +178,25 @@ class EncodeWorkload(object):
 
     def roofline(self, ms_per_step, pk):
         ach = self.n * ENC_BYTES_PER_POSITION / (ms_per_step * 1e-3) / 1e9
-        return {"bound": "hbm", "achieved": round(ach, 2), "peak": pk["hbm"], "unit": "GB/s",
-                "frac": round(ach / pk["hbm"], 5), "traffic": None, "kernel": "ag::enc::encode_kernel",
-                "peak_source": pk["source"] + " (copy bandwidth, kernel timed inside a long step)",
-                "algorithmic_bytes_per_launch": self.n * ENC_BYTES_PER_POSITION}
+        out = {"bound": "hbm", "achieved": round(ach, 2), "peak": pk["hbm"], "unit": "GB/s",
+               "frac": round(ach / pk["hbm"], 5), "traffic": None, "kernel": "ag::enc::encode_kernel + ag::enc::ladder_resolve_kernel",
+               "peak_source": pk["source"] + " (copy bandwidth, kernel timed inside a long step)",
+               "algorithmic_bytes_per_launch": self.n * ENC_BYTES_PER_POSITION}
+        tp = os.path.join(ROOT, "profiles", "r2_traffic.json")
+        if os.path.exists(tp) and self.n == 16384 and self.pp.output_dim == 48:
+            t = json.load(open(tp))
+            out["traffic"] = t["encode_kernel"]["dram_bytes_per_launch"] + t["ladder_resolve_kernel"]["dram_bytes_per_launch"]
+        # The encoder is integer work: what bounds it in practice is instruction issue, not bandwidth.  Warp instructions per
+        # position from the committed ncu capture (profiles/r2_encode_ncu_summary.json: smsp__inst_executed.sum / 16384
+        # positions, 48 planes) against 148 SMs x 4 schedulers x 1 instruction per cycle at the SM clock seen under this load.
+        if self.pp.output_dim == 48:
+            inst = ENC_WARP_INST_PER_POSITION_48
+            clk = 1.9e9
+            floor_ms = self.n * inst / (148 * 4 * clk) * 1e3
+            out["issue_roofline"] = {"warp_instructions_per_position": inst, "sm_clock_hz": clk, "floor_ms": round(floor_ms, 4),
+                                     "frac": round(floor_ms / ms_per_step, 4),
+                                     "note": "encode_kernel 26.5 k + ladder_resolve_kernel 57.1 k warp instructions per position"}
+        return out
 
     def config(self):
         return encode_config(self.n, self.feats, self.pp.output_dim)
