@@ -164,7 +164,7 @@ __device__ __forceinline__ void lb_nbrs(const LadderBoard& B, int a, int out[4])
     out[3] = y < B.size - 1 ? a + 1 : -1;
 }
 
-__device__ bool lb_legal(const LadderBoard& B, int a) {  // go.py:181-216 for the side to move
+__device__ inline bool lb_legal(const LadderBoard& B, int a) {  // go.py:181-216 for the side to move
     if (lb_colour(B, a) != 0 || a == B.ko) return false;
     const Bits nb = lb_dilate(B, lb_point(a));
     if (bits_any(bits_andnot(bits_andnot(nb, B.blk), B.wht))) return true;  // an empty neighbour
@@ -178,7 +178,7 @@ __device__ bool lb_legal(const LadderBoard& B, int a) {  // go.py:181-216 for th
 }
 
 // go.py:295-338 without bookkeeping; a must be legal.  Pushes an undo record.
-__device__ void lb_play(LadderBoard& B, int a) {
+__device__ inline void lb_play(LadderBoard& B, int a) {
     const int color = B.player;
     const int old_ko = B.ko;
     Bits captured = bits_zero();
@@ -206,7 +206,7 @@ __device__ void lb_play(LadderBoard& B, int a) {
     B.undo_top += LW + 2;
     B.player = -color;
 }
-__device__ void lb_undo(LadderBoard& B) {
+__device__ inline void lb_undo(LadderBoard& B) {
     B.undo_top -= LW + 2;
     const uint32_t* u = B.undo + B.undo_top;
     B.player = -B.player;  // the side that played
@@ -230,7 +230,7 @@ struct LadderFrame {
 enum { LP_ENTER, LP_NEXT_PREY, LP_NEXT_CHILD, LP_WAIT_CHILD };
 
 // is (kind ? ladder_escape : ladder_capture)(a) true on board B for the side to move?  B is left unchanged.
-__device__ bool ladder_query(LadderBoard& B, LadderFrame* fr, int kind, int a) {
+__device__ inline bool ladder_query(LadderBoard& B, LadderFrame* fr, int kind, int a) {
     int nodes = kLadderNodes, sp = 0;
     bool ret = false;
     fr[0].a = (uint16_t)a; fr[0].prey = kNoPoint; fr[0].kind = (uint8_t)kind; fr[0].phase = LP_ENTER;

@@ -213,8 +213,11 @@ class SequentialModel(object):
         from .training import SLTrainer
         if self.optimizer is None:
             self.compile()
-        X = np.ascontiguousarray(X, dtype=np.uint8)
-        labels = np.ascontiguousarray(np.asarray(Y).reshape(len(X), -1).argmax(1), dtype=np.int32)
+        on_device = torch.is_tensor(X) and X.is_cuda   # selfplay.make_training_pairs_device keeps the planes on the device
+        X = X.contiguous() if on_device else np.ascontiguousarray(X, dtype=np.uint8)
+        Y = np.asarray(Y)
+        # one-hot rows (the reference's form) or the move indices themselves
+        labels = np.ascontiguousarray(Y if Y.ndim == 1 else Y.reshape(len(X), -1).argmax(1), dtype=np.int32)
         self.ensure_batch(min(batch_size, len(X)))
         if self._trainer is None:
             self._trainer = SLTrainer(self.net, lr=self.optimizer.lr.get_value(), decay=self.optimizer.decay, momentum=self.optimizer.momentum)
@@ -222,7 +225,8 @@ class SequentialModel(object):
         for _ in range(nb_epoch):
             for s in range(0, len(X), batch_size):
                 tr.lr0 = self.optimizer.lr.get_value()
-                tr.step(torch.from_numpy(X[s:s + batch_size]).cuda(), torch.from_numpy(labels[s:s + batch_size]).cuda())
+                xb = X[s:s + batch_size] if on_device else torch.from_numpy(X[s:s + batch_size]).cuda()
+                tr.step(xb, torch.from_numpy(labels[s:s + batch_size]).cuda())
         loss, acc = tr.pop_metrics(len(X) * nb_epoch)
         return {"loss": loss, "acc": acc}
 

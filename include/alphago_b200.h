@@ -192,6 +192,21 @@ int ag_wgrad(const void* d_g, const void* d_x, long long rows, int ldout, int ki
 size_t ag_wgrad_static_max_bytes(void);
 int ag_wgrad_static(const void* d_g, const void* d_x, long long rows, int ldout, int kin, int width, int row_stride,
                     float* d_dw, void* stream);
+/* Device-resident self-play (the mini-batch of games of reinforcement_policy_trainer.py:16-76 and the move choice of
+ * ProbabilisticPolicyPlayer, ai.py:38-68, without a host round trip per ply).  `games` positions of one board size live
+ * in the encoder's input arrays (d_board / d_age / d_player / d_ko: feed them to ag_encode as they are) plus
+ *   d_flags  uint8 [games]     bit 0 = is_end_of_game (go.py:345-348), bit 1 = the previous move was a pass
+ *   d_passes int32 [games][2]  passes_black, passes_white (go.py:341-344)
+ * One call plays one ply in every game that is not over: it samples a move with probability proportional to
+ * d_probs[g][p] ^ beta over the points where d_mask[g * mask_stride + p] != 0 (the encoder's `sensibleness` plane of that
+ * position: legal and not the mover's own eye, ai.py:15,38), using the uniform number d_uniform[g] in [0, 1) -- no such point
+ * means pass (ai.py:49) -- and applies it with the reference's rules (go.py:295-349: captures, ko, pass bookkeeping).
+ * d_moves int16 [games]: the move played (x*size+y), -1 for a pass, -2 if the game was already over. */
+int ag_selfplay_step(int8_t* d_board, uint8_t* d_age, int8_t* d_player, int16_t* d_ko, uint8_t* d_flags, int32_t* d_passes,
+                     const float* d_probs, const uint8_t* d_mask, long long mask_stride, const float* d_uniform, float beta,
+                     int games, int size, int16_t* d_moves, void* stream);
+/* GameState.get_winner (go.py:269-293) for every game: +1 black, -1 white, 0 tie */
+int ag_selfplay_winner(const int8_t* d_board, const int32_t* d_passes, int games, int size, float komi, int8_t* d_winner, void* stream);
 /* LZF byte streams on the host (no GPU work): the chunk filter the reference's converter asks h5py for
  * (compression="lzf", game_converter.py:73-74,81-82).  decompress returns the number of bytes written, or -1 on a
  * corrupt stream / too small an output buffer; compress returns the stream's length, or 0 when it does not fit

@@ -39,4 +39,26 @@ for games in (16, 128):
     t4 = time.time()
     rows.append({"games": games, "plies_per_game": plies, "selfplay_plies_per_s": round(games * plies / (t1 - t0), 1),
                  "selfplay_s": round(t1 - t0, 3), "fast_selfplay_plies_per_s": round(games * plies / (t4 - t3), 1), "update_s": round(t2 - t1, 3), "training_pairs": int(sum(len(a) for a in X))})
+# device-resident games (alphago_b200/selfplay.py): a ply is encode -> forward -> ag_selfplay_step, no host round trip
+from alphago_b200.selfplay import make_training_pairs_device
+dev_rows = []
+for games in (128, 1024, 4096):
+    pol = CNNPolicy(FEATS, layers=12, filters_per_layer=128, seed=1, max_batch=games)
+    pl = ProbabilisticPolicyPlayer(pol)
+    pol.model.compile(loss="binary_crossentropy", optimizer=SGD(lr=0.001))
+    make_training_pairs_device(pl, pl, FEATS, games, max_plies=8)
+    plies = 80
+    torch.cuda.synchronize()
+    t0 = time.time()
+    X, y, w = make_training_pairs_device(pl, pl, FEATS, games, max_plies=plies)
+    torch.cuda.synchronize()
+    t1 = time.time()
+    if games <= 128:
+        train_batch(pl, X, y, w, 0.001)
+    torch.cuda.synchronize()
+    t2 = time.time()
+    dev_rows.append({"games": games, "plies_per_game": plies, "device_selfplay_plies_per_s": round(games * plies / (t1 - t0), 1),
+                     "selfplay_s": round(t1 - t0, 3), "update_s": round(t2 - t1, 3), "training_pairs": int(sum(len(a) for a in y))})
+    del pol, pl
+print(json.dumps({"what": "device-resident self-play, 19x19, 12 x 128-filter policy vs itself (encode + forward + ag_selfplay_step per ply)", "rows": dev_rows}))
 print(json.dumps({"what": "make_training_pairs + train_batch, 19x19, 12 x 128-filter policy vs itself", "rows": rows}))
