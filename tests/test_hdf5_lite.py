@@ -345,3 +345,68 @@ def test_take_rows_reads_only_what_a_shuffled_minibatch_needs(tmp_path):
     assert f["states"].take_rows([]).shape == (0, 5, 7, 7)
     with pytest.raises(IndexError):
         f["states"].take_rows([300])
+
+
+def _structure(path):
+    """what libhdf5 reads before it touches any data: superblock fields, and per object the header messages that define
+    it -- datatype, dataspace, layout, filter pipeline, fill value -- byte for byte (addresses and times left out)"""
+    f = h5.File(path, "r")
+    b = f.b
+    sb = {"version": b[8], "free_space_version": b[9], "root_group_version": b[10], "shared_header_version": b[12],
+          "size_of_offsets": b[13], "size_of_lengths": b[14], "group_leaf_k": int.from_bytes(b[16:18], "little"),
+          "group_internal_k": int.from_bytes(b[18:20], "little")}
+    keep = {0x0001: "dataspace", 0x0003: "datatype", 0x0005: "fill_value", 0x000B: "filter_pipeline"}
+
+    def obj(o):
+        out = {"header_version": b[o.addr], "messages": sorted(t for t, _, _ in o.msgs if t not in (0x0000, 0x0010, 0x0012))}
+        for t, d, s in o.msgs:
+            if t in keep:
+                out[keep[t]] = bytes(b[d:d + s]).rstrip(b"\0")
+            if t == 0x0008:   # layout: version, class, then (chunked) rank and dims -- not the B-tree address
+                ver, cls = b[d], b[d + 1]
+                out["layout"] = (ver, cls) if cls != 2 else (ver, cls, b[d + 2], bytes(b[d + 11:d + 11 + 4 * b[d + 2]]))
+        return out
+    tree = {"/": obj(f.obj)}
+    for name in f.keys():
+        node = f[name]
+        tree[name] = obj(node.obj)
+        if isinstance(node, h5.Group):
+            for sub in node.keys():
+                tree[name + "/" + sub] = obj(node[sub].obj)
+    return sb, tree
+
+
+def test_writer_reproduces_the_structure_of_the_references_h5py_file(tmp_path):
+    """The reference's own dataset file (tests/test_data/hdf5/alphago-vs-lee-sedol-features.hdf5, written by h5py 2.6 /
+    libhdf5 through its converter) re-written by hdf5_lite with the converter's calls (game_converter.py:71-88,122-125):
+    superblock fields and, object by object, the datatype / dataspace / layout / filter-pipeline / fill-value messages must
+    come out byte for byte as libhdf5 wrote them, the same message types must be present, and the data must read back
+    equal.  No libhdf5 exists in this image, so this is the closest stand-in for opening the file with h5py.  Needs the
+    reference tree (build container only)."""
+    from oracle import ref_shim
+    src = os.path.join(ref_shim.REFERENCE_ROOT, "tests", "test_data", "hdf5", "alphago-vs-lee-sedol-features.hdf5")
+    if not os.path.exists(src):
+        pytest.skip("reference tree not present")
+    ref = h5.File(src, "r")
+    states, actions = ref["states"][:], ref["actions"][:]
+    path = os.path.join(str(tmp_path), "rewritten.hdf5")
+    with h5.File(path, "w") as f:   # the converter's calls
+        s = f.require_dataset("states", dtype=np.uint8, shape=(1, 12, 19, 19), maxshape=(None, 12, 19, 19), exact=False,
+                              chunks=(64, 12, 19, 19), compression="lzf")
+        a = f.require_dataset("actions", dtype=np.uint8, shape=(1, 2), maxshape=(None, 2), exact=False, chunks=(1024, 2),
+                              compression="lzf")
+        offs = f.require_group("file_offsets")
+        s.resize((len(states), 12, 19, 19)); a.resize((len(actions), 2))
+        for i in range(len(states)):
+            s[i] = states[i]; a[i] = actions[i]
+        for name in ref["file_offsets"].keys():
+            offs[name] = [int(v) for v in ref["file_offsets"][name][:]]
+    got = h5.File(path, "r")
+    assert np.array_equal(got["states"][:], states) and np.array_equal(got["actions"][:], actions)
+    sb_ref, tree_ref = _structure(src)
+    sb_got, tree_got = _structure(path)
+    assert sb_got == sb_ref
+    assert sorted(tree_got) == sorted(tree_ref)
+    for name in sorted(tree_ref):
+        for key in sorted(tree_ref[name]):
+            assert tree_got[name].get(key) == tree_ref[name][key], (name, key, tree_got[name].get(key), tree_ref[name][key])
