@@ -140,13 +140,14 @@ def make_training_pairs_device(player, opp, features, mini_batch_size, reference
     # every recorded position of every game through ONE encoder launch, then cut per game
     board = torch.stack(rec["board"]).reshape(T * G, n); age = torch.stack(rec["age"]).reshape(T * G, n)
     pl = torch.stack(rec["player"]).reshape(T * G); ko = torch.stack(rec["ko"]).reshape(T * G)
-    sel = torch.from_numpy(np.flatnonzero(keep.reshape(-1))).cuda()
+    # kept (position, game) pairs ordered by game, then by ply: one gather, one encoder launch, per-game views of its output
+    flat_keep = np.flatnonzero(keep.reshape(-1))                      # index = ply * G + game
+    order = np.argsort(flat_keep % G, kind="stable")
+    sel = torch.from_numpy(flat_keep[order]).cuda()
     planes = pre.encode_packed(board[sel].contiguous(), age[sel].contiguous(), pl[sel].contiguous(), ko[sel].contiguous(), bsize)
-    game_of = np.tile(np.arange(G), T)[keep.reshape(-1)]
-    X_list, y_list = [], []
-    for g in range(G):
-        idx = np.flatnonzero(game_of == g)
-        X_list.append(planes[torch.from_numpy(idx).cuda()] if len(idx) else planes[:0])
-        y_list.append(moves[:, g][keep[:, g]].astype(np.int32))
+    counts = keep.sum(0)
+    starts = np.concatenate([[0], np.cumsum(counts)])
+    X_list = [planes[int(starts[g]):int(starts[g + 1])] for g in range(G)]
+    y_list = [moves[:, g][keep[:, g]].astype(np.int32) for g in range(G)]
     make_training_pairs_device.games = games
     return X_list, y_list, winners

@@ -104,7 +104,8 @@ def test_run_training_streams_a_dataset_larger_than_the_device_budget(tmp_path, 
         f.create_dataset("states", data=states, chunks=(64,) + states.shape[1:], compression="lzf")
         f.create_dataset("actions", data=actions, chunks=(1024, 2), compression="lzf")
     model = os.path.join(d, "model.json")
-    CNNPolicy(feats, layers=3, filters_per_layer=32, seed=5).save_model(model)
+    # with its weights: a model file without them is initialised afresh by every load_model (policy.py:158-169)
+    CNNPolicy(feats, layers=3, filters_per_layer=32, seed=5).save_model(model, os.path.join(d, "start.hdf5"))
     common = ["--epochs", "2", "--minibatch", "32", "--epoch-length", "320", "--learning-rate", "0.05", "--seed", "4"]
     meta_a = run_training([model, data, os.path.join(d, "resident")] + common)
     meta_b = run_training([model, data, os.path.join(d, "streamed")] + common + ["--device-dataset-mb", "1", "--io-threads", "3"])
