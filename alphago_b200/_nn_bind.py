@@ -33,6 +33,11 @@ def bind(L):
     L.ag_wgrad.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, C.c_size_t, vp, vp]
     L.ag_wgrad_static_max_bytes.restype = C.c_size_t
     L.ag_wgrad_static.argtypes = [vp, vp, C.c_longlong, i, i, i, i, vp, vp]
+    L.ag_xchg_create.restype = vp
+    L.ag_xchg_create.argtypes = [i, i, vp, C.c_longlong, i, vp]
+    L.ag_xchg_connect.argtypes = [vp, vp]
+    L.ag_xchg_allreduce.argtypes = [vp, C.c_longlong, C.c_longlong, vp]
+    L.ag_xchg_destroy.argtypes = [vp]; L.ag_xchg_destroy.restype = None
     L.ag_selfplay_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, vp, C.c_float, i, i, vp, vp]
     L.ag_selfplay_winner.argtypes = [vp, vp, i, i, C.c_float, vp, vp]
     L.ag_augment.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp]

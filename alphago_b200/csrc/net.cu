@@ -778,6 +778,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
     net->grad_offsets.push_back((long long)gcount);  // head slice
     const int ldh = net->L[n_conv - 1].ldout, pts = board * board;
     gcount += 256 + 1 + 368;
+    gcount = (gcount + 3) & ~(size_t)3;   // whole 16-byte groups (the head's 625 values + 3 unused zeros): the exchange moves float4
     net->grad_offsets.push_back((long long)gcount);
     net->grad_count = gcount;
     rc = dev_alloc(&net->grads, gcount);

@@ -1,0 +1,216 @@
+// Gradient exchange over NVLink peer memory: a two-shot sum all-reduce written for the data-parallel SL step
+// ("one exchange step"; the reference trains on one device and has no counterpart).
+//
+// Every rank of the node maps every other rank's gradient buffer (CUDA IPC).  One kernel per bucket, a few CTAs:
+//   0. tell every peer "my part of this bucket is final" and wait until all of them have said so
+//   1. reduce-scatter: this rank owns slice r of the bucket and sums it over all ranks' buffers with plain 16-byte peer
+//      loads, always in rank order 0..world-1, into its own buffer
+//   2. tell every peer "my slice is reduced", wait for theirs, and copy the other slices from their owners
+//   3. tell every peer "I have stopped reading", wait for theirs: nobody's buffer is written again (the next backward pass)
+//      while a peer may still read it
+// Flags are 32-bit sequence numbers in each rank's own signal block, written by the peers with system-scope release
+// stores and polled locally with acquire loads; they only ever grow, so a rank that runs ahead cannot confuse a slower one.
+// Because the owner alone reduces a slice and everybody copies its result, all ranks end with bit-identical sums
+// (a ring all-reduce gives each rank its own summation order).  Measured against NCCL on this box (8 x B200 without NVLS:
+// ring, LL protocol, 118 us for the 15.5 MB of one step): see DESIGN.md section 5.
+//
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+// the GPU; this kernel reads peers with ordinary ld.global only.
+#include <cuda.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace ag {
+
+constexpr int kXchgMaxWorld = 16;
+constexpr int kXchgThreads = 512;
+
+struct XchgPeers {
+    float* buf[kXchgMaxWorld];            // every rank's gradient buffer (own one included), same layout
+    unsigned int* sig[kXchgMaxWorld];     // every rank's signal block: [3][kXchgMaxWorld] words + CTA counters
+};
+// signal block layout (words): ready[w] at 0, reduced[w] at 16, finished[w] at 32, CTA arrival counters at 48, 49
+constexpr int kSigReady = 0, kSigReduced = 16, kSigFinished = 32, kSigCtas1 = 48, kSigCtas2 = 49, kSigWords = 64;
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// wait until all `world` words of my own block starting at `base` have reached seq (wrap-around compare); one lane per word
+__device__ __forceinline__ void wait_all(const unsigned int* mine, int base, int world, unsigned int seq) {
+    if (threadIdx.x < (unsigned)world) {
+        long long t0 = 0;
+        while ((int)(ld_acquire_sys(mine + base + threadIdx.x) - seq) < 0) {
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 20000000000LL) {   // ~10 s: a peer died; do not hang the device for ever
+                printf("alphago_b200: gradient exchange timed out waiting for rank %d (flag %d, seq %u)\n", (int)threadIdx.x, base, seq);
+                __trap();
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kXchgThreads)
+xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size_t count, unsigned int seq) {
+    unsigned int* mine = P.sig[rank];
+    // ---- 0. my bucket is final (stream order / the caller's gate says so): tell everybody, wait for everybody
+    if (blockIdx.x == 0 && threadIdx.x < (unsigned)world) {
+        __threadfence_system();
+        st_release_sys(P.sig[threadIdx.x] + kSigReady + rank, seq);
+    }
+    wait_all(mine, kSigReady, world, seq);
+
+    // ---- 1. reduce my slice (count is a multiple of 4 floats, slices are too)
+    const size_t n4 = count / 4;
+    const size_t per = (n4 + world - 1) / world;
+    const size_t lo = per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = lo + tid; i < hi; i += nthr) {
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+        for (int r = 0; r < world; r++) {
+            const float4 v = __ldcv(reinterpret_cast<const float4*>(P.buf[r] + start) + i);
+            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+        }
+        reinterpret_cast<float4*>(P.buf[rank] + start)[i] = a;
+    }
+    // all my CTAs done -> the last one tells the peers
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int arrived = atomicAdd(mine + kSigCtas1, 1u) + 1u;
+        if (arrived == gridDim.x * seq) {
+            for (int r = 0; r < world; r++) st_release_sys(P.sig[r] + kSigReduced + rank, seq);
+        }
+    }
+    // ---- 2. fetch the other slices from their owners
+    wait_all(mine, kSigReduced, world, seq);
+    for (int d = 1; d < world; d++) {
+        const int r = (rank + d) % world;   // start with different owners on different ranks
+        const size_t rlo = per * r < n4 ? per * r : n4, rhi = rlo + per < n4 ? rlo + per : n4;
+        const float4* src = reinterpret_cast<const float4*>(P.buf[r] + start);
+        float4* dst = reinterpret_cast<float4*>(P.buf[rank] + start);
+        for (size_t i = rlo + tid; i < rhi; i += nthr) dst[i] = __ldcv(src + i);
+    }
+    // ---- 3. I have stopped reading: tell everybody; leave only when everybody has (their buffers are about to be reused, mine too)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int arrived = atomicAdd(mine + kSigCtas2, 1u) + 1u;
+        if (arrived == gridDim.x * seq) {
+            for (int r = 0; r < world; r++) st_release_sys(P.sig[r] + kSigFinished + rank, seq);
+        }
+    }
+    wait_all(mine, kSigFinished, world, seq);
+}
+
+}  // namespace ag
+
+struct ag_xchg {
+    int rank, world, ctas;
+    float* local;
+    size_t count;
+    unsigned int* sig;           // my signal block (device)
+    ag::XchgPeers peers;
+    void* opened[2 * ag::kXchgMaxWorld];
+    int n_opened;
+    unsigned int seq;
+    long long buf_offset;        // of `local` inside its allocation (IPC handles name allocations)
+};
+
+extern "C" {
+
+// Creates this rank's end of the exchange over d_buf[count] (the buffer ag_net_grads() returns).  h_handle receives 144 bytes
+// to be all-gathered by the caller: the IPC handles of the buffer's allocation and of the signal block, and the buffer's
+// offset inside its allocation.
+ag_xchg* ag_xchg_create(int rank, int world, float* d_buf, long long count, int ctas, unsigned char* h_handle) {
+    using namespace ag;
+    if (world < 2 || world > kXchgMaxWorld || rank < 0 || rank >= world || !d_buf || count < 4 || ctas < 1 || ctas > 148) {
+        set_error("ag_xchg_create: bad argument (world 2..%d)", kXchgMaxWorld);
+        return nullptr;
+    }
+    ag_xchg* x = new ag_xchg();
+    memset(x, 0, sizeof(*x));
+    x->rank = rank; x->world = world; x->ctas = ctas; x->local = d_buf; x->count = (size_t)count;
+    if (cudaMalloc(&x->sig, kSigWords * sizeof(unsigned int)) != cudaSuccess || cudaMemset(x->sig, 0, kSigWords * sizeof(unsigned int)) != cudaSuccess) {
+        set_error("ag_xchg_create: cannot allocate the signal block");
+        delete x;
+        return nullptr;
+    }
+    CUdeviceptr base = 0;
+    size_t size = 0;
+    typedef CUresult (*range_fn)(CUdeviceptr*, size_t*, CUdeviceptr);
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fp, cudaEnableDefault, &q) != cudaSuccess || !fp ||
+        ((range_fn)fp)(&base, &size, (CUdeviceptr)(uintptr_t)d_buf) != CUDA_SUCCESS) {
+        set_error("ag_xchg_create: cuMemGetAddressRange failed");
+        cudaFree(x->sig); delete x;
+        return nullptr;
+    }
+    x->buf_offset = (long long)((uintptr_t)d_buf - (uintptr_t)base);
+    cudaIpcMemHandle_t hb, hs;
+    if (cudaIpcGetMemHandle(&hb, (void*)(uintptr_t)base) != cudaSuccess || cudaIpcGetMemHandle(&hs, x->sig) != cudaSuccess) {
+        set_error("ag_xchg_create: cudaIpcGetMemHandle failed (%s)", cudaGetErrorString(cudaGetLastError()));
+        cudaFree(x->sig); delete x;
+        return nullptr;
+    }
+    memcpy(h_handle, &hb, 64);
+    memcpy(h_handle + 64, &hs, 64);
+    memcpy(h_handle + 128, &x->buf_offset, 8);
+    memset(h_handle + 136, 0, 8);
+    return x;
+}
+
+// h_all: the 144-byte records of all ranks in rank order.  Maps the peers' buffers and signal blocks.
+int ag_xchg_connect(ag_xchg* x, const unsigned char* h_all) {
+    using namespace ag;
+    for (int r = 0; r < x->world; r++) {
+        if (r == x->rank) { x->peers.buf[r] = x->local; x->peers.sig[r] = x->sig; continue; }
+        cudaIpcMemHandle_t hb, hs;
+        long long off;
+        memcpy(&hb, h_all + (size_t)r * 144, 64);
+        memcpy(&hs, h_all + (size_t)r * 144 + 64, 64);
+        memcpy(&off, h_all + (size_t)r * 144 + 128, 8);
+        void *pb = nullptr, *ps = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&pb, hb, cudaIpcMemLazyEnablePeerAccess);
+        if (e == cudaSuccess) { x->opened[x->n_opened++] = pb; e = cudaIpcOpenMemHandle(&ps, hs, cudaIpcMemLazyEnablePeerAccess); }
+        if (e != cudaSuccess) { (void)cudaGetLastError(); set_error("ag_xchg_connect: cannot map rank %d's memory (%s)", r, cudaGetErrorString(e)); return AG_ECUDA; }
+        x->opened[x->n_opened++] = ps;
+        x->peers.buf[r] = reinterpret_cast<float*>(static_cast<unsigned char*>(pb) + off);
+        x->peers.sig[r] = static_cast<unsigned int*>(ps);
+    }
+    return AG_OK;
+}
+
+// In-place sum all-reduce of buf[start : start + count) on every rank (same arguments, same call order on all ranks; start and
+// count multiples of 4 floats).  Everything queued on `stream` before the call must make this rank's part of the range final.
+int ag_xchg_allreduce(ag_xchg* x, long long start, long long count, void* stream) {
+    using namespace ag;
+    if (start < 0 || count < 0 || (start & 3) || (count & 3) || (size_t)(start + count) > x->count) {
+        set_error("ag_xchg_allreduce: range [%lld, +%lld) must be 4-float aligned and inside the buffer of %zu", start, count, x->count);
+        return AG_EINVAL;
+    }
+    if (count == 0) return AG_OK;
+    x->seq++;
+    xchg_allreduce_kernel<<<x->ctas, kXchgThreads, 0, (cudaStream_t)stream>>>(x->peers, x->rank, x->world, (size_t)start, (size_t)count, x->seq);
+    AG_LAUNCH_CHECK("xchg_allreduce_kernel");
+    return AG_OK;
+}
+
+void ag_xchg_destroy(ag_xchg* x) {
+    if (!x) return;
+    cudaDeviceSynchronize();
+    for (int i = 0; i < x->n_opened; i++) cudaIpcCloseMemHandle(x->opened[i]);
+    cudaFree(x->sig);
+    delete x;
+}
+
+}  // extern "C"

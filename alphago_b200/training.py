@@ -46,6 +46,48 @@ def allreduce_in_buckets(dist, flat, plan, group=None, after_bucket=None):
     return works
 
 
+class PeerExchange(object):
+    """Sum all-reduce of ranges of a net's gradient buffer over NVLink peer memory (csrc/xchg.cu) for the ranks of one node:
+    what SLTrainer uses instead of NCCL's ring when every rank can map every other rank's buffer.  Collective to build
+    (the IPC handles travel through torch.distributed); raises AlphaGoB200Error when the peers cannot be mapped."""
+
+    def __init__(self, net, dist, group=None, ctas=16):
+        import torch
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        rec = (C.c_ubyte * 144)()
+        self._h = _lib.lib().ag_xchg_create(self.rank, self.world, C.c_void_p(net.grad_ptr), net.grad_count, int(ctas), rec)
+        ok = torch.tensor([1 if self._h else 0], device="cuda")
+        mine = torch.frombuffer(bytearray(bytes(rec)), dtype=torch.uint8).cuda()
+        every = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(every, mine, group=group)
+        if self._h:
+            table = b"".join(bytes(t.cpu().numpy().tobytes()) for t in every)
+            if _lib.lib().ag_xchg_connect(self._h, table) != 0:
+                ok[0] = 0
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)   # all ranks use it, or none
+        if int(ok.item()) == 0:
+            err = _lib.last_error()
+            self.close()
+            raise _lib.AlphaGoB200Error("peer gradient exchange unavailable: " + err)
+        dist.barrier(group=group)
+
+    def allreduce(self, start, end, stream):
+        """in place over grads[start:end] (4-float aligned); asynchronous on `stream` (a torch.cuda.Stream)"""
+        _lib.check(_lib.lib().ag_xchg_allreduce(self._h, int(start), int(end - start), C.c_void_p(stream.cuda_stream)), "ag_xchg_allreduce")
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.lib().ag_xchg_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class SLTrainer(object):
     def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=6, process_group=None):
         import torch
@@ -66,7 +108,18 @@ class SLTrainer(object):
             import os
             import torch as _t
             sms = _t.cuda.get_device_properties(_t.cuda.current_device()).multi_processor_count
-            net.set_sm_budget(max(1, sms - int(os.environ.get("AG_DP_RESERVE_SMS", "4"))))
+            # AG_DP_XCHG: "peer" (default) = the library's two-shot all-reduce over mapped peer memory, NCCL if the peers cannot
+            # be mapped; "nccl" = torch.distributed's all_reduce
+            self.xchg = None
+            if os.environ.get("AG_DP_XCHG", "peer") == "peer":
+                try:
+                    self.xchg = PeerExchange(net, self.dist, self.group, ctas=int(os.environ.get("AG_DP_XCHG_CTAS", "16")))
+                except _lib.AlphaGoB200Error:
+                    self.xchg = None
+            # SMs kept out of the weight-gradient grids for the exchange running beside them: NCCL's kernels need SMs of their
+            # own (4 measured best on 2 GPUs); the peer exchange has no shared memory and shares SMs with the chain
+            reserve = os.environ.get("AG_DP_RESERVE_SMS", "0" if self.xchg is not None else "4")
+            net.set_sm_budget(max(1, sms - int(reserve)) if int(reserve) > 0 else 0)
         # gradient buckets: contiguous runs of layers, last layers first (they finish first in backward)
         import os as _os
         self.plan = plan_buckets(net.n_conv, net.grad_offsets, int(_os.environ.get("AG_DP_BUCKETS", buckets)))
@@ -148,8 +201,20 @@ class SLTrainer(object):
             if self._side is None:
                 self._side = torch.cuda.Stream()
             works = []
+            main = torch.cuda.current_stream()
             for lo, hi, start, end in self.plan:
                 gate = net.wgrad_done(lo)
+                if self.xchg is not None:
+                    start4, end4 = start, end                      # layer slices and the buffer's end are whole 16-byte groups
+                    if gate is None:   # final when the main stream gets here
+                        ev = torch.cuda.Event()
+                        ev.record(main)
+                        self._side.wait_event(ev)
+                    else:
+                        _lib.check(_lib.lib().ag_stream_wait_value(C.c_void_p(self._side.cuda_stream), C.c_void_p(gate[0]), gate[1]),
+                                   "ag_stream_wait_value")
+                    self.xchg.allreduce(start4, end4, self._side)
+                    continue
                 if gate is None:   # not a chained layer (the first layer, a refused launch): final when the stream gets there
                     works.append(self.dist.all_reduce(flat[start:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
                     continue
@@ -159,6 +224,10 @@ class SLTrainer(object):
                     works.append(self.dist.all_reduce(flat[start:end], op=self.dist.ReduceOp.SUM, group=self.group, async_op=True))
             for w in works:
                 w.wait()
+            if self.xchg is not None:
+                ev = torch.cuda.Event()
+                ev.record(self._side)
+                main.wait_event(ev)
             net.sgd(lr, self.momentum, 1.0 / self.world)
         self.iterations += 1
 

@@ -352,6 +352,55 @@ class TrainWorkload(object):
         except Exception as e:  # the profiler is an aid: the bench line does not depend on it
             return {"unavailable": str(e)[:120]}
 
+    def timeline(self, path, steps=4):
+        """per-stream GPU timeline of one training step on this rank (CUPTI through torch.profiler's chrome trace): every kernel
+        with its stream, start and duration, NCCL's kernels included, and the time between the end of the last backward kernel
+        and the start of the SGD kernel -- what the gradient exchange leaves exposed"""
+        import tempfile
+        t = self.torch
+        from torch.profiler import ProfilerActivity, profile
+        for _ in range(3):
+            self.step()
+        t.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(steps):
+                self.step()
+            t.cuda.synchronize()
+        fd, tmp = tempfile.mkstemp(suffix=".json")
+        os.close(fd)
+        prof.export_chrome_trace(tmp)
+        ev = [e for e in json.load(open(tmp)).get("traceEvents", []) if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset") and "ts" in e]
+        os.unlink(tmp)
+        ev.sort(key=lambda e: e["ts"])
+        sgd = [i for i, e in enumerate(ev) if "sgd_all" in e["name"]]
+        if len(sgd) < 3:
+            return None
+        a, z = sgd[-3] + 1, sgd[-2] + 1          # one whole step: after an SGD kernel up to and including the next
+        rows = ev[a:z]
+        t0 = rows[0]["ts"]
+        lines = ["# one training step on rank %s of %s: kernels in start order; times in us from the step's first kernel" % (
+            os.environ.get("RANK", "0"), os.environ.get("WORLD_SIZE", "1")), "# %-8s %10s %10s  %s" % ("stream", "start", "dur", "kernel")]
+        last_bwd_end, first_nccl, last_nccl_end, sgd_start = 0.0, None, 0.0, None
+        for e in rows:
+            name = e["name"].replace("(anonymous namespace)::", "").split("(")[0]
+            st = e.get("args", {}).get("stream", "?")
+            lines.append("  %-8s %10.1f %10.1f  %s" % (st, e["ts"] - t0, e.get("dur", 0.0), name[-70:]))
+            end = e["ts"] - t0 + e.get("dur", 0.0)
+            if "nccl" in name.lower():
+                first_nccl = e["ts"] - t0 if first_nccl is None else first_nccl
+                last_nccl_end = max(last_nccl_end, end)
+            elif "sgd_all" in name:
+                sgd_start = e["ts"] - t0
+            elif "wgrad" in name or "conv_chain" in name:
+                last_bwd_end = max(last_bwd_end, end)
+        lines.append("# step span %.1f us; last backward kernel ends at %.1f" % (rows[-1]["ts"] - t0 + rows[-1].get("dur", 0.0), last_bwd_end))
+        if first_nccl is not None and sgd_start is not None:
+            lines.append("# first NCCL kernel starts at %.1f (%.1f us before the backward pass ends), last ends at %.1f; SGD starts at %.1f: "
+                         "%.1f us between the end of backward and the update" % (first_nccl, last_bwd_end - first_nccl, last_nccl_end, sgd_start,
+                                                                               sgd_start - last_bwd_end))
+        open(path, "w").write("\n".join(lines) + "\n")
+        return path
+
     def sustained(self, seconds=2.2, ms_per_step=1.7):
         """the same step for >= `seconds` back to back with its own clock samples: the power governor settles (the SM clock
         drops to ~1.65 GHz), which is what the sustained cuBLAS peak was measured under"""
@@ -493,6 +542,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-encoder", action="store_true")
     ap.add_argument("--no-sustained", action="store_true", help="skip the 2 s sustained run and the in-step kernel timeline")
+    ap.add_argument("--timeline", default=None, help="train workload: write rank 0's per-stream kernel timeline of one step to this file")
     args = ap.parse_args()
     rank, world, local = dist_env()
     workload = args.workload or "train"
@@ -584,6 +634,12 @@ def main():
         sustained = wl.sustained(2.2, ms_per_step)
         barrier()
         in_step = wl.in_step_durations()
+        barrier()
+    if workload == "train" and args.timeline:
+        try:   # every rank profiles (the step holds a collective); rank 0 writes
+            wl.timeline(args.timeline if rank == 0 else os.devnull)
+        except Exception as e:
+            sys.stderr.write("timeline failed: %s\n" % e)
         barrier()
 
     if rank == 0:

@@ -57,7 +57,10 @@ int ag_feature_planes(int feature);
  *                                   can leave a stale ko that cannot be re-derived from the board)
  *   h_features / n_features         feature ids in list order (any subset, order, repeats)
  *   d_out    uint8 [n][planes][size*size], one-hot 0/1 (the reference emits the same values as float64)
- * size in {2..19}; total planes <= 64. */
+ * size in {2..19}; total planes <= 64.  Two launches when ladder planes are asked for (the encoder queues the candidate
+ * moves, a second kernel reads them out); their work list lives in a per-device work area of the library that is
+ * allocated on the first such call and grown when a call brings more positions than any before (cudaMalloc / cudaFree:
+ * those calls synchronise the device); all other calls allocate nothing.  At most four encodes in flight per device. */
 int ag_encode(const int8_t* d_board, const uint8_t* d_age, const int8_t* d_player, const int16_t* d_ko,
               int n, int size, const int32_t* h_features, int n_features, uint8_t* d_out, void* stream);
 
@@ -151,6 +154,20 @@ int ag_net_set_sm_budget(ag_net* net, int sms);
  * bucket's all-reduce. */
 int ag_net_wgrad_done(ag_net* net, int layer, unsigned int** d_counter, unsigned int* target);
 int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int value);
+/* Gradient exchange over NVLink peer memory (no counterpart in the reference): a two-shot sum all-reduce of ranges of the
+ * buffer ag_net_grads() returns, for the ranks of ONE node, one process per GPU.  ag_xchg_create() makes this rank's end and
+ * fills h_handle (144 bytes: CUDA IPC handles of the buffer's allocation and of a signal block, the buffer's offset);
+ * the caller all-gathers the records of all ranks (any transport) and passes them, in rank order, to ag_xchg_connect().
+ * ag_xchg_allreduce(start, count) then sums buf[start : start+count) over the ranks in place -- every rank must make the
+ * same calls in the same order; `stream` order (or a gate such as ag_stream_wait_value) must make this rank's part of the
+ * range final before the kernel starts.  The owner of a slice reduces it in rank order and everybody copies its result:
+ * all ranks end with bit-identical sums.  `ctas` CTAs (16 is plenty) of 512 threads and no shared memory: they fit next
+ * to the network's kernels on the same SMs.  Peer memory is read with ordinary loads only. */
+typedef struct ag_xchg ag_xchg;
+ag_xchg* ag_xchg_create(int rank, int world, float* d_buf, long long count, int ctas, unsigned char* h_handle);
+int ag_xchg_connect(ag_xchg* x, const unsigned char* h_all);
+int ag_xchg_allreduce(ag_xchg* x, long long start, long long count, void* stream);
+void ag_xchg_destroy(ag_xchg* x);
 /* loss differentiated by ag_net_forward_loss: 0 = categorical cross-entropy (compile(loss='categorical_crossentropy'),
  * supervised_policy_trainer.py:200), 1 = Keras binary_crossentropy on the softmax outputs
  * (compile(loss='binary_crossentropy'), reinforcement_policy_trainer.py:109) */

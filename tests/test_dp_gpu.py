@@ -45,6 +45,23 @@ def _worker(rank, world, port, out, shape):
     net, _ = _setup_net(share, shape)
     tr = SLTrainer(net, lr=0.05, decay=0.0, momentum=0.9)
     assert tr.world == world and tr.flag_gated
+    # the peer-memory exchange on its own first: every rank holds (rank + 1) * pattern, the sum is world (world + 1) / 2 * pattern
+    peer = tr.xchg is not None
+    if peer:
+        flat = net.grad_tensor()
+        pattern = (torch.arange(flat.numel(), device="cuda", dtype=torch.float32) % 1021) - 510.0
+        side = torch.cuda.Stream()
+        for start, end in ((0, flat.numel()), (net.grad_offsets[1], net.grad_offsets[2]), (net.grad_offsets[-2], flat.numel())):
+            flat.copy_(pattern * (rank + 1))
+            torch.cuda.synchronize()
+            dist.barrier()
+            tr.xchg.allreduce(start, end, side)
+            side.synchronize()
+            want = pattern * (rank + 1)
+            want[start:end] = pattern[start:end] * (world * (world + 1) / 2)
+            assert torch.equal(flat, want), (rank, start, end)
+        flat.zero_()
+        dist.barrier()
     sl = slice(rank * share, (rank + 1) * share)
     for _ in range(2):
         tr.step(torch.from_numpy(x[sl]).cuda(), torch.from_numpy(y[sl]).cuda())
@@ -53,7 +70,7 @@ def _worker(rank, world, port, out, shape):
     if rank == 0:
         # the exchange of the chained layers was gated by their "gradient final" counters, not by launch boundaries
         gated = [net.wgrad_done(l) is not None for l in range(net.n_conv)]
-        np.savez(out, loss=loss, gated=np.asarray(gated), **{"w%d" % l: net.get_conv(l)[0] for l in range(net.n_conv)},
+        np.savez(out, loss=loss, gated=np.asarray(gated), peer=np.asarray(peer), **{"w%d" % l: net.get_conv(l)[0] for l in range(net.n_conv)},
                  hw=net.get_head(0)[0])
     dist.barrier()
     dist.destroy_process_group()
@@ -78,6 +95,7 @@ def test_two_rank_step_equals_single_rank_step(tmp_path, shape):
         tr.step(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
     loss, _ = tr.pop_metrics(2 * n)
     assert abs(loss - float(dp["loss"])) < 2e-3 * max(1.0, abs(loss))
+    assert bool(dp["peer"])   # the ranks of one node exchange gradients through mapped peer memory (csrc/xchg.cu), not NCCL
     if shape == "bench":   # every hidden layer ran chained and gave a counter to wait for
         assert dp["gated"][1:].all() and not dp["gated"][0], dp["gated"]
     for l in range(net.n_conv):
