@@ -20,6 +20,7 @@ def bind(L):
     L.ag_net_set_loss.argtypes = [vp, i]
     L.ag_net_wgrad_done.argtypes = [vp, i, C.POINTER(vp), C.POINTER(C.c_uint)]
     L.ag_stream_wait_value.argtypes = [vp, vp, C.c_uint]
+    L.ag_net_wait_first_layer.argtypes = [vp, vp]
     L.ag_net_grads.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_longlong), vp]
     L.ag_net_sgd.argtypes = [vp, C.c_float, C.c_float, C.c_float, vp]
     L.ag_net_train_step.argtypes = [vp, vp, vp, i, C.c_float, C.c_float, vp, vp]

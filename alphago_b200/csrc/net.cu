@@ -536,6 +536,8 @@ struct ag_net {
     unsigned int chain_epoch_fwd = 0, chain_epoch_bwd = 0;
     int chain_win_rows = 0, chain_nmax_fwd = 0, chain_nmax_bwd = 0;
     bool dgrad_chain_done = false;  // the data-gradient chain of the current forward_loss has been queued
+    cudaEvent_t ev_first = nullptr;     // recorded after the first layer's weight-gradient kernels when they are queued ahead of the chain
+    bool first_layer_early = false;     // ... in the latest backward pass
     bool wgrad_chain_refused = false;   // a chained weight-gradient launch was refused (grid not co-resident): stay on per-layer kernels
     int chain_fallbacks = 0;        // chained launches the device refused, each answered by the per-layer kernels
     // head
@@ -884,6 +886,7 @@ ag_net* ag_net_create(int board, int in_planes, int n_conv, const int* h_filters
 }
 
 void ag_net_destroy(ag_net* net) {
+    if (net && net->ev_first) cudaEventDestroy(net->ev_first);
     if (!net) return;
     for (auto& c : net->L) { cudaFree(c.w); cudaFree(c.b); cudaFree(c.vw); cudaFree(c.vb); cudaFree(c.wf); cudaFree(c.wb); cudaFree(c.act); cudaFree(c.mask); }
     float* f[] = {net->hw, net->hb, net->hpos, net->vhw, net->vhb, net->vhpos, net->d1w, net->d1b, net->d2w, net->d2b,
@@ -1114,6 +1117,18 @@ static bool same_wgrad_geometry(const ConvLayer& a, const ConvLayer& b) {
 
 // weight gradients of layers hi .. lo: runs of layers with one geometry go out as chained launches (wgrad.cu)
 static int net_wgrad_range(ag_net* net, int hi, int lo, int n, cudaStream_t st) {
+    // The first layer's weight gradient needs only the data-gradient chain's result, and its own kernels do not join the
+    // chained launch: queued FIRST, its gradient can be exchanged while the chain runs, and what is left exposed at the
+    // end of the backward pass is the exchange of the chain's last layer instead of two buckets.  An event marks the point.
+    net->first_layer_early = false;
+    if (lo == 0 && hi > 0 && !net->L[0].wgrad_chain && net->L[1].wgrad_chain) {
+        int rc = net_wgrad_one(net, 0, n, st);
+        if (rc) return rc;
+        if (!net->ev_first) AG_CUDA(cudaEventCreateWithFlags(&net->ev_first, cudaEventDisableTiming));
+        AG_CUDA(cudaEventRecord(net->ev_first, st));
+        net->first_layer_early = true;
+        lo = 1;
+    }
     int l = hi;
     while (l >= lo) {
         ConvLayer& first = net->L[l];
@@ -1245,6 +1260,14 @@ int ag_net_wgrad_done(ag_net* net, int layer, unsigned int** d_counter, unsigned
     if (!c.wgrad_chain || c.wgrad_chain_count == 0) { set_error("ag_net_wgrad_done: layer %d does not run chained", layer); return AG_ESTATE; }
     *d_counter = net->wgrad_counters + (size_t)layer * kWgradCounterStride + (kWgradCounterStride - 1);
     *target = c.wgrad_done_target;
+    return AG_OK;
+}
+
+// Makes `stream` wait for the first layer's weight gradient of the latest ag_net_backward_range when that call queued it ahead
+// of the chained launch (AG_OK), else AG_ESTATE: the gradient is then final where the backward call ends in its stream.
+int ag_net_wait_first_layer(ag_net* net, void* stream) {
+    if (!net->first_layer_early || !net->ev_first) { set_error("ag_net_wait_first_layer: the first layer was not queued early"); return AG_ESTATE; }
+    AG_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, net->ev_first, 0));
     return AG_OK;
 }
 

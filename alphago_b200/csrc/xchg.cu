@@ -24,7 +24,7 @@
 namespace ag {
 
 constexpr int kXchgMaxWorld = 16;
-constexpr int kXchgThreads = 512;
+constexpr int kXchgThreads = 256;   // x 77 registers: a CTA fits next to a chained CTA of the network on the same SM
 
 struct XchgPeers {
     float* buf[kXchgMaxWorld];            // every rank's gradient buffer (own one included), same layout
@@ -72,14 +72,35 @@ xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size
     const size_t per = (n4 + world - 1) / world;
     const size_t lo = per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = lo + tid; i < hi; i += nthr) {
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-        for (int r = 0; r < world; r++) {
-            const float4 v = __ldcv(reinterpret_cast<const float4*>(P.buf[r] + start) + i);
-            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    // kU independent 16-byte groups per thread and pass, every load issued before the first add: the loop is bound by NVLink
+    // latency (2-3 us a round trip), so what counts is how many loads are in flight (one group per pass took 120 us a bucket)
+    constexpr int kU = 4;
+    for (size_t i0 = lo + tid; i0 < hi; i0 += nthr * kU) {
+        float4 a[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+        for (int r0 = 0; r0 < world; r0 += 4) {
+            float4 v[4][kU];
+#pragma unroll
+            for (int rr = 0; rr < 4; rr++) {
+                const float4* src = reinterpret_cast<const float4*>(P.buf[r0 + rr < world ? r0 + rr : rank] + start);
+#pragma unroll
+                for (int u = 0; u < kU; u++) {
+                    const size_t i = i0 + (size_t)u * nthr;
+                    v[rr][u] = (r0 + rr < world && i < hi) ? __ldcv(src + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+#pragma unroll
+            for (int rr = 0; rr < 4; rr++)       // rank order 0, 1, 2, ...: the same sum on whichever rank owns the slice
+#pragma unroll
+                for (int u = 0; u < kU; u++) { a[u].x += v[rr][u].x; a[u].y += v[rr][u].y; a[u].z += v[rr][u].z; a[u].w += v[rr][u].w; }
         }
-        reinterpret_cast<float4*>(P.buf[rank] + start)[i] = a;
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const size_t i = i0 + (size_t)u * nthr;
+            if (i < hi) reinterpret_cast<float4*>(P.buf[rank] + start)[i] = a[u];
+        }
     }
     // all my CTAs done -> the last one tells the peers
     __syncthreads();
@@ -97,7 +118,14 @@ xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size
         const size_t rlo = per * r < n4 ? per * r : n4, rhi = rlo + per < n4 ? rlo + per : n4;
         const float4* src = reinterpret_cast<const float4*>(P.buf[r] + start);
         float4* dst = reinterpret_cast<float4*>(P.buf[rank] + start);
-        for (size_t i = rlo + tid; i < rhi; i += nthr) dst[i] = __ldcv(src + i);
+        constexpr int kC = 8;
+        for (size_t i0 = rlo + tid; i0 < rhi; i0 += nthr * kC) {
+            float4 v[kC];
+#pragma unroll
+            for (int u = 0; u < kC; u++) { const size_t i = i0 + (size_t)u * nthr; if (i < rhi) v[u] = __ldcv(src + i); }
+#pragma unroll
+            for (int u = 0; u < kC; u++) { const size_t i = i0 + (size_t)u * nthr; if (i < rhi) dst[i] = v[u]; }
+        }
     }
     // ---- 3. I have stopped reading: tell everybody; leave only when everybody has (their buffers are about to be reused, mine too)
     __syncthreads();

@@ -35,6 +35,25 @@ def plan_buckets(n_conv, offsets, buckets=4):
     return plan
 
 
+def plan_exchange(n_conv, offsets, buckets=5):
+    """Exchange plan for the counter-gated path: [(layer_lo, layer_hi, start, end)] in the order the slices become final
+    when the first layer's weight gradient is queued ahead of the chained launch: the first layer alone, then runs of
+    layers top down (the first of them also carries the head's slice), the LAST bucket being layer 1 alone -- its exchange is
+    the only one nothing is left to hide behind, so it should be the smallest."""
+    if n_conv < 3:
+        return plan_buckets(n_conv, offsets, min(buckets, 2))
+    plan = [(0, 1, offsets[0], offsets[1])]
+    body = max(1, min(buckets - 2, n_conv - 2))          # buckets between the first layer's and layer 1's
+    per = (n_conv - 2 + body - 1) // body
+    hi = n_conv
+    while hi > 2:
+        lo = max(2, hi - per)
+        plan.append((lo, hi, offsets[lo], offsets[-1] if hi == n_conv else offsets[hi]))
+        hi = lo
+    plan.append((1, 2, offsets[1], offsets[2]))
+    return plan
+
+
 def allreduce_in_buckets(dist, flat, plan, group=None, after_bucket=None):
     """sum-all-reduce `flat` slice by slice following `plan`; `after_bucket(i)` (optional) runs before bucket i is
     issued -- SLTrainer enqueues that bucket's backward kernels there.  Returns the async work handles."""
@@ -51,7 +70,7 @@ class PeerExchange(object):
     what SLTrainer uses instead of NCCL's ring when every rank can map every other rank's buffer.  Collective to build
     (the IPC handles travel through torch.distributed); raises AlphaGoB200Error when the peers cannot be mapped."""
 
-    def __init__(self, net, dist, group=None, ctas=16):
+    def __init__(self, net, dist, group=None, ctas=32):
         import torch
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -113,7 +132,7 @@ class SLTrainer(object):
             self.xchg = None
             if os.environ.get("AG_DP_XCHG", "peer") == "peer":
                 try:
-                    self.xchg = PeerExchange(net, self.dist, self.group, ctas=int(os.environ.get("AG_DP_XCHG_CTAS", "16")))
+                    self.xchg = PeerExchange(net, self.dist, self.group, ctas=int(os.environ.get("AG_DP_XCHG_CTAS", "32")))
                 except _lib.AlphaGoB200Error:
                     self.xchg = None
             # SMs kept out of the weight-gradient grids for the exchange running beside them: NCCL's kernels need SMs of their
@@ -127,6 +146,8 @@ class SLTrainer(object):
         # (cuStreamWaitValue32 on a side stream), so the exchange starts inside the one chained launch; 0: buckets are cut
         # at launch boundaries and gated by stream order
         self.flag_gated = _os.environ.get("AG_DP_FLAGS", "1") != "0"
+        if self.dist is not None and self.flag_gated and getattr(self, "xchg", None) is not None:
+            self.plan = plan_exchange(net.n_conv, net.grad_offsets, int(_os.environ.get("AG_DP_BUCKETS", buckets)))
         self._side = None
         self._out = None
         self._labels = None
@@ -206,10 +227,13 @@ class SLTrainer(object):
                 gate = net.wgrad_done(lo)
                 if self.xchg is not None:
                     start4, end4 = start, end                      # layer slices and the buffer's end are whole 16-byte groups
-                    if gate is None:   # final when the main stream gets here
-                        ev = torch.cuda.Event()
-                        ev.record(main)
-                        self._side.wait_event(ev)
+                    if gate is None:
+                        # the first layer: queued ahead of the chain, the library marks the point; else final when the main
+                        # stream gets here
+                        if not (lo == 0 and hi == 1 and _lib.lib().ag_net_wait_first_layer(net._h, C.c_void_p(self._side.cuda_stream)) == 0):
+                            ev = torch.cuda.Event()
+                            ev.record(main)
+                            self._side.wait_event(ev)
                     else:
                         _lib.check(_lib.lib().ag_stream_wait_value(C.c_void_p(self._side.cuda_stream), C.c_void_p(gate[0]), gate[1]),
                                    "ag_stream_wait_value")

@@ -154,6 +154,10 @@ int ag_net_set_sm_budget(ag_net* net, int sms);
  * bucket's all-reduce. */
 int ag_net_wgrad_done(ag_net* net, int layer, unsigned int** d_counter, unsigned int* target);
 int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int value);
+/* ag_net_backward_range over all layers queues the first layer's weight gradient (its own kernels) AHEAD of the chained
+ * launch of the others; this makes `stream` wait for exactly that point, so the first layer's gradient can be exchanged
+ * while the chain runs.  AG_ESTATE when the latest backward call did not do so. */
+int ag_net_wait_first_layer(ag_net* net, void* stream);
 /* Gradient exchange over NVLink peer memory (no counterpart in the reference): a two-shot sum all-reduce of ranges of the
  * buffer ag_net_grads() returns, for the ranks of ONE node, one process per GPU.  ag_xchg_create() makes this rank's end and
  * fills h_handle (144 bytes: CUDA IPC handles of the buffer's allocation and of a signal block, the buffer's offset);
@@ -161,7 +165,7 @@ int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int 
  * ag_xchg_allreduce(start, count) then sums buf[start : start+count) over the ranks in place -- every rank must make the
  * same calls in the same order; `stream` order (or a gate such as ag_stream_wait_value) must make this rank's part of the
  * range final before the kernel starts.  The owner of a slice reduces it in rank order and everybody copies its result:
- * all ranks end with bit-identical sums.  `ctas` CTAs (16 is plenty) of 512 threads and no shared memory: they fit next
+ * all ranks end with bit-identical sums.  `ctas` CTAs (32 is plenty) of 256 threads and no shared memory: they fit next
  * to the network's kernels on the same SMs.  Peer memory is read with ordinary loads only. */
 typedef struct ag_xchg ag_xchg;
 ag_xchg* ag_xchg_create(int rank, int world, float* d_buf, long long count, int ctas, unsigned char* h_handle);

@@ -6,7 +6,7 @@ tail -3 gpurun_out/pytest_dp.log
 CONFIGS=${CONFIGS:-8,4 4,4 2,4 0,4 4,3 4,6}
 for cfg in $CONFIGS; do
   r=${cfg%,*}; b=${cfg#*,}
-  AG_DP_XCHG=${XCHG:-peer} AG_DP_XCHG_CTAS=${CTAS:-16} AG_DP_RESERVE_SMS=$r AG_DP_BUCKETS=$b timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps ${STEPS:-100} --warmup 10 --no-cpu-baseline --no-encoder --no-sustained --timeline gpurun_out/r2_timeline_${N}gpu_${XCHG:-peer}_r${r}_b${b}.txt > gpurun_out/dp${N}_r${r}_b${b}.json 2> gpurun_out/dp${N}_r${r}_b${b}.err
+  AG_DP_XCHG=${XCHG:-peer} AG_DP_XCHG_CTAS=${CTAS:-32} AG_DP_RESERVE_SMS=$r AG_DP_BUCKETS=$b timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps ${STEPS:-100} --warmup 10 --no-cpu-baseline --no-encoder --no-sustained --timeline gpurun_out/r2_timeline_${N}gpu_${XCHG:-peer}_r${r}_b${b}.txt > gpurun_out/dp${N}_r${r}_b${b}.json 2> gpurun_out/dp${N}_r${r}_b${b}.err
   python - <<PY
 import json
 try:
