@@ -108,7 +108,7 @@ class PeerExchange(object):
 
 
 class SLTrainer(object):
-    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=6, process_group=None):
+    def __init__(self, net, lr=0.03, decay=0.0001, momentum=0.0, buckets=5, process_group=None):
         import torch
         self.torch = torch
         self.net, self.lr0, self.decay, self.momentum = net, float(lr), float(decay), float(momentum)

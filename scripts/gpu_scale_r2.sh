@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 N=${NGPU:-8}
 for steps in 20 100; do
-  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps $steps --warmup 5 --no-cpu-baseline --no-encoder > gpurun_out/r2_scale_${N}gpu_${steps}steps.json 2> gpurun_out/scale_${N}_${steps}.err
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps $steps --warmup 5 --no-cpu-baseline --no-encoder --timeline gpurun_out/r2_timeline_${N}gpu_peer_${steps}steps.txt > gpurun_out/r2_scale_${N}gpu_${steps}steps.json 2> gpurun_out/scale_${N}_${steps}.err
   python - <<PY
 import json
 try:
