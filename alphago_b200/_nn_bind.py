@@ -38,6 +38,7 @@ def bind(L):
     L.ag_xchg_create.argtypes = [i, i, vp, C.c_longlong, i, vp]
     L.ag_xchg_connect.argtypes = [vp, vp]
     L.ag_xchg_allreduce.argtypes = [vp, C.c_longlong, C.c_longlong, vp]
+    L.ag_xchg_wait_readers.argtypes = [vp, vp]
     L.ag_xchg_destroy.argtypes = [vp]; L.ag_xchg_destroy.restype = None
     L.ag_selfplay_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_longlong, vp, C.c_float, i, i, vp, vp]
     L.ag_selfplay_winner.argtypes = [vp, vp, i, i, C.c_float, vp, vp]

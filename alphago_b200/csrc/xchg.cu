@@ -6,8 +6,8 @@
 //   1. reduce-scatter: this rank owns slice r of the bucket and sums it over all ranks' buffers with plain 16-byte peer
 //      loads, always in rank order 0..world-1, into its own buffer
 //   2. tell every peer "my slice is reduced", wait for theirs, and copy the other slices from their owners
-//   3. tell every peer "I have stopped reading", wait for theirs: nobody's buffer is written again (the next backward pass)
-//      while a peer may still read it
+//   3. count itself off in every rank's signal block ("I have stopped reading"); a rank waits for that count -- a stream
+//      memory operation, ag_xchg_wait_readers -- before its next backward pass writes its buffer again
 // Flags are 32-bit sequence numbers in each rank's own signal block, written by the peers with system-scope release
 // stores and polled locally with acquire loads; they only ever grow, so a rank that runs ahead cannot confuse a slower one.
 // Because the owner alone reduces a slice and everybody copies its result, all ranks end with bit-identical sums
@@ -20,6 +20,8 @@
 #include <string.h>
 
 #include "common.cuh"
+
+extern "C" int ag_stream_wait_value(void* stream, const unsigned int* d_addr, unsigned int value);
 
 namespace ag {
 
@@ -74,16 +76,16 @@ xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
     // kU independent 16-byte groups per thread and pass, every load issued before the first add: the loop is bound by NVLink
     // latency (2-3 us a round trip), so what counts is how many loads are in flight (one group per pass took 120 us a bucket)
-    constexpr int kU = 4;
+    constexpr int kU = 2, kR = 8;   // 16 loads in flight per thread: two groups x eight ranks
     for (size_t i0 = lo + tid; i0 < hi; i0 += nthr * kU) {
         float4 a[kU];
 #pragma unroll
         for (int u = 0; u < kU; u++) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
-        for (int r0 = 0; r0 < world; r0 += 4) {
-            float4 v[4][kU];
+        for (int r0 = 0; r0 < world; r0 += kR) {
+            float4 v[kR][kU];
 #pragma unroll
-            for (int rr = 0; rr < 4; rr++) {
+            for (int rr = 0; rr < kR; rr++) {
                 const float4* src = reinterpret_cast<const float4*>(P.buf[r0 + rr < world ? r0 + rr : rank] + start);
 #pragma unroll
                 for (int u = 0; u < kU; u++) {
@@ -92,7 +94,7 @@ xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size
                 }
             }
 #pragma unroll
-            for (int rr = 0; rr < 4; rr++)       // rank order 0, 1, 2, ...: the same sum on whichever rank owns the slice
+            for (int rr = 0; rr < kR; rr++)       // rank order 0, 1, 2, ...: the same sum on whichever rank owns the slice
 #pragma unroll
                 for (int u = 0; u < kU; u++) { a[u].x += v[rr][u].x; a[u].y += v[rr][u].y; a[u].z += v[rr][u].z; a[u].w += v[rr][u].w; }
         }
@@ -113,30 +115,39 @@ xchg_allreduce_kernel(const XchgPeers P, int rank, int world, size_t start, size
     }
     // ---- 2. fetch the other slices from their owners
     wait_all(mine, kSigReduced, world, seq);
-    for (int d = 1; d < world; d++) {
-        const int r = (rank + d) % world;   // start with different owners on different ranks
-        const size_t rlo = per * r < n4 ? per * r : n4, rhi = rlo + per < n4 ? rlo + per : n4;
-        const float4* src = reinterpret_cast<const float4*>(P.buf[r] + start);
+    {
+        // one flat index over (owner, element) so that loads from ALL owners are in flight together (owner by owner, each pass
+        // paid an NVLink round trip: 7 of them on 8 GPUs); thread t starts with owner rank + 1 + t % (world - 1)
+        const size_t others = (size_t)(world - 1) * per;
         float4* dst = reinterpret_cast<float4*>(P.buf[rank] + start);
         constexpr int kC = 8;
-        for (size_t i0 = rlo + tid; i0 < rhi; i0 += nthr * kC) {
+        for (size_t j0 = tid; j0 < others; j0 += nthr * kC) {
             float4 v[kC];
+            size_t at[kC];
 #pragma unroll
-            for (int u = 0; u < kC; u++) { const size_t i = i0 + (size_t)u * nthr; if (i < rhi) v[u] = __ldcv(src + i); }
+            for (int u = 0; u < kC; u++) {
+                const size_t j = j0 + (size_t)u * nthr;
+                at[u] = (size_t)-1;
+                if (j < others) {
+                    const int r = (rank + 1 + (int)(j % (size_t)(world - 1))) % world;   // interleave the owners
+                    const size_t i = per * r + j / (size_t)(world - 1);
+                    if (i < n4 && i < per * (r + 1)) { at[u] = i; v[u] = __ldcv(reinterpret_cast<const float4*>(P.buf[r] + start) + i); }
+                }
+            }
 #pragma unroll
-            for (int u = 0; u < kC; u++) { const size_t i = i0 + (size_t)u * nthr; if (i < rhi) dst[i] = v[u]; }
+            for (int u = 0; u < kC; u++) if (at[u] != (size_t)-1) dst[at[u]] = v[u];
         }
     }
-    // ---- 3. I have stopped reading: tell everybody; leave only when everybody has (their buffers are about to be reused, mine too)
+    // ---- 3. I have stopped reading: count myself off in every rank's block.  Nobody waits here: the owner of a buffer waits for
+    // the count (ag_xchg_wait_readers, a stream memory operation) before its next backward pass writes the buffer again
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
         const unsigned int arrived = atomicAdd(mine + kSigCtas2, 1u) + 1u;
         if (arrived == gridDim.x * seq) {
-            for (int r = 0; r < world; r++) st_release_sys(P.sig[r] + kSigFinished + rank, seq);
+            for (int r = 0; r < world; r++) asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(P.sig[r] + kSigFinished) : "memory");
         }
     }
-    wait_all(mine, kSigFinished, world, seq);
 }
 
 }  // namespace ag
@@ -231,6 +242,13 @@ int ag_xchg_allreduce(ag_xchg* x, long long start, long long count, void* stream
     xchg_allreduce_kernel<<<x->ctas, kXchgThreads, 0, (cudaStream_t)stream>>>(x->peers, x->rank, x->world, (size_t)start, (size_t)count, x->seq);
     AG_LAUNCH_CHECK("xchg_allreduce_kernel");
     return AG_OK;
+}
+
+// Makes `stream` wait until every rank has finished reading this rank's buffer in all exchanges issued so far: call it on
+// the stream that will overwrite the buffer (the next backward pass) before it does.  Costs no SM time.
+int ag_xchg_wait_readers(ag_xchg* x, void* stream) {
+    if (x->seq == 0) return AG_OK;
+    return ag_stream_wait_value(stream, x->sig + ag::kSigFinished, (unsigned int)x->world * x->seq);
 }
 
 void ag_xchg_destroy(ag_xchg* x) {

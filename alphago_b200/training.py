@@ -38,19 +38,21 @@ def plan_buckets(n_conv, offsets, buckets=4):
 def plan_exchange(n_conv, offsets, buckets=5):
     """Exchange plan for the counter-gated path: [(layer_lo, layer_hi, start, end)] in the order the slices become final
     when the first layer's weight gradient is queued ahead of the chained launch: the first layer alone, then runs of
-    layers top down (the first of them also carries the head's slice), the LAST bucket being layer 1 alone -- its exchange is
-    the only one nothing is left to hide behind, so it should be the smallest."""
-    if n_conv < 3:
+    layers top down (the first of them also carries the head's slice), and layers 1-2 last."""
+    if n_conv < 4:
         return plan_buckets(n_conv, offsets, min(buckets, 2))
+    # Every exchange kernel costs three cross-GPU barriers whatever its size (25-70 us from 2 to 8 GPUs): few buckets, and
+    # the last one -- gated by the end of the chained launch, so fully exposed -- is the two lowest chained layers together
+    # rather than two kernels of one layer each.
     plan = [(0, 1, offsets[0], offsets[1])]
-    body = max(1, min(buckets - 2, n_conv - 2))          # buckets between the first layer's and layer 1's
-    per = (n_conv - 2 + body - 1) // body
+    body = max(1, min(buckets - 2, n_conv - 3))          # buckets between the first layer's and the last two layers'
+    per = (n_conv - 3 + body - 1) // body
     hi = n_conv
-    while hi > 2:
-        lo = max(2, hi - per)
+    while hi > 3:
+        lo = max(3, hi - per)
         plan.append((lo, hi, offsets[lo], offsets[-1] if hi == n_conv else offsets[hi]))
         hi = lo
-    plan.append((1, 2, offsets[1], offsets[2]))
+    plan.append((1, 3, offsets[1], offsets[3]))
     return plan
 
 
@@ -94,6 +96,11 @@ class PeerExchange(object):
     def allreduce(self, start, end, stream):
         """in place over grads[start:end] (4-float aligned); asynchronous on `stream` (a torch.cuda.Stream)"""
         _lib.check(_lib.lib().ag_xchg_allreduce(self._h, int(start), int(end - start), C.c_void_p(stream.cuda_stream)), "ag_xchg_allreduce")
+
+    def wait_readers(self, stream):
+        """makes `stream` wait until every rank has finished reading this rank's buffer in the exchanges issued so far: to be
+        queued on the stream that overwrites the buffer next, before it does (SLTrainer.step does so at its start)"""
+        _lib.check(_lib.lib().ag_xchg_wait_readers(self._h, C.c_void_p(stream.cuda_stream)), "ag_xchg_wait_readers")
 
     def close(self):
         h, self._h = getattr(self, "_h", None), None
@@ -216,6 +223,8 @@ class SLTrainer(object):
             # and NCCL's stream waits for the side stream, so bucket k is on the wire while the same launch is still
             # computing the layers below it.
             torch = self.torch
+            if self.xchg is not None:   # the peers have finished reading last step's gradients before this step overwrites them
+                self.xchg.wait_readers(torch.cuda.current_stream())
             net.forward_loss(planes, labels, self.loss_acc)
             net.backward_range(net.n_conv - 1, 0, n)
             flat = net.grad_tensor()

@@ -171,6 +171,9 @@ typedef struct ag_xchg ag_xchg;
 ag_xchg* ag_xchg_create(int rank, int world, float* d_buf, long long count, int ctas, unsigned char* h_handle);
 int ag_xchg_connect(ag_xchg* x, const unsigned char* h_all);
 int ag_xchg_allreduce(ag_xchg* x, long long start, long long count, void* stream);
+/* makes `stream` wait until all ranks have finished reading this rank's buffer in the exchanges issued so far; call it on
+ * the stream that overwrites the buffer next (the following backward pass), before it does */
+int ag_xchg_wait_readers(ag_xchg* x, void* stream);
 void ag_xchg_destroy(ag_xchg* x);
 /* loss differentiated by ag_net_forward_loss: 0 = categorical cross-entropy (compile(loss='categorical_crossentropy'),
  * supervised_policy_trainer.py:200), 1 = Keras binary_crossentropy on the softmax outputs

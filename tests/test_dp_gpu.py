@@ -52,6 +52,7 @@ def _worker(rank, world, port, out, shape):
         pattern = (torch.arange(flat.numel(), device="cuda", dtype=torch.float32) % 1021) - 510.0
         side = torch.cuda.Stream()
         for start, end in ((0, flat.numel()), (net.grad_offsets[1], net.grad_offsets[2]), (net.grad_offsets[-2], flat.numel())):
+            tr.xchg.wait_readers(torch.cuda.current_stream())   # the peers are done with the previous round's values
             flat.copy_(pattern * (rank + 1))
             torch.cuda.synchronize()
             dist.barrier()
@@ -60,7 +61,9 @@ def _worker(rank, world, port, out, shape):
             want = pattern * (rank + 1)
             want[start:end] = pattern[start:end] * (world * (world + 1) / 2)
             assert torch.equal(flat, want), (rank, start, end)
+        tr.xchg.wait_readers(torch.cuda.current_stream())
         flat.zero_()
+        torch.cuda.synchronize()
         dist.barrier()
     sl = slice(rank * share, (rank + 1) * share)
     for _ in range(2):
