@@ -11,6 +11,7 @@ try:
 except Exception as e: print("n=$N steps=$steps failed", e)
 PY
 done
+[ -n "$SKIP1" ] && exit 0
 for steps in 20 100; do
   python bench.py --steps $steps --warmup 5 --no-cpu-baseline --no-encoder > gpurun_out/r2_scale_1gpu_samebox${N}_${steps}steps.json 2>> gpurun_out/scale_1.err
   python -c "
