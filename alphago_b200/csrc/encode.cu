@@ -135,9 +135,10 @@ __device__ __forceinline__ uint32_t plane_desc(int arr, int val) {
 // work list of ladder queries: header {appended, taken} then entries position << 16 | point << 5 | kind << 4 | prey mask
 // (bit j of the mask: neighbour j of the point, in go.py:96 order, is the first to touch a prey group)
 struct LadderWork {
-    unsigned int* head;      // [0] entries appended by encode_kernel, [1] next entry to take (ladder_resolve_kernel)
+    unsigned int* head;      // [0] capture queries appended by encode_kernel, [2] escape queries, [1] next query to take
     uint32_t* entries;
     uint32_t* bits;          // per position: 12 words of black stones, 12 words of white stones
+    unsigned int esc_base;   // where the escape queries start in `entries` (head[2] counts them)
 };
 
 __device__ __forceinline__ uint32_t uf_find(volatile uint32_t* parent, uint32_t a) {
@@ -432,14 +433,18 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
             if (tab.need_ladder && work.entries) {
                 __syncwarp();
                 const uint32_t bc = __ballot_sync(0xffffffffu, (lad & 0xFu) != 0), be = __ballot_sync(0xffffffffu, (lad >> 4) != 0);
-                if (bc | be) {
-                    unsigned int base = 0;
-                    if (lane == 0) base = atomicAdd(work.head, (unsigned int)(__popc(bc) + __popc(be)));
-                    base = __shfl_sync(0xffffffffu, base, 0);
+                if (bc | be) {   // two lists: capture queries from the front of the area, escape queries from its middle
+                    unsigned int bcap = 0, besc = 0;
+                    if (lane == 0) {
+                        if (bc) bcap = atomicAdd(work.head, (unsigned int)__popc(bc));
+                        if (be) besc = atomicAdd(work.head + 2, (unsigned int)__popc(be));
+                    }
+                    bcap = __shfl_sync(0xffffffffu, bcap, 0);
+                    besc = __shfl_sync(0xffffffffu, besc, 0);
                     const uint32_t lt = (1u << lane) - 1u;
                     const uint32_t e = (uint32_t)pos << 16 | (uint32_t)p << 5;
-                    if (lad & 0xFu) work.entries[base + __popc(bc & lt)] = e | (lad & 0xFu);
-                    if (lad >> 4) work.entries[base + __popc(bc) + __popc(be & lt)] = e | 16u | (lad >> 4);
+                    if (lad & 0xFu) work.entries[bcap + __popc(bc & lt)] = e | (lad & 0xFu);
+                    if (lad >> 4) work.entries[work.esc_base + besc + __popc(be & lt)] = e | 16u | (lad >> 4);
                 }
             }
         }
@@ -500,6 +505,9 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
 // (ladder_warp.cuh: the board's bit sets are spread over the lanes, so the search has one control path).  Only "yes"
 // answers are written: encode_kernel has already written zeros on both planes.
 constexpr int kResolveWarps = 8;
+#ifndef AG_LADDER_PICK
+#define AG_LADDER_PICK(idx) ((idx) < nesc ? work.entries[work.esc_base + nesc - 1u - (idx)] : work.entries[ncap - 1u - ((idx) - nesc)])
+#endif
 
 __global__ void __launch_bounds__(kResolveWarps * 32)
 ladder_resolve_kernel(const int8_t* __restrict__ g_player, const int16_t* __restrict__ g_ko, int size, int n_planes,
@@ -510,14 +518,16 @@ ladder_resolve_kernel(const int8_t* __restrict__ g_player, const int16_t* __rest
     WBoard B;
     B.m = wmasks_make(size, lane);
     B.size = size; B.lane = lane;
-    const unsigned int total = work.head[0];
+    const unsigned int ncap = work.head[0], nesc = work.head[2], total = ncap + nesc;
     unsigned int cur = 0xFFFFFFFFu;
     while (true) {
         unsigned int idx = 0;
         if (lane == 0) idx = atomicAdd(&work.head[1], 1u);
         idx = __shfl_sync(0xffffffffu, idx, 0);
         if (idx >= total) break;
-        const uint32_t e = work.entries[idx];
+        // escape queries first, each list from its END: the queries of the positions that took the encoder longest
+        // come last in a list and are, on average, the long read-outs -- started first, they do not end up as the launch's tail
+        const uint32_t e = AG_LADDER_PICK(idx);
         const unsigned int pos = e >> 16;           // position << 16 | point << 5 | kind << 4 | prey-neighbour mask
         const int kind = (e >> 4) & 1, a = (e >> 5) & 511;
         const int pl = kind ? esc_plane : cap_plane;
@@ -581,6 +591,7 @@ int work_get(int npos, enc::LadderWork* w) {
     w->head = reinterpret_cast<unsigned int*>(s.mem);
     w->bits = reinterpret_cast<uint32_t*>(s.mem + 256);
     w->entries = w->bits + s.cap_pos * 24;
+    w->esc_base = (unsigned int)(s.cap_pos * (kWorkEntriesPerPos / 2));
     return AG_OK;
 }
 }  // namespace
@@ -602,11 +613,11 @@ int encode_launch(const int8_t* board, const uint8_t* age, const int8_t* player,
     const int n = size * size;
     for (int start = 0; start < npos; start += kWorkChunk) {
         const int cnt = npos - start < kWorkChunk ? npos - start : kWorkChunk;
-        enc::LadderWork work = {nullptr, nullptr, nullptr};
+        enc::LadderWork work = {nullptr, nullptr, nullptr, 0};
         if (tab.need_ladder) {
             int rc = work_get(cnt, &work);
             if (rc) return rc;
-            AG_CUDA(cudaMemsetAsync(work.head, 0, 2 * sizeof(unsigned int), stream));
+            AG_CUDA(cudaMemsetAsync(work.head, 0, 4 * sizeof(unsigned int), stream));
         }
         // small batches: fewer warps per CTA so that every SM gets positions
         int warps = cnt / (sm_count() * 3);

@@ -70,3 +70,24 @@ def test_bucketed_allreduce_world2_gloo():
         assert p.exitcode == 0
     assert all(ok for _, ok, _ in res)
     assert abs(res[0][2] - res[1][2]) < 1e-3  # both ranks hold the same averaged gradient
+
+
+def test_exchange_plan_for_the_counter_gated_path():
+    """plan_exchange: the first layer's bucket first (its gradient is queued ahead of the chained launch), the chain's layers
+    top down with the head's slice in the first of them, layers 1-2 together last; every float covered exactly once"""
+    from alphago_b200.training import plan_exchange
+    for n_conv in (3, 4, 5, 12, 13):
+        for buckets in (2, 3, 5, 6, 20):
+            offs = _offsets(n_conv)
+            plan = plan_exchange(n_conv, offs, buckets)
+            cover = np.zeros(offs[-1], np.int32)
+            for lo, hi, s, e in plan:
+                assert 0 <= lo < hi <= n_conv and s == offs[lo]
+                cover[s:e] += 1
+            assert (cover == 1).all(), (n_conv, buckets)
+            if n_conv >= 4:
+                assert plan[0][:2] == (0, 1) and plan[-1][:2] == (1, 3)
+                assert plan[1][1] == n_conv and plan[1][3] == offs[-1]          # the head's slice rides with the top layers
+                tops = [hi for lo, hi, _, _ in plan[1:]]
+                assert tops == sorted(tops, reverse=True)                        # top down: the order the chain finishes them
+                assert len(plan) <= max(3, buckets)
