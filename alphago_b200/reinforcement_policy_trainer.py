@@ -8,19 +8,24 @@ the game's result (rpt.py:95-102); `run` loops over mini-batches.  What changes 
 PACKED when they occur (726 bytes) and each game's planes are produced by one encoder launch at the end of the game
 instead of one Python feature pass per move, and the update is the CUDA training step.
 
-Two things the reference does are kept because a drop-in must learn the same thing, and can be switched off with
+Three things the reference does are kept because a drop-in must learn the same thing, and can be switched off with
 `reference_quirks=False`: (1) the positions cached before Black's move are also the ones paired with White's reply, so a
 learner playing White is trained on positions one ply old (rpt.py:56-65: `states_prev` is not refreshed between the two
 `do_move` calls); (2) the update is negative iff `winner == -1`, i.e. iff WHITE won, whatever colour the learner had
-(rpt.py:95-100).  With the switch off, White's moves are paired with the positions they were played in and the sign is
-positive iff the learner won.
+(rpt.py:95-100); (3) `GameState.copy()` shares the history list with the original (go.py:167), and the cached position is
+encoded only AFTER the move(s) were played on the original (rpt.py:39-41), so its turns_since planes are computed from a
+history that already holds those moves: every stone looks one (Black learner) or two (White learner) entries older, and a
+stone captured by Black's move shows up with age 0 if White then plays on its point.  `tests/test_rl_trainer_gpu.py` holds
+this to the reference's own `make_training_pairs`, run from its source on fake policies (`tests/golden/ref_selfplay.npz`).
+With the switch off, White's moves are paired with the positions they were played in, ages are the position's own and the
+sign is positive iff the learner won.
 """
 import argparse
 import os
 
 import numpy as np
 
-from . import go
+from . import _lib, go
 from .ai import ProbabilisticPolicyPlayer
 from .go import GameState
 from .models import SGD, CNNPolicy
@@ -50,7 +55,15 @@ def make_training_pairs(player, opp, features, mini_batch_size, reference_quirks
             if not st.is_end_of_game:   # only do more moves if not end of game already
                 st.do_move(mv)
                 if st.current_player != player_color and mv is not go.PASS_MOVE:   # the learner just moved
-                    packed[i].append(prev_packed[i])
+                    pk = prev_packed[i]
+                    if reference_quirks:
+                        # the reference encodes its cached copy NOW, and the copy shares the history list that has grown
+                        # meanwhile (go.py:167, rpt.py:39-41): the literal turns_since walk over (history now, board then)
+                        hist = np.asarray([-1 if m is None else m[0] * bsize + m[1] for m in st.history] or [0], np.int16)
+                        age = np.empty(bsize * bsize, np.uint8)
+                        _lib.lib().ag_age_from_history(bsize, _lib.np_ptr(pk[0]), _lib.np_ptr(hist), len(st.history), _lib.np_ptr(age))
+                        pk = (pk[0], age, pk[2], pk[3])
+                    packed[i].append(pk)
                     moves_made[i].append(flatten_idx(mv, bsize))
 
     plies = 0

@@ -8,6 +8,9 @@ arguments, same meaning of the result, but the positions and moves of the learne
 over and the planes of ALL recorded positions come from one encoder launch.  Moves are drawn as
 `ProbabilisticPolicyPlayer` draws them (ai.py:38-68: the policy over the sensible moves, raised to 1/temperature) from
 uniform numbers generated on the device, so the random stream differs from the host players' `np.random.choice`.
+Of the reference behaviours `reinforcement_policy_trainer.make_training_pairs` keeps under `reference_quirks=True`, this path
+reproduces the pairing of a White learner's moves with positions one ply old; the turns_since ageing through the shared
+history list of copied states (go.py:167) is NOT reproduced here: positions carry their own ages.
 """
 import ctypes as C
 

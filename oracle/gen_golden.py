@@ -385,14 +385,72 @@ def export_generator():
     print("ref_generator.npz written; used index", log_idx[:24], "transforms", log_tf[:16])
 
 
+class FakePolicy(object):
+    """stands in for CNNPolicy in the self-play pins: a deterministic, position-dependent weight for every move asked for
+    (the players normalise), and the `model.input_shape` the trainer reads (rpt.py:51).  tests/test_rl_trainer_gpu.py holds
+    the same class."""
+
+    def __init__(self, salt, size=19, planes=46):
+        self.salt = salt
+        self.model = type("M", (), {"input_shape": (None, planes, size, size)})()
+
+    def batch_eval_state(self, states, moves_lists=None):
+        return [[(m, 1.0 + ((m[0] * 7 + m[1] * 13 + len(st.history) * 3 + self.salt) % 11)) for m in ml]
+                for st, ml in zip(states, moves_lists)]
+
+
+def export_selfplay():
+    """tests/golden/ref_selfplay.npz: the reference's own self-play loop -- `make_training_pairs`
+    (reinforcement_policy_trainer.py:16-76) driving `ProbabilisticPolicyPlayer.get_moves` (ai.py:24-68), both executed from
+    the reference source by line range (the files as wholes are Python 2) on the reference GameState and Preprocess --
+    with FakePolicy in place of the Keras networks: two mini-batches of two 19x19 games played to the end, one with the
+    learner as Black and one as White.  Recorded: the planes and moves of every training pair, the winners.  This pins the
+    pairing of positions and moves (incl. positions one ply old for a White learner), the history aliasing of
+    GameState.copy() in the turns_since planes, pass and end-of-game handling, the sampling's use of np.random, and
+    get_winner."""
+    go, pp = ref_shim.load()
+    ai = os.path.join(ref_shim.REFERENCE_ROOT, "AlphaGo", "ai.py")
+    rpt = os.path.join(ref_shim.REFERENCE_ROOT, "AlphaGo", "training", "reinforcement_policy_trainer.py")
+    ns = _exec_reference_lines(ai, [(24, 68)], {"np": np, "go": go})
+    ns2 = _exec_reference_lines(rpt, [(16, 76)], {"np": np, "go": go, "GameState": go.GameState, "Preprocess": pp.Preprocess,
+                                                  "flatten_idx": lambda pos, size: pos[0] * size + pos[1], "xrange": range})
+    Player = ns["ProbabilisticPolicyPlayer"]
+    out = {"features": np.asarray(FEATS46)}
+    want = {go.BLACK: None, go.WHITE: None}
+    seed = 100
+    while any(v is None for v in want.values()):
+        np.random.seed(seed)
+        colour = int(np.random.choice([go.BLACK, go.WHITE]))   # what make_training_pairs draws first (rpt.py:54)
+        if want[colour] is None:
+            want[colour] = seed
+        seed += 1
+    for colour, seed in want.items():
+        tag = "black" if colour == go.BLACK else "white"
+        learner, opponent = Player(FakePolicy(3), temperature=0.67), Player(FakePolicy(8))
+        np.random.seed(seed)
+        X_list, y_list, winners = ns2["make_training_pairs"](learner, opponent, FEATS46, 2)
+        out["seed_" + tag] = np.int32(seed)
+        out["winners_" + tag] = np.asarray(winners, np.int8)
+        for g, (X, y) in enumerate(zip(X_list, y_list)):
+            assert X.shape[1:] == (46, 19, 19) and set(np.unique(X)) <= {0.0, 1.0} and (y.sum(1) == 1).all()
+            out["X_%s_%d" % (tag, g)] = np.packbits(X.astype(np.uint8).reshape(len(X), -1), axis=1)
+            out["y_%s_%d" % (tag, g)] = y.argmax(1).astype(np.int16)
+            print("self-play", tag, "game", g, "pairs", len(X), "winner", winners[g], flush=True)
+    np.savez_compressed(os.path.join(OUT, "ref_selfplay.npz"), **out)
+    print("ref_selfplay.npz written")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "hdf5":
         export_reference_hdf5_fixture()
     elif len(sys.argv) > 1 and sys.argv[1] == "sgf":
         export_reference_sgf_fixtures()
+    elif len(sys.argv) > 1 and sys.argv[1] == "selfplay":
+        export_selfplay()
     elif len(sys.argv) > 1 and sys.argv[1] == "stage2":
         export_policy_glue()
         export_generator()
+        export_selfplay()
     else:
         main()
         export_reference_hdf5_fixture()

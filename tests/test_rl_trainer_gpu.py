@@ -91,3 +91,40 @@ def test_run_loop_plays_to_the_end_on_a_small_board():
     np.random.seed(5)
     out = run(learner, args, [learner], FEATS)
     assert out == [learner] and len(run.player_wins_per_batch) == 2 and all(0 <= w <= 3 for w in run.player_wins_per_batch)
+
+
+class FakePolicy(object):
+    """the stand-in network of oracle/gen_golden.py `selfplay` (same weights for the same position and move)"""
+
+    def __init__(self, salt, size=19, planes=46):
+        self.salt = salt
+        self.model = type("M", (), {"input_shape": (None, planes, size, size)})()
+
+    def batch_eval_state(self, states, moves_lists=None):
+        return [[(m, 1.0 + ((m[0] * 7 + m[1] * 13 + len(st.history) * 3 + self.salt) % 11)) for m in ml]
+                for st, ml in zip(states, moves_lists)]
+
+
+@pytest.mark.parametrize("tag", ["black", "white"])
+def test_make_training_pairs_equals_the_reference_loop(golden_dir, tag):
+    """tests/golden/ref_selfplay.npz: the reference's make_training_pairs + ProbabilisticPolicyPlayer.get_moves run from their
+    source on the reference GameState / Preprocess with FakePolicy for the networks, two 19x19 games to the end per colour
+    of the learner.  The product's loop (host rules engine, CUDA encoder) must yield the same pairs bit for bit: same moves
+    drawn from np.random, the same positions -- one ply old for a White learner --, turns_since planes aged by the history
+    the copied state shares with the live one (go.py:167), the same winners."""
+    import os
+    g = np.load(os.path.join(golden_dir, "ref_selfplay.npz"))
+    feats = [str(f) for f in g["features"]]
+    learner, opponent = ProbabilisticPolicyPlayer(FakePolicy(3), temperature=0.67), ProbabilisticPolicyPlayer(FakePolicy(8))
+    np.random.seed(int(g["seed_" + tag]))
+    X_list, y_list, winners = make_training_pairs(learner, opponent, feats, 2)
+    assert make_training_pairs.player_color == (go.BLACK if tag == "black" else go.WHITE)
+    assert [int(w) for w in winners] == [int(w) for w in g["winners_" + tag]]
+    for i in range(2):
+        want_y = g["y_%s_%d" % (tag, i)]
+        want_X = np.unpackbits(g["X_%s_%d" % (tag, i)], axis=1)[:, :46 * 361].reshape(-1, 46, 19, 19)
+        assert np.array_equal(y_list[i].argmax(1), want_y), (tag, i)
+        assert X_list[i].shape == want_X.shape
+        if not np.array_equal(X_list[i], want_X):
+            bad = np.argwhere(X_list[i] != want_X)
+            raise AssertionError("%s game %d: %d bytes differ, planes %s, first %s" % (tag, i, len(bad), sorted(set(bad[:, 1].tolist())), bad[:3].tolist()))
