@@ -289,6 +289,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
             if (r3 != 0xFFFFu && r3 != r0 && r3 != r1 && r3 != r2) atomicAdd(&W.cnt[r3], 1u);
         }
         __syncwarp();
+        uint32_t pool_used = 0;
         {   // pool offsets: exclusive prefix sum of min(liberties, 8) over the root points of own groups
             uint32_t base = 0;
 #pragma unroll 1
@@ -302,6 +303,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                 if (p < NPAD) W.off[p] = base + incl - m;
                 base += __shfl_sync(0xffffffffu, incl, 31);
             }
+            pool_used = base;
         }
         __syncwarp();
 #pragma unroll 1
@@ -328,16 +330,47 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
         __syncwarp();
         ENC_T(2);
 
-        // ---- 4. per-point codes
+        // ---- 4. per-point codes.  4a: stones (liberties plane) and pad points, and the list of the EMPTY points, kept in the
+        // unused end of the liberty pool: the expensive part (4b) then runs on full warps of empty points instead of on
+        // whatever mix of stones and empty points 32 consecutive points hold.  When the pool leaves no room (it never
+        // does on positions from play) 4b walks all points as before.
+        int n_empty = 0;
+        {
+            const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll 1
-        for (int k = 0; k < 12; k++) {
-            const int p = k * 32 + lane;
-            uint32_t c_libs = 0xF, c_cap = 0xF, c_sa = 0xF, c_la = 0xF, c_sens = 0xF, lad = 0;
-            const int c = p < n ? W.col[p] : 1;
-            if (p < n && c != 0) {
-                const int l = W.cnt[W.lab[p]] & 0xFFFF;                       // preprocessing.py:46-61
-                if (l >= 1) c_libs = (uint32_t)(l >= 8 ? 7 : l - 1);
-            } else if (p < n) {
+            for (int k = 0; k < 12; k++) {
+                const int p = k * 32 + lane;
+                const int c = p < n ? W.col[p] : 1;
+                const bool e = p < n && c == 0;
+                const uint32_t bal = __ballot_sync(0xffffffffu, e);
+                if (e) {
+                    const uint32_t at = POOL - 1 - (uint32_t)(n_empty + __popc(bal & lt));
+                    if (at >= pool_used) W.pool[at] = (uint16_t)p;
+                } else if (p < NPAD) {
+                    uint32_t c_libs = 0xF;
+                    if (p < n) {
+                        const int l = W.cnt[W.lab[p]] & 0xFFFF;                   // preprocessing.py:46-61
+                        if (l >= 1) c_libs = (uint32_t)(l >= 8 ? 7 : l - 1);
+                    }
+                    W.codes[1][p] = (uint8_t)(c_libs | 0xF0u);
+                    W.codes[2][p] = 0xFF;
+                    W.codes[3][p] = 0x0F;
+                }
+                n_empty += __popc(bal);
+            }
+        }
+        const bool compact = pool_used + (uint32_t)n_empty <= (uint32_t)POOL;
+        const int iters = compact ? (n_empty + 31) >> 5 : 12;
+        __syncwarp();
+        // 4b: the empty points
+#pragma unroll 1
+        for (int k = 0; k < iters; k++) {
+            const int slot = k * 32 + lane;
+            int p = slot;
+            if (compact) p = slot < n_empty ? (int)W.pool[POOL - 1 - slot] : -1;
+            const bool valid = p >= 0 && p < n && W.col[p < 0 ? 0 : p] == 0;
+            uint32_t c_cap = 0xF, c_sa = 0xF, c_la = 0xF, c_sens = 0xF, lad = 0;
+            if (valid) {
                 const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
                 int nb[4];                                                    // go.py:96 order; -1 = off the board
                 nb[0] = x > 0 ? p - size : -1; nb[1] = x < size - 1 ? p + size : -1;
@@ -423,8 +456,8 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
                     if (tab.need_ladder) lad = mcap | mesc << 4;
                 }
             }
-            if (p < NPAD) {
-                W.codes[1][p] = (uint8_t)(c_libs | c_cap << 4);
+            if (valid) {
+                W.codes[1][p] = (uint8_t)(0xFu | c_cap << 4);   // no liberties plane on an empty point
                 W.codes[2][p] = (uint8_t)(c_sa | c_la << 4);
                 W.codes[3][p] = (uint8_t)c_sens;
             }
