@@ -30,7 +30,7 @@ sys.path.insert(0, ROOT)
 FEATS46 = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
            "liberties_after", "sensibleness", "zeros"]
 ENC_BYTES_PER_POSITION = 48 * 361 + 361 + 361 + 4  # planes out + board + age + player/ko
-ENC_WARP_INST_PER_POSITION_48 = (434935893 + 935732771) / 16384.0   # profiles/r2_encode_ncu_summary.json
+ENC_WARP_INST_PER_POSITION_48 = (365413068 + 947008922) / 16384.0   # profiles/r2_encode_ncu_summary.json
 
 
 def encode_config(n, feats, planes):
@@ -195,7 +195,7 @@ class EncodeWorkload(object):
             floor_ms = self.n * inst / (148 * 4 * clk) * 1e3
             out["issue_roofline"] = {"warp_instructions_per_position": inst, "sm_clock_hz": clk, "floor_ms": round(floor_ms, 4),
                                      "frac": round(floor_ms / ms_per_step, 4),
-                                     "note": "encode_kernel 26.5 k + ladder_resolve_kernel 57.1 k warp instructions per position"}
+                                     "note": "encode_kernel 22.3 k + ladder_resolve_kernel 57.8 k warp instructions per position"}
         return out
 
     def config(self):
