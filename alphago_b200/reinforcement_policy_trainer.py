@@ -117,8 +117,15 @@ def run(player, args, opponents, features, reference_quirks=True):
     for i_iter in range(args.iterations):
         for i_batch in range(args.save_every):
             opp = opponents[np.random.randint(len(opponents))]   # randomly choose opponent from pool
-            X_list, y_list, winners = make_training_pairs(player, opp, features, args.game_batch_size, reference_quirks,
-                                                          getattr(args, "max_plies", None))
+            if getattr(args, "device_games", False):
+                # the games live on the device (selfplay.py): a ply is encode -> forward -> one step kernel, no host round trip
+                from .selfplay import make_training_pairs_device
+                X_list, y_list, winners = make_training_pairs_device(player, opp, features, args.game_batch_size, reference_quirks,
+                                                                     getattr(args, "max_plies", None))
+                make_training_pairs.player_color = make_training_pairs_device.player_color
+            else:
+                X_list, y_list, winners = make_training_pairs(player, opp, features, args.game_batch_size, reference_quirks,
+                                                              getattr(args, "max_plies", None))
             n_wins = int(np.sum(np.array(winners) == 1))
             player_wins_per_batch.append(n_wins)
             print("Number of wins this batch: {}/{}".format(n_wins, args.game_batch_size))
@@ -136,6 +143,7 @@ def main(cmd_line_args=None):
     parser.add_argument("--save_every", help="Save policy every n mini-batches (Default: 500)", type=int, default=500)
     parser.add_argument("--game_batch_size", help="Number of games per mini-batch (Default: 20)", type=int, default=20)
     parser.add_argument("--iterations", help="Number of training iterations (i.e. mini-batch) (Default: 20)", type=int, default=20)
+    parser.add_argument("--device-games", help="Keep the games of a mini-batch in device memory (added flag; moves are then drawn from torch's generator)", default=False, action="store_true")
     args = parser.parse_args(cmd_line_args)
     # the reference ignores both positional files for now and starts from a fresh default net (rpt.py:155-165); here they are
     # honoured when they exist

@@ -107,3 +107,21 @@ def test_make_training_pairs_device_and_update():
     train_batch(pl, X, y, winners, 0.05)
     after = pol.model.get_weights()
     assert any(not np.array_equal(a, b) for a, b in zip(before, after)) and all(np.isfinite(a).all() for a in after)
+
+
+def test_run_loop_with_device_games():
+    """reinforcement_policy_trainer.run with --device-games: the same loop, the mini-batch's games on the device"""
+    import argparse
+    import torch
+    from alphago_b200.ai import ProbabilisticPolicyPlayer
+    from alphago_b200.models import CNNPolicy
+    from alphago_b200.reinforcement_policy_trainer import run
+    learner = ProbabilisticPolicyPlayer(CNNPolicy(FEATS, board=5, layers=3, filters_per_layer=32, seed=4, max_batch=16))
+    args = argparse.Namespace(learning_rate=0.02, iterations=1, save_every=2, game_batch_size=3, device_games=True)
+    torch.manual_seed(3)
+    np.random.seed(5)
+    before = [w.copy() for w in learner.policy.model.get_weights()]
+    out = run(learner, args, [learner], FEATS)
+    assert out == [learner] and len(run.player_wins_per_batch) == 2 and all(0 <= w <= 3 for w in run.player_wins_per_batch)
+    after = learner.policy.model.get_weights()
+    assert any(not np.array_equal(a, b) for a, b in zip(before, after)) and all(np.isfinite(a).all() for a in after)
