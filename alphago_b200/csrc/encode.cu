@@ -216,7 +216,11 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
         long long t_phase = clock64();
 #endif
         // ---- 1. load; board / turns_since codes; the position's bit boards for the ladder read-out
+        // The EMPTY points are listed at the end of the liberty pool (its front is filled in step 3): steps 3 and 4 then run on
+        // full warps of empty points instead of on whatever mix of stones and empty points 32 consecutive points hold.
         uint32_t my_blk = 0, my_wht = 0;
+        int n_empty = 0;
+        const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll 1
         for (int k = 0; k < 12; k++) {
             const int p = k * 32 + lane;
@@ -224,6 +228,9 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
             if (p < n) { c = board[p]; a = age[p]; }
             W.col[p] = (int8_t)c;
             const uint32_t bb = __ballot_sync(0xffffffffu, c > 0), bw = __ballot_sync(0xffffffffu, c < 0);
+            const uint32_t be = __ballot_sync(0xffffffffu, p < n && c == 0);
+            if (p < n && c == 0) W.pool[POOL - 1 - (n_empty + __popc(be & lt))] = (uint16_t)p;
+            n_empty += __popc(be);
             if (lane == k) { my_blk = bb; my_wht = bw; }
             if (p < NPAD) {
                 W.cnt[p] = 0;
@@ -236,23 +243,24 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
         __syncwarp();
         ENC_T(0);
 
-        // ---- 2. groups.  2a: every stone points at the left end of its horizontal run (pointer jumping)
+        // ---- 2. groups.  2a: every stone points at the left end of its horizontal run.  Run starts grow with the point index, so
+        // an inclusive max-scan of "my index if I start a run, else 0" over the lanes, carried from block to block, finds them
+        {
+            uint32_t carry = 0;
 #pragma unroll 1
-        for (int k = 0; k < 12; k++) {
-            const int p = k * 32 + lane;
-            if (p < NPAD) {
-                const int c = W.col[p];
-                const int y = s_xy[p] >> 8;
-                W.off[p] = (p < n && c != 0 && y > 0 && W.col[p - 1] == c) ? p - 1 : p;
+            for (int k = 0; k < 12; k++) {
+                const int p = k * 32 + lane;
+                const int c = p < n ? W.col[p] : 0;
+                const bool cont = c != 0 && (s_xy[p] >> 8) > 0 && W.col[p - 1] == c;
+                uint32_t r = cont ? 0u : (uint32_t)p;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, r, d); if (lane >= d) r = max(r, v); }
+                r = max(r, carry);
+                if (p < NPAD) W.off[p] = r;
+                carry = __shfl_sync(0xffffffffu, r, 31);
             }
         }
         __syncwarp();
-#pragma unroll 1
-        for (int r = 0; r < 5; r++) {   // runs are at most 19 long: 2^5 >= 19.  In place: a racing read sees an ancestor either way
-#pragma unroll 4
-            for (int k = 0; k < 12; k++) { const int p = k * 32 + lane; if (p < NPAD) W.off[p] = W.off[W.off[p]]; }
-            __syncwarp();
-        }
         // 2b: one union per pair of vertically touching runs (the edge whose left neighbour does not already join them)
 #pragma unroll 1
         for (int k = 0; k < 12; k++) {
@@ -278,8 +286,14 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
 #pragma unroll 1
         for (int k = 0; k < 12; k++) {
             const int p = k * 32 + lane;
-            if (p >= n) continue;
-            if (W.col[p] != 0) { atomicAdd(&W.cnt[W.lab[p]], 1u << 16); continue; }
+            if (p < n && W.col[p] != 0) atomicAdd(&W.cnt[W.lab[p]], 1u << 16);
+        }
+        const int e_iters = (n_empty + 31) >> 5;
+#pragma unroll 1
+        for (int k = 0; k < e_iters; k++) {
+            const int slot = k * 32 + lane;
+            if (slot >= n_empty) continue;
+            const int p = W.pool[POOL - 1 - slot];
             const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
             const uint32_t r0 = x > 0 ? W.lab[p - size] : 0xFFFFu, r1 = x < size - 1 ? W.lab[p + size] : 0xFFFFu;
             const uint32_t r2 = y > 0 ? W.lab[p - 1] : 0xFFFFu, r3 = y < size - 1 ? W.lab[p + 1] : 0xFFFFu;
@@ -306,9 +320,14 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
             pool_used = base;
         }
         __syncwarp();
+        // the list of empty points survives only if the liberty lists written now stay below it (always, on positions from play)
+        const bool compact = pool_used + (uint32_t)n_empty <= (uint32_t)POOL;
+        const int iters = compact ? e_iters : 12;
 #pragma unroll 1
-        for (int k = 0; k < 12; k++) {
-            const int p = k * 32 + lane;
+        for (int k = 0; k < iters; k++) {
+            const int slot = k * 32 + lane;
+            int p = slot;
+            if (compact) p = slot < n_empty ? (int)W.pool[POOL - 1 - slot] : n;
             if (p >= n || W.col[p] != 0) continue;
             const int x = s_xy[p] & 255, y = s_xy[p] >> 8;
             uint32_t r[4];
@@ -330,37 +349,22 @@ __global__ void __launch_bounds__(WARPS * 32, 3) encode_kernel(
         __syncwarp();
         ENC_T(2);
 
-        // ---- 4. per-point codes.  4a: stones (liberties plane) and pad points, and the list of the EMPTY points, kept in the
-        // unused end of the liberty pool: the expensive part (4b) then runs on full warps of empty points instead of on
-        // whatever mix of stones and empty points 32 consecutive points hold.  When the pool leaves no room (it never
-        // does on positions from play) 4b walks all points as before.
-        int n_empty = 0;
-        {
-            const uint32_t lt = (1u << lane) - 1u;
+        // ---- 4. per-point codes.  4a: stones (liberties plane) and pad points; 4b: the empty points, by the list when it is intact
 #pragma unroll 1
-            for (int k = 0; k < 12; k++) {
-                const int p = k * 32 + lane;
-                const int c = p < n ? W.col[p] : 1;
-                const bool e = p < n && c == 0;
-                const uint32_t bal = __ballot_sync(0xffffffffu, e);
-                if (e) {
-                    const uint32_t at = POOL - 1 - (uint32_t)(n_empty + __popc(bal & lt));
-                    if (at >= pool_used) W.pool[at] = (uint16_t)p;
-                } else if (p < NPAD) {
-                    uint32_t c_libs = 0xF;
-                    if (p < n) {
-                        const int l = W.cnt[W.lab[p]] & 0xFFFF;                   // preprocessing.py:46-61
-                        if (l >= 1) c_libs = (uint32_t)(l >= 8 ? 7 : l - 1);
-                    }
-                    W.codes[1][p] = (uint8_t)(c_libs | 0xF0u);
-                    W.codes[2][p] = 0xFF;
-                    W.codes[3][p] = 0x0F;
+        for (int k = 0; k < 12; k++) {
+            const int p = k * 32 + lane;
+            const int c = p < n ? W.col[p] : 1;
+            if (c != 0 && p < NPAD) {
+                uint32_t c_libs = 0xF;
+                if (p < n) {
+                    const int l = W.cnt[W.lab[p]] & 0xFFFF;                   // preprocessing.py:46-61
+                    if (l >= 1) c_libs = (uint32_t)(l >= 8 ? 7 : l - 1);
                 }
-                n_empty += __popc(bal);
+                W.codes[1][p] = (uint8_t)(c_libs | 0xF0u);
+                W.codes[2][p] = 0xFF;
+                W.codes[3][p] = 0x0F;
             }
         }
-        const bool compact = pool_used + (uint32_t)n_empty <= (uint32_t)POOL;
-        const int iters = compact ? (n_empty + 31) >> 5 : 12;
         __syncwarp();
         // 4b: the empty points
 #pragma unroll 1
