@@ -8,7 +8,7 @@
 //
 // Per position (flat point p = x*size+y, planes [f][x][y], AlphaGo/util.py:6-8); lane l owns points l, l+32, ...:
 //   1. board / age -> shared memory; colour and turns_since codes           (coalesced byte loads)
-//   2. groups: horizontal runs by pointer jumping (5 rounds), then ONE pass of lock-free unions (atomicMin hooking)
+//   2. groups: horizontal runs by a segmented max-scan over the lanes, then ONE pass of lock-free unions (atomicMin hooking)
 //      over the vertical edges that join two runs for the first time, then a flatten to the root point
 //   3. per group: stones and liberties (shared-memory atomics); the liberties of the side to move's groups, up to 8
 //      each, in one pool laid out by a warp prefix sum (sum of min(libs, 8) <= 964 on any 19x19 board)
