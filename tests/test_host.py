@@ -140,3 +140,33 @@ def test_playout_positions_are_consistent():
     planes = og.encode_batch(b, a, pl, ko, 19, ["board", "liberties"])
     stones = planes[:, 0] + planes[:, 1]
     assert np.array_equal(planes[:, 3:].sum(1), stones)
+
+
+def test_entry_points_refuse_bad_arguments_before_touching_the_device():
+    """error behaviour of the C ABI: a negative status (or NULL) and a message, no CUDA call -- checkable without a GPU"""
+    L = _lib.lib()
+    i32 = np.asarray([0, 1, 2], np.int32)
+    p = _lib.np_ptr(i32)
+    nul = ctypes.c_void_p(0)
+    assert L.ag_encode(nul, nul, nul, nul, 4, 20, p, 3, nul, nul) == -1 and "size" in _lib.last_error()          # AG_EINVAL
+    assert L.ag_encode(nul, nul, nul, nul, 4, 19, p, 0, nul, nul) == -1
+    bad = np.asarray([0, 99], np.int32)
+    assert L.ag_encode(nul, nul, nul, nul, 4, 19, _lib.np_ptr(bad), 2, nul, nul) == -1 and "feature" in _lib.last_error()
+    assert L.ag_encode(nul, nul, nul, nul, 4, 19, p, 3, nul, nul) == -1 and "null" in _lib.last_error()
+    assert L.ag_encode(nul, nul, nul, nul, 0, 19, p, 3, nul, nul) == 0                                              # empty batch: nothing to do
+    f = np.asarray([64, 64], np.int32)
+    for widths, what in (([5, 4], "odd"), ([7, 3], "odd")):
+        w = np.asarray(widths, np.int32)
+        assert not L.ag_net_create(19, 48, 2, _lib.np_ptr(f), _lib.np_ptr(w), 0, 8) and what in _lib.last_error()
+    w = np.asarray([5, 3], np.int32)
+    g = np.asarray([64, 32], np.int32)
+    assert not L.ag_net_create(19, 48, 2, _lib.np_ptr(g), _lib.np_ptr(w), 0, 8) and "same filter count" in _lib.last_error()
+    assert L.ag_selfplay_step(nul, nul, nul, nul, nul, nul, nul, nul, 361, nul, 1.0, 4, 25, nul, nul) == -1
+    assert L.ag_selfplay_step(nul, nul, nul, nul, nul, nul, nul, nul, 10, nul, 1.0, 4, 19, nul, nul) == -1           # mask rows shorter than a board
+    assert L.ag_selfplay_step(nul, nul, nul, nul, nul, nul, nul, nul, 361, nul, 1.0, 4, 19, nul, nul) == -1 and "null" in _lib.last_error()
+    assert L.ag_selfplay_winner(nul, nul, 0, 19, 7.5, nul, nul) == 0
+    rec = (ctypes.c_ubyte * 144)()
+    assert not L.ag_xchg_create(0, 1, nul, 1024, 16, rec) and "world" in _lib.last_error()                          # a lone rank has nothing to exchange
+    assert not L.ag_xchg_create(3, 2, nul, 1024, 16, rec)
+    assert L.ag_state_new(1) is None and L.ag_state_new(20) is None
+    assert L.ag_wgrad_partial_bytes(3, 192, 192) > 9 * 192 * 192 * 4 - 1 and L.ag_wgrad_scratch_bytes(3, 100, 192, 1000) == 0
